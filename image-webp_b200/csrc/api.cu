@@ -1,0 +1,958 @@
+// api.cu -- C ABI of libwebpb200.so (include/webpb200.h): contexts, the batched lossy path
+// (host entropy decode -> packed arrays -> device kernels -> RGB(A)), the WebPDecoder-shaped
+// single-image surface and animation compositing.  There is no CPU pixel path in this library:
+// every decode call needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/webpb200.h"
+#include "host_container.h"
+#include "host_vp8.h"
+#include "host_vp8l.h"
+#include "kernels.cuh"
+
+using namespace webpb200;
+
+namespace {
+
+template <class F>
+void parallel_for(int n, int threads, F fn) {
+    if (threads < 1) threads = 1;
+    if (threads > n) threads = n;
+    if (threads <= 1) {
+        for (int i = 0; i < n; i++) fn(i);
+        return;
+    }
+    std::atomic<int> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const int i = next.fetch_add(1);
+            if (i >= n) return;
+            fn(i);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; t++) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+}
+
+struct DevBuf {
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        n = (n + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+struct PinBuf {
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        n = (n + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
+        cudaError_t e = cudaMallocHost(&p, n);
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// One unit of reconstruction work: a VP8 chunk, optionally with the ALPH chunk that goes with it.
+struct WorkItem {
+    const uint8_t* vp8 = nullptr;
+    size_t vp8_len = 0;
+    const uint8_t* alph = nullptr;
+    size_t alph_len = 0;
+    int check_w = 0, check_h = 0;  // container's size; 0 = do not compare (decoder.rs:814-857)
+    int alph_w = 0, alph_h = 0;    // size the ALPH plane is coded for
+    int bpp = 3;
+    int status = 0;
+    Vp8Dims dims{0, 0, 0, 0};
+};
+
+inline uint64_t align256(uint64_t v) { return (v + 255) & ~uint64_t(255); }
+
+static_assert(sizeof(webpb200_frame_desc) == 136 && sizeof(webpb200_mb_desc) == 16 && sizeof(webpb200_segment) == 16,
+              "boundary structs changed size: update include/webpb200.h and the bindings");
+
+}  // namespace
+
+struct webpb200_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    std::string err;
+    uint64_t launches = 0;
+
+    PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux;
+    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out;
+
+    // current batch
+    int n = 0;
+    std::vector<WorkItem> items;
+    uint64_t total_mbs = 0, total_rows = 0, total_px = 0;
+    uint64_t plane_bytes = 0, out_bytes = 0, alpha_bytes = 0;
+    size_t aux_rowmap_off = 0, aux_lists_off = 0, aux_bytes = 0;
+    BatchDev bd{};
+    bool uploaded = false;
+
+    bool fail(cudaError_t e, const char* what) {
+        if (e == cudaSuccess) return false;
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        return true;
+    }
+};
+
+namespace {
+
+#define CU(c, call, what)                      \
+    do {                                       \
+        if ((c)->fail((call), what)) return -WEBPB200_ERR_CUDA; \
+    } while (0)
+
+// Host side of a batch: probe sizes, lay the arenas out, entropy-decode into pinned staging.
+int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
+    cudaSetDevice(c->device);
+    c->items = std::move(in_items);
+    c->n = (int)c->items.size();
+    c->uploaded = false;
+    const int n = c->n;
+    auto& items = c->items;
+
+    parallel_for(n, threads, [&](int i) {
+        WorkItem& it = items[i];
+        if (it.status) return;
+        it.status = vp8_probe(it.vp8, it.vp8_len, &it.dims);
+        if (it.status) return;
+        if (it.dims.width == 0 || it.dims.height == 0) {
+            it.status = WEBPB200_ERR_INCONSISTENT_SIZE;  // no pixels to reconstruct
+            return;
+        }
+        if (it.check_w && (it.dims.width != it.check_w || it.dims.height != it.check_h)) it.status = WEBPB200_ERR_INCONSISTENT_SIZE;
+    });
+
+    // arenas: dead items keep zero-sized slots
+    CU(c, c->h_frames.reserve(sizeof(webpb200_frame_desc) * (size_t)std::max(n, 1)), "pinned frames");
+    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
+    std::memset(frames, 0, sizeof(webpb200_frame_desc) * (size_t)n);
+    uint64_t mbs = 0, rows = 0, px = 0, poff = 0, ooff = 0, aoff = 0;
+    uint32_t max_w = 0, max_h = 0;
+    for (int i = 0; i < n; i++) {
+        WorkItem& it = items[i];
+        webpb200_frame_desc& fd = frames[i];
+        fd.mb_base = (uint32_t)mbs;
+        fd.row_base = (uint32_t)rows;
+        fd.y_off = poff;
+        fd.u_off = poff;
+        fd.v_off = poff;
+        fd.out_off = ooff;
+        fd.alpha_off = aoff;
+        fd.out_bpp = (uint8_t)it.bpp;
+        fd.upsampling = (uint8_t)upsampling;
+        if (it.status) continue;  // width/height/mbw/mbh stay 0: kernels see an empty frame
+        const uint64_t m = (uint64_t)it.dims.mbw * it.dims.mbh;
+        if (mbs + m > 0xffffffffull) { it.status = WEBPB200_ERR_IMAGE_TOO_LARGE; continue; }
+        fd.width = (uint16_t)it.dims.width; fd.height = (uint16_t)it.dims.height;
+        fd.mbw = (uint16_t)it.dims.mbw; fd.mbh = (uint16_t)it.dims.mbh;
+        fd.y_off = poff;
+        fd.u_off = align256(fd.y_off + m * 256);
+        fd.v_off = align256(fd.u_off + m * 64);
+        poff = align256(fd.v_off + m * 64);
+        ooff = align256(ooff + (uint64_t)it.dims.width * it.dims.height * it.bpp);
+        if (it.alph && it.bpp == 4) {
+            fd.alpha_mode = 1;
+            aoff = align256(aoff + (uint64_t)it.dims.width * it.dims.height);
+        }
+        mbs += m;
+        rows += it.dims.mbh;
+        px += (uint64_t)it.dims.width * it.dims.height;
+        max_w = std::max<uint32_t>(max_w, it.dims.width);
+        max_h = std::max<uint32_t>(max_h, it.dims.height);
+    }
+    c->total_mbs = mbs; c->total_rows = rows; c->total_px = px;
+    c->plane_bytes = poff; c->out_bytes = ooff; c->alpha_bytes = aoff;
+
+    CU(c, c->h_mbs.reserve(sizeof(webpb200_mb_desc) * (size_t)std::max<uint64_t>(mbs, 1)), "pinned mbs");
+    CU(c, c->h_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(mbs, 1)), "pinned levels");
+    CU(c, c->h_alpha.reserve((size_t)std::max<uint64_t>(aoff, 1)), "pinned alpha");
+    c->aux_rowmap_off = 0;
+    c->aux_lists_off = (size_t)align256(4 * rows);
+    c->aux_bytes = c->aux_lists_off + (size_t)align256(16 * (uint64_t)std::max(n, 1));
+    CU(c, c->h_aux.reserve(c->aux_bytes), "pinned aux");
+    webpb200_mb_desc* hm = reinterpret_cast<webpb200_mb_desc*>(c->h_mbs.p);
+    int16_t* hl = reinterpret_cast<int16_t*>(c->h_levels.p);
+
+    // entropy decode (the serial-per-image part) on the host threads
+    parallel_for(n, threads, [&](int i) {
+        WorkItem& it = items[i];
+        if (it.status) return;
+        webpb200_frame_desc& fd = frames[i];
+        const size_t m = (size_t)fd.mbw * fd.mbh;
+        int st = vp8_entropy_decode(it.vp8, it.vp8_len, &fd, hm + fd.mb_base, hl + (size_t)fd.mb_base * WEBPB200_LEVELS_PER_MB);
+        if (!st && fd.alpha_mode) {
+            int filter = 0;
+            bool compressed = false;
+            st = parse_alph_header(it.alph, it.alph_len, &filter, &compressed);
+            uint8_t* dst = c->h_alpha.p + fd.alpha_off;
+            const size_t want = (size_t)it.alph_w * it.alph_h, have = (size_t)fd.width * fd.height;
+            if (!st && want != have) st = WEBPB200_ERR_INCONSISTENT_SIZE;
+            if (!st) {
+                fd.alpha_filter = (uint8_t)filter;
+                if (compressed) st = vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, dst);
+                else if (it.alph_len - 1 < want) st = WEBPB200_ERR_IO;
+                else std::memcpy(dst, it.alph + 1, want);
+            }
+        }
+        if (st) {  // keep the slot harmless for the kernels: all-DC, all-zero macroblocks
+            it.status = st;
+            std::memset(hm + fd.mb_base, 0, sizeof(webpb200_mb_desc) * m);
+            std::memset(hl + (size_t)fd.mb_base * WEBPB200_LEVELS_PER_MB, 0, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * m);
+            fd.filter_level = 0;
+            fd.alpha_mode = 0;
+        }
+    });
+
+    // ticket -> image map and the ALPH lists by filter method
+    uint32_t* rowmap = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
+    int* lists = reinterpret_cast<int*>(c->h_aux.p + c->aux_lists_off);
+    BatchDev& bd = c->bd;
+    std::memset(&bd, 0, sizeof(bd));
+    for (int i = 0; i < n; i++) {
+        const webpb200_frame_desc& fd = frames[i];
+        for (uint32_t r = 0; r < fd.mbh; r++) rowmap[fd.row_base + r] = (uint32_t)i;
+        if (fd.alpha_mode && fd.out_bpp == 4) {
+            const int m = fd.alpha_filter & 3;
+            lists[m * n + bd.alpha_counts[m]++] = i;
+            bd.alpha_maxw[m] = std::max<uint32_t>(bd.alpha_maxw[m], fd.width);
+            bd.alpha_maxh[m] = std::max<uint32_t>(bd.alpha_maxh[m], fd.height);
+        }
+    }
+    bd.n_frames = n;
+    bd.total_rows = (uint32_t)rows;
+    bd.max_w = max_w;
+    bd.max_h = max_h;
+    bd.sm_count = c->sm_count;
+    bd.lay = scratch_layout(rows, mbs);
+    return 0;
+}
+
+int upload(webpb200_ctx* c) {
+    cudaSetDevice(c->device);
+    const int n = c->n;
+    CU(c, c->d_frames.reserve(sizeof(webpb200_frame_desc) * (size_t)std::max(n, 1)), "device frames");
+    CU(c, c->d_mbs.reserve(sizeof(webpb200_mb_desc) * (size_t)std::max<uint64_t>(c->total_mbs, 1)), "device mbs");
+    CU(c, c->d_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(c->total_mbs, 1)), "device levels");
+    CU(c, c->d_alpha.reserve((size_t)std::max<uint64_t>(c->alpha_bytes, 1)), "device alpha");
+    CU(c, c->d_aux.reserve(c->aux_bytes), "device aux");
+    CU(c, c->d_planes.reserve((size_t)std::max<uint64_t>(c->plane_bytes, 1)), "device planes");
+    CU(c, c->d_out.reserve((size_t)std::max<uint64_t>(c->out_bytes, 1)), "device out");
+    CU(c, c->d_scratch.reserve((size_t)c->bd.lay.total), "device scratch");
+    cudaStream_t s = c->stream;
+    CU(c, cudaMemcpyAsync(c->d_frames.p, c->h_frames.p, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
+    if (c->total_mbs) {
+        CU(c, cudaMemcpyAsync(c->d_mbs.p, c->h_mbs.p, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D mbs");
+        CU(c, cudaMemcpyAsync(c->d_levels.p, c->h_levels.p, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D levels");
+    }
+    if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+    CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
+    // the row map lives in the scratch arena next to the counters it is used with
+    if (c->total_rows)
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
+    BatchDev& bd = c->bd;
+    bd.frames = reinterpret_cast<const webpb200_frame_desc*>(c->d_frames.p);
+    bd.mbs = reinterpret_cast<const webpb200_mb_desc*>(c->d_mbs.p);
+    bd.levels = reinterpret_cast<const int16_t*>(c->d_levels.p);
+    bd.alpha = c->d_alpha.p;
+    bd.planes = c->d_planes.p;
+    bd.out = c->d_out.p;
+    bd.scratch = c->d_scratch.p;
+    bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + c->aux_lists_off);
+    c->uploaded = true;
+    return 0;
+}
+
+// events: optional array of 5 events recorded before/after each stage (timing runs)
+int reconstruct(webpb200_ctx* c, const BatchDev& bd, unsigned stages, cudaStream_t s, cudaEvent_t* events) {
+    if (bd.total_rows == 0) return 0;
+    CU(c, cudaMemsetAsync(bd.scratch, 0, (size_t)bd.lay.zero_bytes, s), "clear counters");
+    if (events) cudaEventRecord(events[0], s);
+    if (stages & 1) { CU(c, launch_predict(bd, s), "k_predict"); c->launches++; }
+    if (events) cudaEventRecord(events[1], s);
+    if (stages & 2) { CU(c, launch_loopfilter(bd, s), "k_loopfilter"); c->launches++; }
+    if (events) cudaEventRecord(events[2], s);
+    if (stages & 4) { CU(c, launch_yuv2rgb(bd, s), "k_yuv2rgb"); c->launches++; }
+    if (events) cudaEventRecord(events[3], s);
+    if (stages & 8) {
+        int l = 0;
+        CU(c, launch_alpha(bd, s, &l), "k_alpha");
+        c->launches += (uint64_t)l;
+    }
+    if (events) cudaEventRecord(events[4], s);
+    return 0;
+}
+
+// after a stream sync: did a wavefront kernel trip its watchdog?
+int check_abort(webpb200_ctx* c) {
+    if (!c->uploaded || c->bd.total_rows == 0) return 0;
+    unsigned int word = 0;
+    CU(c, cudaMemcpy(&word, c->bd.scratch + c->bd.lay.tickets_off + 8, 4, cudaMemcpyDeviceToHost), "read abort word");
+    if (word) {
+        c->err = "wavefront watchdog: a row waited too long for the row above";
+        return -WEBPB200_ERR_CUDA;
+    }
+    return 0;
+}
+
+// D2H of the output arena into caller buffers; neighbouring images are sent as one copy when
+// both sides are contiguous
+int download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens) {
+    cudaSetDevice(c->device);
+    const webpb200_frame_desc* frames = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
+    const int n = c->n;
+    int i = 0;
+    while (i < n) {
+        if (c->items[i].status) { i++; continue; }
+        const size_t len = (size_t)frames[i].width * frames[i].height * frames[i].out_bpp;
+        if (out_lens[i] != len) { c->items[i].status = WEBPB200_ERR_IMAGE_TOO_LARGE; i++; continue; }  // decoder.rs:670-672
+        uint64_t src = frames[i].out_off;
+        uint8_t* dst = outs[i];
+        size_t run = len;
+        int j = i + 1;
+        while (j < n && !c->items[j].status && frames[j].out_off == src + run && outs[j] == dst + run &&
+               out_lens[j] == (size_t)frames[j].width * frames[j].height * frames[j].out_bpp) {
+            run += out_lens[j];
+            j++;
+        }
+        CU(c, cudaMemcpyAsync(dst, c->d_out.p + src, run, cudaMemcpyDeviceToHost, c->stream), "D2H out");
+        i = j;
+    }
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    return check_abort(c);
+}
+
+int items_from_files(const uint8_t* const* files, const size_t* lens, int n, int threads, std::vector<WorkItem>* out) {
+    out->assign((size_t)n, WorkItem());
+    parallel_for(n, threads, [&](int i) {
+        WorkItem& it = (*out)[i];
+        Container ct;
+        it.status = parse_container(files[i], lens[i], &ct);
+        if (it.status) return;
+        if (ct.animated) { it.status = WEBPB200_ERR_INVALID_PARAM; return; }  // frames go through decode_animation / read_frame
+        if (!ct.chunks[CK_VP8].present) { it.status = ct.chunks[CK_VP8L].present ? WEBPB200_ERR_NOT_LOSSY : WEBPB200_ERR_CHUNK_MISSING; return; }
+        const Range r = ct.chunks[CK_VP8];
+        if (r.end > lens[i]) { it.status = WEBPB200_ERR_IO; return; }
+        it.vp8 = files[i] + r.start;
+        it.vp8_len = (size_t)r.size();
+        it.check_w = (int)ct.width;
+        it.check_h = (int)ct.height;
+        it.bpp = ct.has_alpha ? 4 : 3;
+        if (ct.has_alpha) {
+            const Range a = ct.chunks[CK_ALPH];
+            if (!a.present) { it.status = WEBPB200_ERR_CHUNK_MISSING; return; }  // decoder.rs:707-711
+            if (a.end > lens[i]) { it.status = WEBPB200_ERR_IO; return; }
+            it.alph = files[i] + a.start;
+            it.alph_len = (size_t)a.size();
+            it.alph_w = (int)ct.width;
+            it.alph_h = (int)ct.height;
+        }
+    });
+    return 0;
+}
+
+std::mutex g_default_mu;
+webpb200_ctx* g_default_ctx = nullptr;
+
+webpb200_ctx* default_ctx(int* status) {
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    if (!g_default_ctx) {
+        *status = webpb200_ctx_create(0, &g_default_ctx);
+        if (*status) g_default_ctx = nullptr;
+    }
+    return g_default_ctx;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// contexts
+// ------------------------------------------------------------------------------------------------
+extern "C" int webpb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
+    *out = nullptr;
+    if (device < 0 || device >= webpb200_device_count()) return WEBPB200_ERR_NO_DEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return WEBPB200_ERR_NO_DEVICE;
+    webpb200_ctx* c = new webpb200_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c;
+        return WEBPB200_ERR_CUDA;
+    }
+    c->sm_count = prop.multiProcessorCount;
+    for (auto& e : c->ev) cudaEventCreate(&e);
+    upload_tables_once();
+    if (cudaDeviceSynchronize() != cudaSuccess) {
+        delete c;
+        return WEBPB200_ERR_CUDA;
+    }
+    *out = c;
+    return 0;
+}
+
+extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux}) b->release();
+    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out})
+        b->release();
+    for (auto& e : c->ev) cudaEventDestroy(e);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" void* webpb200_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void webpb200_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+extern "C" const char* webpb200_last_cuda_error(const webpb200_ctx* c) { return c ? c->err.c_str() : ""; }
+extern "C" uint64_t webpb200_launch_count(const webpb200_ctx* c) { return c->launches; }
+
+// ------------------------------------------------------------------------------------------------
+// batched path
+// ------------------------------------------------------------------------------------------------
+extern "C" int webpb200_batch_prepare(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, int* status,
+                                      int upsampling, int host_threads) {
+    if (!c || n < 0) return -WEBPB200_ERR_INVALID_PARAM;
+    std::vector<WorkItem> items;
+    items_from_files(files, lens, n, host_threads, &items);
+    int rc = prepare_items(c, std::move(items), upsampling, host_threads);
+    if (rc) return rc;
+    int bad = 0;
+    for (int i = 0; i < n; i++) {
+        if (status) status[i] = c->items[i].status;
+        bad += c->items[i].status != 0;
+    }
+    return bad;
+}
+
+extern "C" int webpb200_batch_upload(webpb200_ctx* c) { return upload(c); }
+
+extern "C" int webpb200_batch_reconstruct(webpb200_ctx* c, unsigned stages) {
+    if (!c->uploaded) return -WEBPB200_ERR_INVALID_PARAM;
+    cudaSetDevice(c->device);
+    return reconstruct(c, c->bd, stages, c->stream, nullptr);
+}
+
+extern "C" int webpb200_batch_sync(webpb200_ctx* c) {
+    cudaSetDevice(c->device);
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    return check_abort(c);
+}
+
+extern "C" int webpb200_batch_download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens) { return download(c, outs, out_lens); }
+
+extern "C" int webpb200_batch_time(webpb200_ctx* c, unsigned stages, int iters, int flush_l2, float* ms_per_pass, float* kernel_ms) {
+    if (!c->uploaded || iters < 1) return -WEBPB200_ERR_INVALID_PARAM;
+    cudaSetDevice(c->device);
+    const size_t flush_bytes = size_t(256) << 20;  // > 126 MB of L2
+    if (flush_l2) CU(c, c->d_flush.reserve(flush_bytes), "flush buffer");
+    double total = 0, per[4] = {0, 0, 0, 0};
+    for (int it = 0; it < iters; it++) {
+        if (flush_l2) CU(c, cudaMemsetAsync(c->d_flush.p, it & 0xff, flush_bytes, c->stream), "flush");
+        int rc = reconstruct(c, c->bd, stages, c->stream, c->ev);
+        if (rc) return rc;
+        CU(c, cudaEventSynchronize(c->ev[4]), "event sync");
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]);
+        total += ms;
+        for (int k = 0; k < 4; k++) {
+            cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]);
+            per[k] += ms;
+        }
+    }
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    if (int rc = check_abort(c)) return rc;
+    if (ms_per_pass) *ms_per_pass = (float)(total / iters);
+    if (kernel_ms)
+        for (int k = 0; k < 4; k++) kernel_ms[k] = (float)(per[k] / iters);
+    return 0;
+}
+
+extern "C" int webpb200_batch_size(const webpb200_ctx* c, int* n_images, uint64_t* n_macroblocks, uint64_t* n_pixels, uint64_t* in_bytes,
+                                   uint64_t* out_bytes) {
+    if (n_images) *n_images = c->n;
+    if (n_macroblocks) *n_macroblocks = c->total_mbs;
+    if (n_pixels) *n_pixels = c->total_px;
+    if (in_bytes)
+        *in_bytes = sizeof(webpb200_frame_desc) * (uint64_t)c->n + c->total_mbs * (sizeof(webpb200_mb_desc) + 2 * WEBPB200_LEVELS_PER_MB) +
+                    c->alpha_bytes + c->aux_bytes;
+    if (out_bytes) {
+        uint64_t o = 0;
+        const webpb200_frame_desc* f = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
+        for (int i = 0; i < c->n; i++) o += (uint64_t)f[i].width * f[i].height * f[i].out_bpp;
+        *out_bytes = o;
+    }
+    return 0;
+}
+
+extern "C" int webpb200_batch_get_planes(webpb200_ctx* c, int image, uint8_t* y, uint8_t* u, uint8_t* v) {
+    if (!c->uploaded || image < 0 || image >= c->n) return -WEBPB200_ERR_INVALID_PARAM;
+    cudaSetDevice(c->device);
+    const webpb200_frame_desc& fd = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p)[image];
+    const size_t m = (size_t)fd.mbw * fd.mbh;
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    if (m == 0) return 0;
+    CU(c, cudaMemcpy(y, c->d_planes.p + fd.y_off, m * 256, cudaMemcpyDeviceToHost), "D2H y");
+    CU(c, cudaMemcpy(u, c->d_planes.p + fd.u_off, m * 64, cudaMemcpyDeviceToHost), "D2H u");
+    CU(c, cudaMemcpy(v, c->d_planes.p + fd.v_off, m * 64, cudaMemcpyDeviceToHost), "D2H v");
+    return 0;
+}
+
+extern "C" int webpb200_batch_get_packed(webpb200_ctx* c, int image, const webpb200_frame_desc** frame, const webpb200_mb_desc** mbs,
+                                         const int16_t** levels) {
+    if (image < 0 || image >= c->n) return -WEBPB200_ERR_INVALID_PARAM;
+    const webpb200_frame_desc* f = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p) + image;
+    if (frame) *frame = f;
+    if (mbs) *mbs = reinterpret_cast<const webpb200_mb_desc*>(c->h_mbs.p) + f->mb_base;
+    if (levels) *levels = reinterpret_cast<const int16_t*>(c->h_levels.p) + (size_t)f->mb_base * WEBPB200_LEVELS_PER_MB;
+    return 0;
+}
+
+extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
+                                     const size_t* out_lens, int* status, int upsampling, int host_threads) {
+    if (!c) return -WEBPB200_ERR_NO_DEVICE;
+    int rc = webpb200_batch_prepare(c, files, lens, n, nullptr, upsampling, host_threads);
+    if (rc < 0) return rc;
+    if ((rc = upload(c)) != 0) return rc;
+    if ((rc = reconstruct(c, c->bd, 0xF, c->stream, nullptr)) != 0) return rc;
+    if ((rc = download(c, outs, out_lens)) != 0) return rc;
+    int bad = 0;
+    for (int i = 0; i < n; i++) {
+        if (status) status[i] = c->items[i].status;
+        bad += c->items[i].status != 0;
+    }
+    return bad;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host half alone (no CUDA calls): container walk + entropy decode into caller arrays
+// ------------------------------------------------------------------------------------------------
+extern "C" int webpb200_host_entropy_decode(const uint8_t* file, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs, size_t mbs_cap,
+                                            int16_t* levels, size_t levels_cap, uint8_t* alpha, size_t alpha_cap) {
+    std::vector<WorkItem> items;
+    const uint8_t* files[1] = {file};
+    const size_t lens[1] = {len};
+    items_from_files(files, lens, 1, 1, &items);
+    WorkItem& it = items[0];
+    if (it.status) return it.status;
+    int st = vp8_probe(it.vp8, it.vp8_len, &it.dims);
+    if (st) return st;
+    if (it.dims.width != it.check_w || it.dims.height != it.check_h) return WEBPB200_ERR_INCONSISTENT_SIZE;
+    std::memset(fd, 0, sizeof(*fd));
+    fd->width = (uint16_t)it.dims.width; fd->height = (uint16_t)it.dims.height;
+    fd->mbw = (uint16_t)it.dims.mbw; fd->mbh = (uint16_t)it.dims.mbh;
+    fd->out_bpp = (uint8_t)it.bpp;
+    fd->alpha_mode = it.alph != nullptr;
+    if (!mbs || !levels) return 0;  // size query
+    const size_t m = (size_t)it.dims.mbw * it.dims.mbh;
+    if (mbs_cap < m || levels_cap < m * WEBPB200_LEVELS_PER_MB) return WEBPB200_ERR_INVALID_PARAM;
+    st = vp8_entropy_decode(it.vp8, it.vp8_len, fd, mbs, levels);
+    if (st) return st;
+    if (it.alph && alpha) {
+        int filter = 0;
+        bool compressed = false;
+        st = parse_alph_header(it.alph, it.alph_len, &filter, &compressed);
+        if (st) return st;
+        const size_t want = (size_t)it.alph_w * it.alph_h;
+        if (alpha_cap < want) return WEBPB200_ERR_INVALID_PARAM;
+        fd->alpha_filter = (uint8_t)filter;
+        if (compressed) return vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, alpha);
+        if (it.alph_len - 1 < want) return WEBPB200_ERR_IO;
+        std::memcpy(alpha, it.alph + 1, want);
+    }
+    return 0;
+}
+
+extern "C" void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8_t* out16) { bpred_table_eval(mode, edge13, out16); }
+
+// ------------------------------------------------------------------------------------------------
+// device-resident seam
+// ------------------------------------------------------------------------------------------------
+extern "C" int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n, uint64_t* plane_bytes, uint64_t* out_bytes,
+                                        uint64_t* scratch_bytes) {
+    uint64_t p = 0, o = 0, rows = 0, mbs = 0;
+    for (int i = 0; i < n; i++) {
+        const uint64_t m = (uint64_t)frames[i].mbw * frames[i].mbh;
+        p = std::max(p, align256(frames[i].v_off + m * 64));
+        o = std::max(o, align256(frames[i].out_off + (uint64_t)frames[i].width * frames[i].height * frames[i].out_bpp));
+        rows = std::max<uint64_t>(rows, (uint64_t)frames[i].row_base + frames[i].mbh);
+        mbs = std::max<uint64_t>(mbs, (uint64_t)frames[i].mb_base + m);
+    }
+    if (plane_bytes) *plane_bytes = p;
+    if (out_bytes) *out_bytes = o;
+    if (scratch_bytes) *scratch_bytes = scratch_layout(rows, mbs).total + align256(16 * (uint64_t)std::max(n, 1));
+    return 0;
+}
+
+extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const webpb200_frame_desc* d_frames, int n,
+                                           const webpb200_mb_desc* d_mbs, const int16_t* d_levels, const uint8_t* d_alpha,
+                                           uint8_t* d_planes, uint8_t* d_out, void* d_scratch, unsigned stages, void* stream) {
+    if (n <= 0) return 0;
+    int st = 0;
+    webpb200_ctx* c = default_ctx(&st);
+    if (!c) return -st;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    uint64_t rows = 0, mbs = 0;
+    BatchDev bd;
+    std::memset(&bd, 0, sizeof(bd));
+    for (int i = 0; i < n; i++) {
+        rows = std::max<uint64_t>(rows, (uint64_t)hf[i].row_base + hf[i].mbh);
+        mbs = std::max<uint64_t>(mbs, (uint64_t)hf[i].mb_base + (uint64_t)hf[i].mbw * hf[i].mbh);
+        bd.max_w = std::max<uint32_t>(bd.max_w, hf[i].width);
+        bd.max_h = std::max<uint32_t>(bd.max_h, hf[i].height);
+    }
+    bd.lay = scratch_layout(rows, mbs);
+    // row map and ALPH lists are built on the host and copied into the caller's scratch arena
+    std::vector<uint32_t> rowmap((size_t)rows, 0);
+    std::vector<int> lists((size_t)4 * n, 0);
+    for (int i = 0; i < n; i++) {
+        for (uint32_t r = 0; r < hf[i].mbh; r++) rowmap[hf[i].row_base + r] = (uint32_t)i;
+        if (hf[i].alpha_mode && hf[i].out_bpp == 4) {
+            const int m = hf[i].alpha_filter & 3;
+            lists[(size_t)m * n + bd.alpha_counts[m]++] = i;
+            bd.alpha_maxw[m] = std::max<uint32_t>(bd.alpha_maxw[m], hf[i].width);
+            bd.alpha_maxh[m] = std::max<uint32_t>(bd.alpha_maxh[m], hf[i].height);
+        }
+    }
+    uint8_t* scratch = static_cast<uint8_t*>(d_scratch);
+    CU(c, cudaMemcpyAsync(scratch + bd.lay.rowmap_off, rowmap.data(), 4 * (size_t)rows, cudaMemcpyHostToDevice, s), "rowmap");
+    CU(c, cudaMemcpyAsync(scratch + bd.lay.total, lists.data(), sizeof(int) * lists.size(), cudaMemcpyHostToDevice, s), "lists");
+    CU(c, cudaStreamSynchronize(s), "sync");  // the host vectors go away
+    bd.frames = d_frames; bd.mbs = d_mbs; bd.levels = d_levels; bd.alpha = d_alpha;
+    bd.planes = d_planes; bd.out = d_out; bd.scratch = scratch;
+    bd.n_frames = n; bd.total_rows = (uint32_t)rows; bd.sm_count = c->sm_count;
+    bd.alpha_lists = reinterpret_cast<const int*>(scratch + bd.lay.total);
+    return reconstruct(c, bd, stages, s, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------
+// WebPDecoder surface
+// ------------------------------------------------------------------------------------------------
+struct webpb200_decoder {
+    Container ct;
+    int upsampling = 0;
+    bool has_bg = false;
+    uint8_t bg[4] = {0, 0, 0, 0};
+    // AnimationState, decoder.rs:240-263
+    uint32_t next_frame = 0;
+    uint64_t next_frame_start = 0;
+    bool dispose_next = true;
+    uint32_t pw = 0, ph = 0, px = 0, py = 0;
+    bool canvas_live = false;
+    DevBuf canvas, frame_out;
+};
+
+extern "C" int webpb200_open(const uint8_t* data, size_t len, int upsampling, webpb200_decoder** out) {
+    *out = nullptr;
+    webpb200_decoder* d = new webpb200_decoder();
+    int st = parse_container(data, len, &d->ct);
+    if (st) {
+        delete d;
+        return st;
+    }
+    d->upsampling = upsampling;
+    d->next_frame_start = d->ct.first_anmf;
+    *out = d;
+    return 0;
+}
+extern "C" void webpb200_close(webpb200_decoder* d) {
+    if (!d) return;
+    d->canvas.release();
+    d->frame_out.release();
+    delete d;
+}
+extern "C" void webpb200_dimensions(const webpb200_decoder* d, uint32_t* w, uint32_t* h) { *w = d->ct.width; *h = d->ct.height; }
+extern "C" int webpb200_has_alpha(const webpb200_decoder* d) { return d->ct.has_alpha; }
+extern "C" int webpb200_is_animated(const webpb200_decoder* d) { return d->ct.animated; }
+extern "C" int webpb200_is_lossy(const webpb200_decoder* d) { return d->ct.is_lossy; }
+extern "C" uint32_t webpb200_num_frames(const webpb200_decoder* d) { return d->ct.num_frames; }
+extern "C" uint32_t webpb200_loop_count(const webpb200_decoder* d) { return d->ct.loop_count; }
+extern "C" uint64_t webpb200_loop_duration(const webpb200_decoder* d) { return d->ct.loop_duration; }
+extern "C" size_t webpb200_output_buffer_size(const webpb200_decoder* d) {
+    return (size_t)d->ct.width * d->ct.height * (d->ct.has_alpha ? 4 : 3);
+}
+extern "C" int webpb200_set_background_color(webpb200_decoder* d, const uint8_t rgba[4]) {
+    if (d->ct.kind != 2) return WEBPB200_ERR_INVALID_PARAM;
+    d->has_bg = true;
+    std::memcpy(d->bg, rgba, 4);
+    return 0;
+}
+extern "C" void webpb200_set_lossy_upsampling(webpb200_decoder* d, int upsampling) { d->upsampling = upsampling; }
+
+namespace {
+
+// One animation frame: reconstruct it as a batch of one and composite it on the device canvas.
+// state_* mirror AnimationState; canvas lives in `canvas` (device).
+int decode_and_composite(webpb200_ctx* c, const Container& ct, uint64_t pos, int upsampling, bool has_bg, const uint8_t bg[4],
+                         bool dispose_next_in, uint32_t pw, uint32_t ph, uint32_t px, uint32_t py, DevBuf& canvas, bool& canvas_live,
+                         DevBuf& frame_out, uint8_t* host_out, AnmfFrame* fr_out) {
+    AnmfFrame fr;
+    int st = parse_anmf(ct, pos, &fr);
+    if (st) return st;
+    if (fr.lossless) return WEBPB200_ERR_NOT_LOSSY;
+    std::vector<WorkItem> items(1);
+    WorkItem& it = items[0];
+    it.vp8 = ct.data + fr.vp8.start;
+    it.vp8_len = (size_t)fr.vp8.size();
+    const bool frame_has_alpha = fr.alph.present;
+    if (frame_has_alpha) {
+        it.alph = ct.data + fr.alph.start;
+        it.alph_len = (size_t)fr.alph.size();
+        it.alph_w = (int)fr.w;
+        it.alph_h = (int)fr.h;
+        it.bpp = 4;
+        // decoder.rs:814-857 does not compare the VP8 frame with the ANMF size; a mismatch would
+        // index out of range there, so it is refused here
+        it.check_w = (int)fr.w;
+        it.check_h = (int)fr.h;
+    } else {
+        it.bpp = 3;
+        it.check_w = (int)fr.w;
+        it.check_h = (int)fr.h;  // decoder.rs:798-802
+    }
+    int rc = prepare_items(c, std::move(items), upsampling, 1);
+    if (rc) return -rc;
+    if (c->items[0].status) return c->items[0].status;
+    if ((rc = upload(c)) != 0) return -rc;
+    if ((rc = reconstruct(c, c->bd, 0xF, c->stream, nullptr)) != 0) return -rc;
+
+    const size_t cbytes = (size_t)ct.width * ct.height * 4;
+    const int out_bpp = ct.has_alpha ? 4 : 3;
+    if (!canvas_live) {  // decoder.rs:872-882
+        if (c->fail(canvas.reserve(cbytes), "canvas")) return WEBPB200_ERR_CUDA;
+        if (has_bg) {
+            std::vector<uint8_t> fill(cbytes);
+            for (size_t i = 0; i < cbytes; i += 4) std::memcpy(&fill[i], bg, 4);
+            if (c->fail(cudaMemcpy(canvas.p, fill.data(), cbytes, cudaMemcpyHostToDevice), "canvas fill")) return WEBPB200_ERR_CUDA;
+        } else if (c->fail(cudaMemsetAsync(canvas.p, 0, cbytes, c->stream), "canvas clear")) {
+            return WEBPB200_ERR_CUDA;
+        }
+        canvas_live = true;
+    }
+    if (c->fail(frame_out.reserve((size_t)ct.width * ct.height * out_bpp), "frame out")) return WEBPB200_ERR_CUDA;
+    CompositeArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.canvas = canvas.p;
+    a.frame = c->d_out.p + reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p)[0].out_off;
+    a.out = frame_out.p;
+    a.canvas_w = ct.width; a.canvas_h = ct.height;
+    a.fx = fr.x; a.fy = fr.y; a.fw = fr.w; a.fh = fr.h;
+    a.px = px; a.py = py; a.pw = pw; a.ph = ph;
+    if (dispose_next_in) {  // decoder.rs:861-869
+        if (has_bg) { a.has_clear = 1; std::memcpy(a.clear, bg, 4); }
+        else if (frame_has_alpha) { a.has_clear = 1; }
+    }
+    a.frame_has_alpha = frame_has_alpha;
+    a.use_blend = fr.blend;
+    a.out_bpp = out_bpp;
+    if (c->fail(launch_composite(a, c->stream), "k_composite")) return WEBPB200_ERR_CUDA;
+    c->launches++;
+    if (c->fail(cudaMemcpyAsync(host_out, frame_out.p, (size_t)ct.width * ct.height * out_bpp, cudaMemcpyDeviceToHost, c->stream), "D2H canvas"))
+        return WEBPB200_ERR_CUDA;
+    if (c->fail(cudaStreamSynchronize(c->stream), "sync")) return WEBPB200_ERR_CUDA;
+    *fr_out = fr;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int webpb200_read_frame(webpb200_decoder* d, uint8_t* buf, size_t len, uint32_t* duration_ms) {
+    if (!d->ct.animated) return WEBPB200_ERR_NOT_ANIMATED;
+    if (len != webpb200_output_buffer_size(d)) return WEBPB200_ERR_IMAGE_TOO_LARGE;
+    if (d->next_frame == d->ct.num_frames) return WEBPB200_ERR_NO_MORE_FRAMES;
+    int st = 0;
+    webpb200_ctx* c = default_ctx(&st);
+    if (!c) return st;
+    AnmfFrame fr;
+    st = decode_and_composite(c, d->ct, d->next_frame_start, d->upsampling, d->has_bg, d->bg, d->dispose_next, d->pw, d->ph, d->px, d->py,
+                              d->canvas, d->canvas_live, d->frame_out, buf, &fr);
+    if (st) return st;
+    d->pw = fr.w; d->ph = fr.h; d->px = fr.x; d->py = fr.y;
+    d->dispose_next = fr.dispose;
+    d->next_frame_start = fr.next;
+    d->next_frame++;
+    if (duration_ms) *duration_ms = fr.duration;
+    return 0;
+}
+
+extern "C" int webpb200_reset_animation(webpb200_decoder* d) {
+    if (!d->ct.animated) return WEBPB200_ERR_NOT_ANIMATED;
+    d->next_frame = 0;
+    d->next_frame_start = d->ct.first_anmf;
+    d->dispose_next = true;
+    return 0;
+}
+
+extern "C" int webpb200_read_image(webpb200_decoder* d, uint8_t* buf, size_t len) {
+    if (len != webpb200_output_buffer_size(d)) return WEBPB200_ERR_IMAGE_TOO_LARGE;
+    int st = 0;
+    webpb200_ctx* c = default_ctx(&st);
+    if (!c) return st;
+    if (d->ct.animated) {  // decoder.rs:674-680: frame 1 on a fresh animation state
+        DevBuf canvas, fout;
+        bool live = false;
+        AnmfFrame fr;
+        st = decode_and_composite(c, d->ct, d->ct.first_anmf, d->upsampling, d->has_bg, d->bg, true, 0, 0, 0, 0, canvas, live, fout, buf, &fr);
+        canvas.release();
+        fout.release();
+        return st;
+    }
+    const uint8_t* files[1] = {d->ct.data};
+    const size_t lens[1] = {d->ct.len};
+    uint8_t* outs[1] = {buf};
+    const size_t out_lens[1] = {len};
+    int status = 0;
+    int rc = webpb200_decode_batch(c, files, lens, 1, outs, out_lens, &status, d->upsampling, 1);
+    if (rc < 0) return -rc;
+    return status;
+}
+
+extern "C" int webpb200_vp8_decode_frame(const uint8_t* vp8, size_t len, uint16_t* width, uint16_t* height, uint8_t* y, uint8_t* u, uint8_t* v) {
+    Vp8Dims dims;
+    int st = vp8_probe(vp8, len, &dims);
+    if (st) return st;
+    if (width) *width = (uint16_t)dims.width;
+    if (height) *height = (uint16_t)dims.height;
+    if (!y || !u || !v) return 0;
+    webpb200_ctx* c = default_ctx(&st);
+    if (!c) return st;
+    std::vector<WorkItem> items(1);
+    items[0].vp8 = vp8;
+    items[0].vp8_len = len;
+    items[0].bpp = 3;
+    int rc = prepare_items(c, std::move(items), 0, 1);
+    if (rc) return -rc;
+    if (c->items[0].status) return c->items[0].status;
+    if ((rc = upload(c)) != 0) return -rc;
+    if ((rc = reconstruct(c, c->bd, 0x3, c->stream, nullptr)) != 0) return -rc;
+    rc = webpb200_batch_get_planes(c, 0, y, u, v);
+    return rc < 0 ? -rc : rc;
+}
+
+extern "C" int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs, size_t out_len,
+                                         uint32_t* durations_ms, int max_frames, int upsampling, int host_threads) {
+    if (!c) return -WEBPB200_ERR_NO_DEVICE;
+    cudaSetDevice(c->device);
+    Container ct;
+    int st = parse_container(file, len, &ct);
+    if (st) return -st;
+    if (!ct.animated) return -WEBPB200_ERR_NOT_ANIMATED;
+    const int out_bpp = ct.has_alpha ? 4 : 3;
+    if (out_len != (size_t)ct.width * ct.height * out_bpp) return -WEBPB200_ERR_IMAGE_TOO_LARGE;
+    const int nf = std::min<int>((int)ct.num_frames, max_frames);
+    std::vector<AnmfFrame> frs((size_t)nf);
+    std::vector<WorkItem> items((size_t)nf);
+    uint64_t pos = ct.first_anmf;
+    for (int f = 0; f < nf; f++) {
+        st = parse_anmf(ct, pos, &frs[f]);
+        if (st) return -st;
+        if (frs[f].lossless) return -WEBPB200_ERR_NOT_LOSSY;
+        WorkItem& it = items[f];
+        it.vp8 = file + frs[f].vp8.start;
+        it.vp8_len = (size_t)frs[f].vp8.size();
+        it.check_w = (int)frs[f].w;
+        it.check_h = (int)frs[f].h;
+        it.bpp = 3;
+        if (frs[f].alph.present) {
+            it.alph = file + frs[f].alph.start;
+            it.alph_len = (size_t)frs[f].alph.size();
+            it.alph_w = (int)frs[f].w;
+            it.alph_h = (int)frs[f].h;
+            it.bpp = 4;
+        }
+        pos = frs[f].next;
+    }
+    // all frames reconstruct as one batch (every VP8 frame is a keyframe, lossy/mod.rs:513-518) ...
+    int rc = prepare_items(c, std::move(items), upsampling, host_threads);
+    if (rc) return rc;
+    for (int f = 0; f < nf; f++)
+        if (c->items[f].status) return -c->items[f].status;
+    if ((rc = upload(c)) != 0) return rc;
+    if ((rc = reconstruct(c, c->bd, 0xF, c->stream, nullptr)) != 0) return rc;
+    // ... compositing is sequential over frames (decoder.rs:861-919)
+    const size_t cbytes = (size_t)ct.width * ct.height * 4;
+    CU(c, c->d_canvas.reserve(cbytes), "canvas");
+    CU(c, c->d_frames_out.reserve(out_len * (size_t)nf), "canvas copies");
+    CU(c, cudaMemsetAsync(c->d_canvas.p, 0, cbytes, c->stream), "canvas clear");
+    const webpb200_frame_desc* hf = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
+    bool dispose_next = true;
+    uint32_t pw = 0, ph = 0, px = 0, py = 0;
+    for (int f = 0; f < nf; f++) {
+        CompositeArgs a;
+        std::memset(&a, 0, sizeof(a));
+        a.canvas = c->d_canvas.p;
+        a.frame = c->d_out.p + hf[f].out_off;
+        a.out = c->d_frames_out.p + out_len * (size_t)f;
+        a.canvas_w = ct.width; a.canvas_h = ct.height;
+        a.fx = frs[f].x; a.fy = frs[f].y; a.fw = frs[f].w; a.fh = frs[f].h;
+        a.px = px; a.py = py; a.pw = pw; a.ph = ph;
+        a.frame_has_alpha = frs[f].alph.present;
+        a.has_clear = dispose_next && a.frame_has_alpha;
+        a.use_blend = frs[f].blend;
+        a.out_bpp = out_bpp;
+        CU(c, launch_composite(a, c->stream), "k_composite");
+        c->launches++;
+        pw = frs[f].w; ph = frs[f].h; px = frs[f].x; py = frs[f].y;
+        dispose_next = frs[f].dispose;
+        if (durations_ms) durations_ms[f] = frs[f].duration;
+    }
+    for (int f = 0; f < nf; f++)
+        CU(c, cudaMemcpyAsync(outs[f], c->d_frames_out.p + out_len * (size_t)f, out_len, cudaMemcpyDeviceToHost, c->stream), "D2H canvases");
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    return nf;
+}

@@ -1,0 +1,29 @@
+// host_vp8.h -- host half of the VP8 keyframe decode: header parse and the serial
+// boolean-entropy decode of modes and coefficient levels into the packed boundary arrays
+// (include/webpb200.h).  No pixel work happens on the host.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+#include "../../include/webpb200.h"
+
+namespace webpb200 {
+
+struct Vp8Dims {
+    int width, height, mbw, mbh;
+};
+
+// First 10 bytes of a VP8 chunk: frame tag, start code, dimensions
+// (reference lossy/mod.rs:511-540).  Returns a WEBPB200_* status.
+int vp8_probe(const uint8_t* data, size_t len, Vp8Dims* dims);
+
+// Everything Vp8Decoder::decode_frame reads from the bitstream (reference
+// lossy/mod.rs:510-671, 785-963, 1252-1281), without reconstructing:
+//   fd     <- frame-level fields (dims, filter, segments with resolved quantisers, deltas);
+//             offsets / out_bpp / upsampling / alpha fields are left untouched
+//   mbs    <- mbw*mbh macroblock descriptors, raster order
+//   levels <- mbw*mbh*400 raw token values (this function zero-fills them)
+int vp8_entropy_decode(const uint8_t* data, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
+                       int16_t* levels);
+
+}  // namespace webpb200

@@ -1,0 +1,1151 @@
+// kernels.cu -- hand-written sm_100a kernels for everything after VP8 entropy decoding.
+//
+//   k_predict     dequantisation + inverse WHT/DCT + intra prediction (16x16, chroma, B_PRED)
+//   k_loopfilter  simple / normal in-loop deblocking filter
+//   k_yuv2rgb     fancy (bilinear) or simple chroma upsampling + YUV420 -> RGB / RGBA
+//   k_alpha_*     ALPH plane un-filter (none / horizontal / vertical / gradient) + merge
+//   k_composite   animation frame compositing (clear, copy, non-premultiplied src-over blend)
+//
+// Arithmetic follows the reference decoder (image-webp v0.2.4) bit for bit; each device
+// function cites the reference lines it reproduces.  Scheduling does not: the reference walks
+// macroblocks in raster order on one thread, here one WARP owns one macroblock ROW of one
+// image and rows advance as a wavefront (row y may work on macroblock x once row y-1 has
+// finished macroblock x+1, i.e. the x+2y order the dependencies allow).  Rows are handed out
+// by a global ticket counter in (image, row) order, so every dependency points at a lower
+// ticket and the scheme cannot deadlock whatever the residency.  Integer/byte work bound by
+// instruction issue and HBM, so no tensor cores and no TMA tiles: coalesced 16-byte loads of
+// the level array, shared-memory staging of the macroblock workspace, L2-coherent (ld.cg)
+// reads of neighbour rows.
+#include "kernels.cuh"
+
+#include <cstring>
+
+namespace webpb200 {
+
+ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs) {
+    ScratchLayout l;
+    auto up = [](uint64_t v) { return (v + 255) & ~(uint64_t)255; };
+    l.tickets_off = 0;
+    l.progress_pred_off = 256;
+    l.progress_lf_off = up(l.progress_pred_off + 4 * total_rows);
+    l.zero_bytes = up(l.progress_lf_off + 4 * total_rows);
+    l.rowmap_off = l.zero_bytes;
+    l.mbinfo_off = up(l.rowmap_off + 4 * total_rows);
+    l.total = up(l.mbinfo_off + total_mbs);
+    return l;
+}
+
+namespace {
+
+constexpr int kWarpsPerBlock = 8;
+constexpr int kThreads = kWarpsPerBlock * 32;
+constexpr unsigned kFull = 0xffffffffu;
+
+// ---------------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int clamp255(int v) { return min(max(v, 0), 255); }
+
+__device__ __forceinline__ uint32_t ld_cg_u32(const void* p) { return __ldcg(reinterpret_cast<const unsigned int*>(p)); }
+__device__ __forceinline__ uint2 ld_cg_u64(const void* p) { return __ldcg(reinterpret_cast<const uint2*>(p)); }
+__device__ __forceinline__ uint4 ld_cg_u128(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Wait until the row above has finished `need` macroblocks.  `seen` caches the last value read.
+// Watchdog: a wait that lasts absurdly long (a scheduling bug, never a data property) raises the
+// abort word; every waiter sees it, the kernel drains and the host reports an error instead of
+// hanging the device.  Returns false when aborted.
+__device__ __forceinline__ bool wait_row(const int* prog, int need, int& seen, int lane, unsigned int* abort_word) {
+    if (seen >= need) return true;
+    if (lane == 0) {
+        int v = ld_acquire(prog);
+        unsigned spins = 0;
+        while (v < need) {
+            __nanosleep(64);
+            v = ld_acquire(prog);
+            if ((++spins & 0x3ff) == 0) {
+                if (spins > (1u << 24)) atomicExch(abort_word, 1u);
+                if (*reinterpret_cast<volatile unsigned int*>(abort_word)) { v = -1; break; }
+            }
+        }
+        seen = v;
+    }
+    seen = __shfl_sync(kFull, seen, 0);
+    __syncwarp();
+    return seen >= 0;
+}
+
+// Publish "macroblocks 0..done-1 of my row are finished": all lanes' global writes first.
+__device__ __forceinline__ void publish_row(int* prog, int done, int lane) {
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence();
+        st_release(prog, done);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// B_PRED lookup table.  Every 4x4 sub-block predictor except B_DC is, per pixel, either
+// (a + 2b + c + 2) >> 2 over three edge pixels (avg3; avg2(a,b) = avg3(a,b,a), copy = avg3(a,a,a))
+// or clamp(a + b - c) (B_TM).  One word per (mode, pixel): three signed byte offsets from the
+// sub-block origin inside the 32-byte-stride workspace, and a TM flag in the top byte.
+// Reference: prediction.rs:339-499 (VE, HE, LD, RD, VR, VL, HD, HU) and 238-269 (TM).
+// ---------------------------------------------------------------------------------------------
+constexpr int kWsStride = 32;
+struct EdgeRef {
+    int off;
+};
+constexpr EdgeRef eA(int i) { return {-kWsStride + i}; }
+constexpr EdgeRef eP() { return {-kWsStride - 1}; }
+constexpr EdgeRef eL(int j) { return {kWsStride * j - 1}; }
+
+struct BpredTable {
+    uint32_t w[10 * 16];
+};
+
+uint32_t pack3(EdgeRef a, EdgeRef b, EdgeRef c, int tm) {
+    return (uint32_t)(uint8_t)(int8_t)a.off | ((uint32_t)(uint8_t)(int8_t)b.off << 8) |
+           ((uint32_t)(uint8_t)(int8_t)c.off << 16) | ((uint32_t)tm << 24);
+}
+
+BpredTable make_bpred_table() {
+    BpredTable t;
+    std::memset(&t, 0, sizeof(t));
+    auto set3 = [&](int mode, int x, int y, EdgeRef a, EdgeRef b, EdgeRef c) { t.w[mode * 16 + y * 4 + x] = pack3(a, b, c, 0); };
+    auto set2 = [&](int mode, int x, int y, EdgeRef a, EdgeRef b) { t.w[mode * 16 + y * 4 + x] = pack3(a, b, a, 0); };
+    auto set1 = [&](int mode, int x, int y, EdgeRef a) { t.w[mode * 16 + y * 4 + x] = pack3(a, a, a, 0); };
+    // top row with the corner in front: T(-1) = P, T(i) = A_i
+    auto T = [&](int i) { return i < 0 ? eP() : eA(i); };
+    // edge e0..e8 = L3 L2 L1 L0 P A0 A1 A2 A3 (prediction.rs:318-337)
+    auto E = [&](int i) { return i < 4 ? eL(3 - i) : i == 4 ? eP() : eA(i - 5); };
+    for (int y = 0; y < 4; y++)
+        for (int x = 0; x < 4; x++) {
+            t.w[1 * 16 + y * 4 + x] = pack3(eL(y), eA(x), eP(), 1);           // B_TM
+            set3(2, x, y, T(x - 1), T(x), T(x + 1));                         // B_VE
+            if (y == 0) set3(3, x, y, eP(), eL(0), eL(1));                   // B_HE
+            else if (y < 3) set3(3, x, y, eL(y - 1), eL(y), eL(y + 1));
+            else set3(3, x, y, eL(2), eL(3), eL(3));
+            const int i = x + y;                                             // B_LD
+            if (i < 6) set3(4, x, y, eA(i), eA(i + 1), eA(i + 2));
+            else set3(4, x, y, eA(6), eA(7), eA(7));
+            const int j = 3 - y + x;                                         // B_RD
+            set3(5, x, y, E(j), E(j + 1), E(j + 2));
+        }
+    // B_VR (prediction.rs:417-436)
+    set3(6, 0, 3, E(1), E(2), E(3));
+    set3(6, 0, 2, E(2), E(3), E(4));
+    set3(6, 1, 3, E(3), E(4), E(5)); set3(6, 0, 1, E(3), E(4), E(5));
+    set2(6, 1, 2, E(4), E(5));       set2(6, 0, 0, E(4), E(5));
+    set3(6, 2, 3, E(4), E(5), E(6)); set3(6, 1, 1, E(4), E(5), E(6));
+    set2(6, 2, 2, E(5), E(6));       set2(6, 1, 0, E(5), E(6));
+    set3(6, 3, 3, E(5), E(6), E(7)); set3(6, 2, 1, E(5), E(6), E(7));
+    set2(6, 3, 2, E(6), E(7));       set2(6, 2, 0, E(6), E(7));
+    set3(6, 3, 1, E(6), E(7), E(8));
+    set2(6, 3, 0, E(7), E(8));
+    // B_VL (prediction.rs:438-457)
+    set2(7, 0, 0, eA(0), eA(1));
+    set3(7, 0, 1, eA(0), eA(1), eA(2));
+    set2(7, 0, 2, eA(1), eA(2));        set2(7, 1, 0, eA(1), eA(2));
+    set3(7, 1, 1, eA(1), eA(2), eA(3)); set3(7, 0, 3, eA(1), eA(2), eA(3));
+    set2(7, 1, 2, eA(2), eA(3));        set2(7, 2, 0, eA(2), eA(3));
+    set3(7, 1, 3, eA(2), eA(3), eA(4)); set3(7, 2, 1, eA(2), eA(3), eA(4));
+    set2(7, 2, 2, eA(3), eA(4));        set2(7, 3, 0, eA(3), eA(4));
+    set3(7, 2, 3, eA(3), eA(4), eA(5)); set3(7, 3, 1, eA(3), eA(4), eA(5));
+    set3(7, 3, 2, eA(4), eA(5), eA(6));
+    set3(7, 3, 3, eA(5), eA(6), eA(7));
+    // B_HD (prediction.rs:459-478)
+    set2(8, 0, 3, E(0), E(1));
+    set3(8, 1, 3, E(0), E(1), E(2));
+    set2(8, 0, 2, E(1), E(2));       set2(8, 2, 3, E(1), E(2));
+    set3(8, 1, 2, E(1), E(2), E(3)); set3(8, 3, 3, E(1), E(2), E(3));
+    set2(8, 2, 2, E(2), E(3));       set2(8, 0, 1, E(2), E(3));
+    set3(8, 3, 2, E(2), E(3), E(4)); set3(8, 1, 1, E(2), E(3), E(4));
+    set2(8, 2, 1, E(3), E(4));       set2(8, 0, 0, E(3), E(4));
+    set3(8, 3, 1, E(3), E(4), E(5)); set3(8, 1, 0, E(3), E(4), E(5));
+    set3(8, 2, 0, E(4), E(5), E(6));
+    set3(8, 3, 0, E(5), E(6), E(7));
+    // B_HU (prediction.rs:480-499)
+    set2(9, 0, 0, eL(0), eL(1));
+    set3(9, 1, 0, eL(0), eL(1), eL(2));
+    set2(9, 2, 0, eL(1), eL(2));        set2(9, 0, 1, eL(1), eL(2));
+    set3(9, 3, 0, eL(1), eL(2), eL(3)); set3(9, 1, 1, eL(1), eL(2), eL(3));
+    set2(9, 2, 1, eL(2), eL(3));        set2(9, 0, 2, eL(2), eL(3));
+    set3(9, 3, 1, eL(2), eL(3), eL(3)); set3(9, 1, 2, eL(2), eL(3), eL(3));
+    set1(9, 2, 2, eL(3)); set1(9, 3, 2, eL(3));
+    set1(9, 0, 3, eL(3)); set1(9, 1, 3, eL(3)); set1(9, 2, 3, eL(3)); set1(9, 3, 3, eL(3));
+    return t;
+}
+
+__constant__ BpredTable c_bpred;
+
+}  // namespace
+
+void bpred_table_eval(int mode, const uint8_t edge[13], uint8_t out[16]) {
+    static const BpredTable t = make_bpred_table();
+    uint8_t ws[6 * kWsStride];
+    std::memset(ws, 0, sizeof(ws));
+    const int org = 1 * kWsStride + 4;
+    ws[org + eP().off] = edge[0];
+    for (int i = 0; i < 8; i++) ws[org + eA(i).off] = edge[1 + i];
+    for (int j = 0; j < 4; j++) ws[org + eL(j).off] = edge[9 + j];
+    for (int p = 0; p < 16; p++) {
+        const uint32_t w = t.w[mode * 16 + p];
+        const int a = ws[org + (int8_t)(w & 0xff)], b = ws[org + (int8_t)((w >> 8) & 0xff)], c = ws[org + (int8_t)((w >> 16) & 0xff)];
+        int v = (w >> 24) ? a + b - c : (a + 2 * b + c + 2) >> 2;
+        out[p] = (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v);
+    }
+}
+
+void upload_tables_once() {
+    static const BpredTable t = make_bpred_table();
+    cudaMemcpyToSymbol(c_bpred, &t, sizeof(t));
+}
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// Inverse transforms (one lane = one 4x4 block, values in registers)
+// ---------------------------------------------------------------------------------------------
+// transform.rs:1-4, 20-25: MUL2(x) = (x*35468)>>16, MUL1(x) = x + ((x*20091)>>16), 64-bit products
+__device__ __forceinline__ int mul_c2(int x) { return (int)(((long long)x * 35468LL) >> 16); }
+__device__ __forceinline__ int mul_c1(int x) { return x + (int)(((long long)x * 20091LL) >> 16); }
+
+// transform.rs:7-51.  Vertical pass first (no rounding), then rows with (x + 4) >> 3.  Sums stay
+// far inside int32 for every level the bitstream can carry (|level| <= 2114, quantisers <= 440);
+// only the products need 64 bits.
+__device__ __forceinline__ void idct4x4(int* c) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int a1 = c[i] + c[8 + i], b1 = c[i] - c[8 + i];
+        const int c1 = mul_c2(c[4 + i]) - mul_c1(c[12 + i]);
+        const int d1 = mul_c1(c[4 + i]) + mul_c2(c[12 + i]);
+        c[i] = a1 + d1;
+        c[4 + i] = b1 + c1;
+        c[12 + i] = a1 - d1;
+        c[8 + i] = b1 - c1;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int a1 = c[4 * i] + c[4 * i + 2], b1 = c[4 * i] - c[4 * i + 2];
+        const int c1 = mul_c2(c[4 * i + 1]) - mul_c1(c[4 * i + 3]);
+        const int d1 = mul_c1(c[4 * i + 1]) + mul_c2(c[4 * i + 3]);
+        c[4 * i] = (a1 + d1 + 4) >> 3;
+        c[4 * i + 3] = (a1 - d1 + 4) >> 3;
+        c[4 * i + 1] = (b1 + c1 + 4) >> 3;
+        c[4 * i + 2] = (b1 - c1 + 4) >> 3;
+    }
+}
+
+// transform.rs:54-86
+__device__ __forceinline__ void iwht4x4(int* c) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int a1 = c[i] + c[12 + i], b1 = c[4 + i] + c[8 + i];
+        const int c1 = c[4 + i] - c[8 + i], d1 = c[i] - c[12 + i];
+        c[i] = a1 + b1;
+        c[4 + i] = c1 + d1;
+        c[8 + i] = a1 - b1;
+        c[12 + i] = d1 - c1;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int a1 = c[4 * i] + c[4 * i + 3], b1 = c[4 * i + 1] + c[4 * i + 2];
+        const int c1 = c[4 * i + 1] - c[4 * i + 2], d1 = c[4 * i] - c[4 * i + 3];
+        c[4 * i] = (a1 + b1 + 3) >> 3;
+        c[4 * i + 1] = (c1 + d1 + 3) >> 3;
+        c[4 * i + 2] = (a1 - b1 + 3) >> 3;
+        c[4 * i + 3] = (d1 - c1 + 3) >> 3;
+    }
+}
+
+__device__ __forceinline__ void unpack8(const uint4& v, int* c) {
+    c[0] = (int)(short)(v.x & 0xffff); c[1] = (int)v.x >> 16;
+    c[2] = (int)(short)(v.y & 0xffff); c[3] = (int)v.y >> 16;
+    c[4] = (int)(short)(v.z & 0xffff); c[5] = (int)v.z >> 16;
+    c[6] = (int)(short)(v.w & 0xffff); c[7] = (int)v.w >> 16;
+}
+// residuals only ever meet a pixel through clamp(p + r, 0, 255) (prediction.rs:133-147), so
+// clamping r to [-255, 255] first changes nothing and makes it fit 16 bits
+__device__ __forceinline__ uint32_t pack_res(int a, int b) {
+    a = min(max(a, -255), 255);
+    b = min(max(b, -255), 255);
+    return ((uint32_t)a & 0xffffu) | ((uint32_t)b << 16);
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_predict
+// ---------------------------------------------------------------------------------------------
+// Per-warp workspace in shared memory.  Luma: 17 rows x 32 bytes; pixel (x, y) of the macroblock
+// sits at row y+1, column x+4; column 3 is the left border, row 0 the row above (columns 0..3 the
+// word holding the corner at column 3, 4..19 the 16 pixels above, 20..23 the 4 above-right);
+// rows 4, 8, 12 carry the above-right pixels again in columns 20..23 for the last sub-block
+// column (prediction.rs:47-51).  Chroma: 9 rows x 16 bytes, pixel (x, y) at row y+1, column x+4.
+struct __align__(16) PredictSmem {
+    uint8_t yw[17 * 32];
+    uint8_t uw[9 * 16];
+    uint8_t vw[9 * 16];
+    int16_t res[24 * 16];  // residuals of the 24 blocks, raster inside a block
+    int32_t wht[16];
+};
+
+struct PredictArgs {
+    const webpb200_frame_desc* frames;
+    const webpb200_mb_desc* mbs;
+    const int16_t* levels;
+    uint8_t* planes;
+    unsigned int* ticket;
+    unsigned int* abort_word;
+    int* progress;
+    const uint32_t* rowmap;
+    uint8_t* mbinfo;
+    uint32_t total_rows;
+};
+
+__global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
+    __shared__ PredictSmem smem[kWarpsPerBlock];
+    __shared__ uint32_t s_bpred[160];
+    for (int i = threadIdx.x; i < 160; i += kThreads) s_bpred[i] = c_bpred.w[i];
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    PredictSmem& S = smem[threadIdx.x >> 5];
+    uint32_t* yw32 = reinterpret_cast<uint32_t*>(S.yw);
+    uint32_t* uw32 = reinterpret_cast<uint32_t*>(S.uw);
+    uint32_t* vw32 = reinterpret_cast<uint32_t*>(S.vw);
+
+    for (;;) {
+        unsigned int t = 0;
+        if (lane == 0) t = atomicAdd(A.ticket, 1u);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= A.total_rows) break;
+        const uint32_t img = __ldg(A.rowmap + t);
+        const webpb200_frame_desc* fd = A.frames + img;
+        const int mbw = fd->mbw;
+        const int mby = (int)(t - fd->row_base);
+        const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
+        uint8_t* Y = A.planes + fd->y_off;
+        uint8_t* U = A.planes + fd->u_off;
+        uint8_t* V = A.planes + fd->v_off;
+        const int* prog_above = A.progress + t - 1;
+        int* prog_mine = A.progress + t;
+        int seen = 0;
+        const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
+
+        for (int mbx = 0; mbx < mbw; mbx++) {
+            const size_t mbi = mb_row0 + mbx;
+            const uint4 mbw4 = __ldg(reinterpret_cast<const uint4*>(A.mbs + mbi));
+            const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff, segment = (mbw4.x >> 16) & 3;
+            const bool skipped = (mbw4.x >> 24) & 1;
+            const uint32_t nflags = mbw4.y;
+            const uint32_t bpred_lo = mbw4.z, bpred_hi = mbw4.w;
+
+            // ---- dequantise + inverse transforms: lane b owns block b (24 = Y2) ----
+            // read_coefficients mod.rs:865-866 (the multiply), read_residual_data 888-952
+            bool nzdct = false;
+            if (!skipped) {
+                int c[16];
+                if (lane < 25) {
+                    const uint4* lp = reinterpret_cast<const uint4*>(A.levels + mbi * WEBPB200_LEVELS_PER_MB + lane * 16);
+                    const uint4 lo = __ldg(lp), hi = __ldg(lp + 1);
+                    unpack8(lo, c);
+                    unpack8(hi, c + 8);
+                }
+                const webpb200_segment* sg = fd->seg + segment;
+                if (ymode != 4) {
+                    if (lane == 24) {
+                        const int dcq = sg->y2dc, acq = sg->y2ac;
+                        c[0] *= dcq;
+#pragma unroll
+                        for (int i = 1; i < 16; i++) c[i] *= acq;
+                        iwht4x4(c);
+#pragma unroll
+                        for (int i = 0; i < 16; i++) S.wht[i] = c[i];
+                    }
+                    __syncwarp();
+                }
+                bool nz = false;
+                if (lane < 24) {
+                    const int dcq = lane < 16 ? sg->ydc : sg->uvdc, acq = lane < 16 ? sg->yac : sg->uvac;
+                    c[0] *= dcq;
+#pragma unroll
+                    for (int i = 1; i < 16; i++) c[i] *= acq;
+                    if (ymode != 4 && lane < 16) c[0] = S.wht[lane];
+                    nz = c[0] != 0 || ((nflags >> lane) & 1);  // mod.rs:920, 949
+                }
+                const unsigned nzmask = __ballot_sync(kFull, nz);
+                nzdct = nzmask != 0;
+                if (nzdct) {  // idct(0) = 0, so running it on blocks without the flag is value-neutral
+                    if (lane < 24) {
+                        idct4x4(c);
+                        uint4 o0, o1;
+                        o0.x = pack_res(c[0], c[1]);  o0.y = pack_res(c[2], c[3]);
+                        o0.z = pack_res(c[4], c[5]);  o0.w = pack_res(c[6], c[7]);
+                        o1.x = pack_res(c[8], c[9]);  o1.y = pack_res(c[10], c[11]);
+                        o1.z = pack_res(c[12], c[13]); o1.w = pack_res(c[14], c[15]);
+                        uint4* rp = reinterpret_cast<uint4*>(S.res + lane * 16);
+                        rp[0] = o0;
+                        rp[1] = o1;
+                    }
+                }
+            }
+            if (!nzdct && lane < 24) {
+                uint4* rp = reinterpret_cast<uint4*>(S.res + lane * 16);
+                rp[0] = make_uint4(0, 0, 0, 0);
+                rp[1] = make_uint4(0, 0, 0, 0);
+            }
+            if (lane == 0) A.mbinfo[mbi] = nzdct ? 1 : 0;
+
+            // ---- neighbours: wait for the above-right macroblock, then build the borders ----
+            // create_border_luma / create_border_chroma, prediction.rs:13-123
+            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
+            if (lane < 12) {
+                uint32_t w;
+                if (mby == 0) {
+                    w = 0x7f7f7f7fu;
+                } else if (lane < 6) {
+                    const uint8_t* row = Y + (size_t)(mby * 16 - 1) * ystride + (size_t)mbx * 16;
+                    if (lane == 0) w = mbx > 0 ? ld_cg_u32(row - 4) : 0x81818181u;
+                    else if (lane < 5) w = ld_cg_u32(row + 4 * (lane - 1));
+                    else w = mbx < mbw - 1 ? ld_cg_u32(row + 16) : (ld_cg_u32(row + 12) >> 24) * 0x01010101u;
+                } else {
+                    const int k = lane - 6;  // 0..2 U, 3..5 V
+                    const uint8_t* row = (k < 3 ? U : V) + (size_t)(mby * 8 - 1) * cstride + (size_t)mbx * 8;
+                    const int j = k % 3;
+                    if (j == 0) w = mbx > 0 ? ld_cg_u32(row - 4) : 0x81818181u;
+                    else w = ld_cg_u32(row + 4 * (j - 1));
+                }
+                if (lane < 6) {
+                    yw32[lane] = w;
+                    if (lane == 5) { yw32[4 * 8 + 5] = w; yw32[8 * 8 + 5] = w; yw32[12 * 8 + 5] = w; }
+                } else if (lane < 9) {
+                    uw32[lane - 6] = w;
+                } else {
+                    vw32[lane - 9] = w;
+                }
+            }
+            if (mbx == 0) {  // left border 129 (prediction.rs:54-57, 104-107)
+                if (lane < 16) S.yw[(1 + lane) * 32 + 3] = 129;
+                else if (lane < 24) S.uw[(1 + lane - 16) * 16 + 3] = 129;
+                else S.vw[(1 + lane - 24) * 16 + 3] = 129;
+            }
+            __syncwarp();
+
+            // ---- luma ----
+            if (ymode == 4) {
+                // predict_4x4 (prediction.rs:159-183) as a 10-step sx + 2*sy wavefront over the
+                // 16 sub-blocks; half-warp h works on sub-block row sy_lo + h, one lane per pixel
+                const int half = lane >> 4, p = lane & 15, px = p & 3, py = p >> 2;
+                const unsigned hmask = half ? 0xffff0000u : 0x0000ffffu;
+#pragma unroll 1
+                for (int s = 0; s < 10; s++) {
+                    const int sy_lo = max(0, (s - 2) >> 1), sy_hi = min(3, s >> 1);
+                    const int sy = sy_lo + half, sx = s - 2 * sy;
+                    if (sy <= sy_hi) {
+                        const int sb = sy * 4 + sx;
+                        const int mode = ((sb < 8 ? bpred_lo : bpred_hi) >> (4 * (sb & 7))) & 15;
+                        const int org = (1 + 4 * sy) * 32 + 4 + 4 * sx;
+                        int pred;
+                        if (mode == 0) {  // predict_bdcpred, prediction.rs:271-288
+                            const int off = (p & 4) ? org + (p & 3) * 32 - 1 : org - 32 + (p & 3);
+                            const int sum = __reduce_add_sync(hmask, (unsigned)S.yw[off]);  // each edge pixel twice
+                            pred = (sum + 8) >> 4;
+                        } else {
+                            const uint32_t w = s_bpred[mode * 16 + p];
+                            const int a = S.yw[org + (int)(int8_t)(w & 0xff)];
+                            const int b = S.yw[org + (int)(int8_t)((w >> 8) & 0xff)];
+                            const int cc = S.yw[org + (int)(int8_t)((w >> 16) & 0xff)];
+                            pred = (w >> 24) ? clamp255(a + b - cc) : (a + 2 * b + cc + 2) >> 2;
+                        }
+                        const int r = S.res[sb * 16 + p];
+                        S.yw[org + py * 32 + px] = (uint8_t)clamp255(pred + r);  // add_residue
+                    }
+                    __syncwarp();
+                }
+            } else {
+                // 16x16 predictors (prediction.rs:185-269): lane = (row, 8-pixel half)
+                const int row = lane >> 1, x0 = (lane & 1) * 8;
+                int pr[8];
+                if (ymode == 0) {  // DC
+                    int v = 0;
+                    if (lane < 16) v = (mby > 0 ? (int)S.yw[4 + lane] : 0) + (mbx > 0 ? (int)S.yw[(1 + lane) * 32 + 3] : 0);
+                    const int sum = __reduce_add_sync(kFull, (unsigned)v);
+                    const int shf = 3 + (mby > 0) + (mbx > 0);
+                    const int dc = (mby == 0 && mbx == 0) ? 128 : (sum + (1 << (shf - 1))) >> shf;
+#pragma unroll
+                    for (int i = 0; i < 8; i++) pr[i] = dc;
+                } else if (ymode == 1) {  // V
+#pragma unroll
+                    for (int i = 0; i < 8; i++) pr[i] = S.yw[4 + x0 + i];
+                } else if (ymode == 2) {  // H
+                    const int l = S.yw[(1 + row) * 32 + 3];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) pr[i] = l;
+                } else {  // TM
+                    const int lmp = (int)S.yw[(1 + row) * 32 + 3] - (int)S.yw[3];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) pr[i] = clamp255(lmp + (int)S.yw[4 + x0 + i]);
+                }
+                __syncwarp();  // all reads of the borders done before the block is written
+                const int blk = (row >> 2) * 4 + (x0 >> 2);
+                const uint2 r0 = *reinterpret_cast<const uint2*>(S.res + blk * 16 + (row & 3) * 4);
+                const uint2 r1 = *reinterpret_cast<const uint2*>(S.res + (blk + 1) * 16 + (row & 3) * 4);
+                const int rr[8] = {(int)(short)(r0.x & 0xffff), (int)r0.x >> 16, (int)(short)(r0.y & 0xffff), (int)r0.y >> 16,
+                                   (int)(short)(r1.x & 0xffff), (int)r1.x >> 16, (int)(short)(r1.y & 0xffff), (int)r1.y >> 16};
+                uint32_t o0 = 0, o1 = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    o0 |= (uint32_t)clamp255(pr[i] + rr[i]) << (8 * i);
+                    o1 |= (uint32_t)clamp255(pr[4 + i] + rr[4 + i]) << (8 * i);
+                }
+                yw32[(1 + row) * 8 + 1 + (x0 >> 2)] = o0;
+                yw32[(1 + row) * 8 + 2 + (x0 >> 2)] = o1;
+                __syncwarp();
+            }
+            {  // macroblock -> unfiltered luma plane (mod.rs:713-720)
+                const int row = lane >> 1, x0 = (lane & 1) * 8;
+                uint2 o;
+                o.x = yw32[(1 + row) * 8 + 1 + (x0 >> 2)];
+                o.y = yw32[(1 + row) * 8 + 2 + (x0 >> 2)];
+                *reinterpret_cast<uint2*>(Y + (size_t)(mby * 16 + row) * ystride + (size_t)mbx * 16 + x0) = o;
+            }
+
+            // ---- chroma (intra_predict_chroma, mod.rs:723-783): lane = (plane, row, 4-pixel half)
+            {
+                const int plane = lane >> 4, j = lane & 15, row = j >> 1, x0 = (j & 1) * 4;
+                uint8_t* cw = plane ? S.vw : S.uw;
+                uint32_t* cw32 = plane ? vw32 : uw32;
+                const unsigned gmask = plane ? 0xffff0000u : 0x0000ffffu;
+                int pr[4];
+                if (uvmode == 0) {
+                    int v;
+                    if (j < 8) v = mby > 0 ? (int)cw[4 + j] : 0;
+                    else v = mbx > 0 ? (int)cw[(1 + j - 8) * 16 + 3] : 0;
+                    const int sum = __reduce_add_sync(gmask, (unsigned)v);
+                    const int shf = 2 + (mby > 0) + (mbx > 0);
+                    const int dc = (mby == 0 && mbx == 0) ? 128 : (sum + (1 << (shf - 1))) >> shf;
+                    pr[0] = pr[1] = pr[2] = pr[3] = dc;
+                } else if (uvmode == 1) {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) pr[i] = cw[4 + x0 + i];
+                } else if (uvmode == 2) {
+                    const int l = cw[(1 + row) * 16 + 3];
+                    pr[0] = pr[1] = pr[2] = pr[3] = l;
+                } else {
+                    const int lmp = (int)cw[(1 + row) * 16 + 3] - (int)cw[3];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) pr[i] = clamp255(lmp + (int)cw[4 + x0 + i]);
+                }
+                __syncwarp();
+                const int blk = 16 + plane * 4 + (row >> 2) * 2 + (x0 >> 2);
+                const uint2 r = *reinterpret_cast<const uint2*>(S.res + blk * 16 + (row & 3) * 4);
+                const int rr[4] = {(int)(short)(r.x & 0xffff), (int)r.x >> 16, (int)(short)(r.y & 0xffff), (int)r.y >> 16};
+                uint32_t o = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) o |= (uint32_t)clamp255(pr[i] + rr[i]) << (8 * i);
+                cw32[(1 + row) * 4 + 1 + (x0 >> 2)] = o;
+                uint8_t* P = plane ? V : U;
+                *reinterpret_cast<uint32_t*>(P + (size_t)(mby * 8 + row) * cstride + (size_t)mbx * 8 + x0) = o;
+            }
+            __syncwarp();
+            // right column becomes the next macroblock's left border (mod.rs:700-704, 1309-1314)
+            if (lane < 16) S.yw[(1 + lane) * 32 + 3] = S.yw[(1 + lane) * 32 + 19];
+            else if (lane < 24) S.uw[(1 + lane - 16) * 16 + 3] = S.uw[(1 + lane - 16) * 16 + 11];
+            else S.vw[(1 + lane - 24) * 16 + 3] = S.vw[(1 + lane - 24) * 16 + 11];
+            publish_row(prog_mine, mbx + 1, lane);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_loopfilter
+// ---------------------------------------------------------------------------------------------
+// loop_filter.rs:4-23
+__device__ __forceinline__ int lf_c(int v) { return min(max(v, -128), 127); }
+__device__ __forceinline__ int u2s(int v) { return v - 128; }
+__device__ __forceinline__ int s2u(int v) { return lf_c(v) + 128; }
+
+// One 8-pixel line across an edge; q0 is at p[0], neighbours at multiples of `st` bytes.
+// kind 0: simple_segment (loop_filter.rs:144-162), 1: subblock_filter (167-206),
+// 2: macroblock_filter (212-295); thresholds per 79-139; common_adjust 28-76.
+__device__ __forceinline__ void lf_line(uint8_t* p, int st, int kind, int edge_limit, int interior, int hev_thr) {
+    const int P1 = p[-2 * st], P0 = p[-st], Q0 = p[0], Q1 = p[st];
+    if (abs(P0 - Q0) * 2 + (abs(P1 - Q1) >> 1) > edge_limit) return;
+    int P3 = 0, P2 = 0, Q2 = 0, Q3 = 0;
+    bool hv = true;  // the simple filter always uses the outer taps
+    if (kind != 0) {
+        P3 = p[-4 * st]; P2 = p[-3 * st]; Q2 = p[2 * st]; Q3 = p[3 * st];
+        if (abs(P3 - P2) > interior || abs(P2 - P1) > interior || abs(P1 - P0) > interior ||
+            abs(Q3 - Q2) > interior || abs(Q2 - Q1) > interior || abs(Q1 - Q0) > interior)
+            return;
+        hv = abs(P1 - P0) > hev_thr || abs(Q1 - Q0) > hev_thr;
+    }
+    const int p1 = u2s(P1), p0 = u2s(P0), q0 = u2s(Q0), q1 = u2s(Q1);
+    if (kind == 2 && !hv) {
+        const int p2 = u2s(P2), q2 = u2s(Q2);
+        const int w = lf_c(lf_c(p1 - q1) + 3 * (q0 - p0));
+        int a = lf_c((27 * w + 63) >> 7);
+        p[0] = (uint8_t)s2u(q0 - a);
+        p[-st] = (uint8_t)s2u(p0 + a);
+        a = lf_c((18 * w + 63) >> 7);
+        p[st] = (uint8_t)s2u(q1 - a);
+        p[-2 * st] = (uint8_t)s2u(p1 + a);
+        a = lf_c((9 * w + 63) >> 7);
+        p[2 * st] = (uint8_t)s2u(q2 - a);
+        p[-3 * st] = (uint8_t)s2u(p2 + a);
+        return;
+    }
+    // common_adjust(use_outer_taps = hv)
+    const int outer = hv ? lf_c(p1 - q1) : 0;
+    int a = lf_c(outer + 3 * (q0 - p0));
+    const int b = lf_c(a + 3) >> 3;
+    a = lf_c(a + 4) >> 3;
+    p[0] = (uint8_t)s2u(q0 - a);
+    p[-st] = (uint8_t)s2u(p0 + b);
+    if (kind == 1 && !hv) {
+        a = (a + 1) >> 1;
+        p[st] = (uint8_t)s2u(q1 - a);
+        p[-2 * st] = (uint8_t)s2u(p1 + a);
+    }
+}
+
+// Per-warp tile: luma rows -4..15 x columns -4..15 of the macroblock (20 x 20, stride 20),
+// chroma 12 x 12 (stride 12) per plane.  The 4 left columns are carried over from the previous
+// macroblock of the row (they are written back one iteration late, after this macroblock's left
+// edge has been filtered); the 4 top rows belong to the row above and are re-read from L2.
+struct __align__(16) FilterSmem {
+    uint8_t y[20 * 20];
+    uint8_t c[2][12 * 12];
+};
+
+struct FilterArgs {
+    const webpb200_frame_desc* frames;
+    const webpb200_mb_desc* mbs;
+    uint8_t* planes;
+    unsigned int* ticket;
+    unsigned int* abort_word;
+    int* progress;
+    const uint32_t* rowmap;
+    const uint8_t* mbinfo;
+    uint32_t total_rows;
+};
+
+__global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
+    __shared__ FilterSmem smem[kWarpsPerBlock];
+    const int lane = threadIdx.x & 31;
+    FilterSmem& S = smem[threadIdx.x >> 5];
+    uint32_t* y32 = reinterpret_cast<uint32_t*>(S.y);
+
+    for (;;) {
+        unsigned int t = 0;
+        if (lane == 0) t = atomicAdd(A.ticket, 1u);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= A.total_rows) break;
+        const uint32_t img = __ldg(A.rowmap + t);
+        const webpb200_frame_desc* fd = A.frames + img;
+        const int frame_level = fd->filter_level;
+        if (frame_level == 0) {  // mod.rs:1195-1198: nothing is filtered in this frame
+            if (lane == 0) st_release(A.progress + t, (int)fd->mbw);
+            continue;
+        }
+        const int mbw = fd->mbw;
+        const int mby = (int)(t - fd->row_base);
+        const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
+        uint8_t* Y = A.planes + fd->y_off;
+        uint8_t* const CPu = A.planes + fd->u_off;
+        uint8_t* const CPv = A.planes + fd->v_off;
+        const int* prog_above = A.progress + t - 1;
+        int* prog_mine = A.progress + t;
+        int seen = 0;
+        const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
+        const bool simple = fd->filter_type != 0;
+        const int sharp = fd->sharpness;
+        const int row_lo = mby > 0 ? 0 : 4;  // tile rows that exist in the plane
+
+        for (int mbx = 0; mbx < mbw; mbx++) {
+            const size_t mbi = mb_row0 + mbx;
+            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
+
+            // ---- load the 16 new columns (rows -4..15) ----
+            if (lane < 20 && lane >= row_lo) {
+                const uint4 v = ld_cg_u128(Y + (size_t)(mby * 16 - 4 + lane) * ystride + (size_t)mbx * 16);
+                uint32_t* d = y32 + lane * 5 + 1;
+                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+            }
+            if (!simple && lane < 24) {
+                const int pl = lane / 12, r = lane % 12;
+                if (r >= row_lo) {
+                    const uint2 v = ld_cg_u64((pl ? CPv : CPu) + (size_t)(mby * 8 - 4 + r) * cstride + (size_t)mbx * 8);
+                    uint32_t* d = reinterpret_cast<uint32_t*>(S.c[pl]) + r * 3 + 1;
+                    d[0] = v.x; d[1] = v.y;
+                }
+            }
+
+            // ---- calculate_filter_parameters, mod.rs:1191-1244 ----
+            const uint32_t mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mbi));
+            const int ymode = mbword & 0xff, segment = (mbword >> 16) & 3;
+            const bool skipped = (mbword >> 24) & 1;
+            int level = frame_level;
+            if (fd->segments_enabled) {
+                const int sl = fd->seg[segment].lf_level;
+                level = fd->seg[segment].delta_values ? level + sl : sl;
+            }
+            level = min(max(level, 0), 63);
+            if (fd->lf_adj_enabled) {
+                level += fd->ref_delta0;
+                if (ymode == 4) level += fd->mode_delta0;
+            }
+            level = min(max(level, 0), 63);
+            int interior = level;
+            if (sharp > 0) {
+                interior >>= sharp > 4 ? 2 : 1;
+                interior = min(interior, 9 - sharp);
+            }
+            if (interior == 0) interior = 1;
+            const int hev_thr = level >= 40 ? 2 : level >= 15 ? 1 : 0;
+            const int mbedge = (level + 2) * 2 + interior, subedge = level * 2 + interior;
+            const bool do_sub = ymode == 4 || (!skipped && A.mbinfo[mbi] != 0);  // mod.rs:977-978
+            __syncwarp();
+
+            // ---- loop_filter, mod.rs:966-1188: four edge groups in the reference's order ----
+            if (level > 0) {
+                if (simple) {
+                    // the simple filter reads 4 and writes 2 pixels per line, so the parallel
+                    // edges of one direction do not touch each other's pixels: do them together
+                    for (int k = lane; k < 64; k += 32) {  // vertical edges x = 0, 4, 8, 12
+                        const int e = k >> 4, r = k & 15;
+                        if (e == 0 ? mbx > 0 : do_sub) lf_line(S.y + (4 + r) * 20 + 4 + 4 * e, 1, 0, e == 0 ? mbedge : subedge, 0, 0);
+                    }
+                    __syncwarp();
+                    for (int k = lane; k < 64; k += 32) {  // horizontal edges y = 0, 4, 8, 12
+                        const int e = k >> 4, cidx = k & 15;
+                        if (e == 0 ? mby > 0 : do_sub) lf_line(S.y + (4 + 4 * e) * 20 + 4 + cidx, 20, 0, e == 0 ? mbedge : subedge, 0, 0);
+                    }
+                    __syncwarp();
+                } else {
+                    // lanes 0..15: luma lines; 16..23: U lines; 24..31: V lines
+                    uint8_t* base;
+                    int st_row, st_col, idx;
+                    if (lane < 16) { base = S.y + 4 * 20 + 4; st_row = 20; st_col = 1; idx = lane; }
+                    else { base = S.c[(lane - 16) >> 3] + 4 * 12 + 4; st_row = 12; st_col = 1; idx = (lane - 16) & 7; }
+                    if (mbx > 0) lf_line(base + idx * st_row, st_col, 2, mbedge, interior, hev_thr);
+                    __syncwarp();
+                    if (do_sub) {
+                        lf_line(base + idx * st_row + 4 * st_col, st_col, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                        if (lane < 16) lf_line(base + idx * st_row + 8, 1, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                        if (lane < 16) lf_line(base + idx * st_row + 12, 1, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                    }
+                    if (mby > 0) lf_line(base + idx * st_col, st_row, 2, mbedge, interior, hev_thr);
+                    __syncwarp();
+                    if (do_sub) {
+                        lf_line(base + idx * st_col + 4 * st_row, st_row, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                        if (lane < 16) lf_line(base + idx + 8 * 20, 20, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                        if (lane < 16) lf_line(base + idx + 12 * 20, 20, 1, subedge, interior, hev_thr);
+                        __syncwarp();
+                    }
+                }
+            }
+
+            // ---- write back columns -4..11 (and 12..15 on the last macroblock) ----
+            const bool last = mbx == mbw - 1;
+            const int wlo = mbx > 0 ? 0 : 1, whi = last ? 5 : 4;  // word columns of the tile row
+            for (int k = lane; k < 100; k += 32) {
+                const int r = k / 5, wc = k % 5;
+                if (r >= row_lo && wc >= wlo && wc < whi)
+                    *reinterpret_cast<uint32_t*>(Y + (size_t)(mby * 16 - 4 + r) * ystride + (size_t)mbx * 16 - 4 + 4 * wc) = y32[r * 5 + wc];
+            }
+            if (!simple) {
+                const int cwhi = last ? 3 : 2;
+                for (int k = lane; k < 72; k += 32) {
+                    const int pl = k / 36, r = (k % 36) / 3, wc = k % 3;
+                    if (r >= row_lo && wc >= wlo && wc < cwhi)
+                        *reinterpret_cast<uint32_t*>((pl ? CPv : CPu) + (size_t)(mby * 8 - 4 + r) * cstride + (size_t)mbx * 8 - 4 + 4 * wc) =
+                            reinterpret_cast<uint32_t*>(S.c[pl])[r * 3 + wc];
+                }
+            }
+            __syncwarp();
+            // ---- carry the 4 right columns over as the next macroblock's left strip ----
+            if (lane < 20) y32[lane * 5] = y32[lane * 5 + 4];
+            if (!simple && lane < 24) {
+                uint32_t* c32 = reinterpret_cast<uint32_t*>(S.c[lane / 12]);
+                c32[(lane % 12) * 3] = c32[(lane % 12) * 3 + 2];
+            }
+            publish_row(prog_mine, mbx + 1, lane);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_yuv2rgb: one thread = 4 horizontally adjacent pixels of one row
+// ---------------------------------------------------------------------------------------------
+// yuv.rs:30-71
+__device__ __forceinline__ int mulhi8(int v, int coeff) { return (v * coeff) >> 8; }
+__device__ __forceinline__ int clip6(int v) { return min(max(v >> 6, 0), 255); }
+__device__ __forceinline__ void yuv_to_rgb(int y, int u, int v, int& r, int& g, int& b) {
+    const int yy = mulhi8(y, 19077);
+    r = clip6(yy + mulhi8(v, 26149) - 14234);
+    g = clip6(yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708);
+    b = clip6(yy + mulhi8(u, 33050) - 17685);
+}
+
+struct RgbArgs {
+    const webpb200_frame_desc* frames;
+    const uint8_t* planes;
+    uint8_t* out;
+};
+
+__global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
+    const webpb200_frame_desc* fd = A.frames + blockIdx.z;
+    const int w = fd->width, h = fd->height;
+    const int y = blockIdx.y;
+    const int x0 = (blockIdx.x * 128 + threadIdx.x) * 4;
+    if (y >= h || x0 >= w) return;
+    const int ystride = fd->mbw * 16, cstride = fd->mbw * 8;
+    const uint8_t* Y = A.planes + fd->y_off + (size_t)y * ystride;
+    const uint8_t* U = A.planes + fd->u_off;
+    const uint8_t* V = A.planes + fd->v_off;
+    const int bpp = fd->out_bpp;
+    uint8_t* out = A.out + fd->out_off + ((size_t)y * w + x0) * bpp;
+    const uint32_t yw = __ldg(reinterpret_cast<const uint32_t*>(Y + x0));
+    const int n = min(4, w - x0);
+    int uu[4], vv[4];
+    if (fd->upsampling == WEBPB200_UPSAMPLING_SIMPLE) {  // fill_rgb_buffer_simple, yuv.rs:293-382
+        const uint8_t* ur = U + (size_t)(y >> 1) * cstride + (x0 >> 1);
+        const uint8_t* vr = V + (size_t)(y >> 1) * cstride + (x0 >> 1);
+        uu[0] = uu[1] = ur[0]; uu[2] = uu[3] = ur[1];
+        vv[0] = vv[1] = vr[0]; vv[2] = vv[3] = vr[1];
+    } else {
+        // fill_rgb_buffer_fancy, yuv.rs:76-282, as a per-pixel rule: main chroma row rm and
+        // second row rs; main column cm and second column cs; 9:3:3:1 blend
+        int rm, rs;
+        if (y == 0) { rm = 0; rs = 0; }
+        else if (y & 1) { rm = (y - 1) >> 1; rs = rm + 1; }
+        else { rm = y >> 1; rs = rm - 1; }
+        if (y == h - 1 && !(h & 1)) rs = rm;
+        const uint8_t* um = U + (size_t)rm * cstride; const uint8_t* us = U + (size_t)rs * cstride;
+        const uint8_t* vm = V + (size_t)rm * cstride; const uint8_t* vs = V + (size_t)rs * cstride;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int x = x0 + i;
+            int cm, cs;
+            if (x == 0) { cm = 0; cs = 0; }
+            else if (x & 1) { cm = (x - 1) >> 1; cs = cm + 1; }
+            else { cm = x >> 1; cs = cm - 1; }
+            if (x == w - 1 && !(w & 1)) cs = cm;
+            if (i < n) {
+                uu[i] = (9 * um[cm] + 3 * um[cs] + 3 * us[cm] + us[cs] + 8) >> 4;
+                vv[i] = (9 * vm[cm] + 3 * vm[cs] + 3 * vs[cm] + vs[cs] + 8) >> 4;
+            } else { uu[i] = 0; vv[i] = 0; }
+        }
+    }
+    int r[4], g[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) yuv_to_rgb((yw >> (8 * i)) & 0xff, uu[i], vv[i], r[i], g[i], b[i]);
+    if (bpp == 4) {
+        // byte 3 is the ALPH merge's (yuv.rs:285-289 leaves it alone; decoder.rs:704-734
+        // always fills it afterwards); 255 until then
+        if (n == 4) {
+            uint4 o;
+            o.x = r[0] | (g[0] << 8) | (b[0] << 16) | 0xff000000u; o.y = r[1] | (g[1] << 8) | (b[1] << 16) | 0xff000000u;
+            o.z = r[2] | (g[2] << 8) | (b[2] << 16) | 0xff000000u; o.w = r[3] | (g[3] << 8) | (b[3] << 16) | 0xff000000u;
+            if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) { *reinterpret_cast<uint4*>(out) = o; }
+            else { uint32_t* o32 = reinterpret_cast<uint32_t*>(out); o32[0] = o.x; o32[1] = o.y; o32[2] = o.z; o32[3] = o.w; }
+        } else {
+            for (int i = 0; i < n; i++) reinterpret_cast<uint32_t*>(out)[i] = r[i] | (g[i] << 8) | (b[i] << 16) | 0xff000000u;
+        }
+    } else {
+        if (n == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+            uint32_t* o32 = reinterpret_cast<uint32_t*>(out);
+            o32[0] = r[0] | (g[0] << 8) | (b[0] << 16) | (r[1] << 24);
+            o32[1] = g[1] | (b[1] << 8) | (r[2] << 16) | (g[2] << 24);
+            o32[2] = b[2] | (r[3] << 8) | (g[3] << 16) | (b[3] << 24);
+        } else {
+            for (int i = 0; i < n; i++) { out[3 * i] = (uint8_t)r[i]; out[3 * i + 1] = (uint8_t)g[i]; out[3 * i + 2] = (uint8_t)b[i]; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ALPH un-filter + merge (decoder.rs:718-734, get_alpha_predictor extended.rs:131-191).
+// alpha = predictor + residual (mod 256), predictor from already-merged neighbours.
+//   none:       alpha = residual
+//   horizontal: row prefix sums, each row started from the pixel above its first pixel
+//   vertical:   column prefix sums, row 0 is a horizontal prefix sum
+//   gradient:   clamp(L + T - TL) -- a true 2-D recurrence, done as a row-skewed wavefront
+// ---------------------------------------------------------------------------------------------
+struct AlphaArgs {
+    const webpb200_frame_desc* frames;
+    const uint8_t* alpha;
+    uint8_t* out;
+    const int* list;  // frame indices handled by this launch
+};
+
+__global__ void k_alpha_none(AlphaArgs A) {
+    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.y];
+    const size_t n = (size_t)fd->width * fd->height;
+    const uint8_t* a = A.alpha + fd->alpha_off;
+    uint8_t* o = A.out + fd->out_off;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) o[4 * i + 3] = a[i];
+}
+
+// first column (horizontal filter) / first row (vertical filter): one warp per image does the
+// serial prefix sum in 32-element steps
+__global__ void k_alpha_seed(AlphaArgs A, int vertical) {
+    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.x];
+    const int w = fd->width, h = fd->height;
+    const uint8_t* a = A.alpha + fd->alpha_off;
+    uint8_t* o = A.out + fd->out_off;
+    const int lane = threadIdx.x;
+    const int n = vertical ? w : h;
+    const size_t stride = vertical ? 1 : (size_t)w;
+    unsigned carry = 0;
+    for (int base = 0; base < n; base += 32) {
+        const int i = base + lane;
+        unsigned v = i < n ? a[(size_t)i * stride] : 0;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned u = __shfl_up_sync(kFull, v, d);
+            if (lane >= d) v += u;
+        }
+        v += carry;
+        if (i < n) o[(size_t)i * stride * 4 + 3] = (uint8_t)v;
+        carry = __shfl_sync(kFull, v, 31) & 0xff;
+    }
+}
+
+// horizontal: one warp per row, continuing from the seeded first pixel
+__global__ void k_alpha_rows(AlphaArgs A) {
+    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.y];
+    const int w = fd->width, h = fd->height;
+    const int y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (y >= h) return;
+    const int lane = threadIdx.x & 31;
+    const uint8_t* a = A.alpha + fd->alpha_off + (size_t)y * w;
+    uint8_t* o = A.out + fd->out_off + (size_t)y * w * 4;
+    unsigned carry = o[3];
+    for (int base = 1; base < w; base += 32) {
+        const int x = base + lane;
+        unsigned v = x < w ? a[x] : 0;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned u = __shfl_up_sync(kFull, v, d);
+            if (lane >= d) v += u;
+        }
+        v += carry;
+        if (x < w) o[(size_t)x * 4 + 3] = (uint8_t)v;
+        carry = __shfl_sync(kFull, v, 31) & 0xff;
+    }
+}
+
+// vertical: one thread per column, walking down from the seeded first row
+__global__ void k_alpha_cols(AlphaArgs A) {
+    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.y];
+    const int w = fd->width, h = fd->height;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= w) return;
+    const uint8_t* a = A.alpha + fd->alpha_off;
+    uint8_t* o = A.out + fd->out_off;
+    unsigned v = o[(size_t)x * 4 + 3];
+    for (int y = 1; y < h; y++) {
+        v = (v + a[(size_t)y * w + x]) & 0xff;
+        o[((size_t)y * w + x) * 4 + 3] = (uint8_t)v;
+    }
+}
+
+// gradient: one warp per image; 32 rows at a time, lane j = row r0 + j running j columns
+// behind the lane above, so T and TL arrive by shuffle; the row above the group is re-read
+// from the output
+__global__ void k_alpha_gradient(AlphaArgs A) {
+    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.x];
+    const int w = fd->width, h = fd->height;
+    const uint8_t* a = A.alpha + fd->alpha_off;
+    uint8_t* o = A.out + fd->out_off;
+    const int lane = threadIdx.x;
+    for (int r0 = 0; r0 < h; r0 += 32) {
+        const int y = r0 + lane;
+        int cur = 0, prev = 0;  // my alpha at column x-1 (cur after update) and the one before
+        for (int t = 0; t < w + 31; t++) {
+            const int x = t - lane;
+            // the lane above finished column x in the previous step (its cur) and x-1 before that
+            int T = __shfl_up_sync(kFull, cur, 1), TL = __shfl_up_sync(kFull, prev, 1);
+            const bool active = x >= 0 && x < w && y < h;
+            if (lane == 0 && active && y > 0) {
+                T = o[((size_t)(y - 1) * w + x) * 4 + 3];
+                TL = x > 0 ? o[((size_t)(y - 1) * w + x - 1) * 4 + 3] : 0;
+            }
+            if (active) {
+                const int L = cur;
+                int pred;
+                if (x == 0 && y == 0) pred = 0;
+                else if (x == 0) pred = T;        // (val, val, val) from above
+                else if (y == 0) pred = L;
+                else pred = min(max(L + T - TL, 0), 255);
+                const int v = (pred + a[(size_t)y * w + x]) & 0xff;
+                o[((size_t)y * w + x) * 4 + 3] = (uint8_t)v;
+                prev = cur;
+                cur = v;
+            }
+        }
+        __threadfence_block();
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_composite: extended.rs:30-129 + alpha_blending.rs:28-75, one thread per canvas pixel
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t div255(uint32_t v) { return (((v + 0x80) >> 8) + v + 0x80) >> 8; }
+
+__global__ void k_composite(CompositeArgs a) {
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= a.canvas_w || y >= a.canvas_h) return;
+    const size_t ci = ((size_t)y * a.canvas_w + x) * 4;
+    const bool full = a.fx == 0 && a.fy == 0 && a.fw == a.canvas_w && a.fh == a.canvas_h;
+    uint32_t c = *reinterpret_cast<const uint32_t*>(a.canvas + ci);
+    const bool in_frame = x >= a.fx && x < a.fx + a.fw && y >= a.fy && y < a.fy + a.fh;
+    uint32_t src = 0;
+    if (in_frame) {
+        const size_t fi = (size_t)(y - a.fy) * a.fw + (x - a.fx);
+        if (a.frame_has_alpha) src = *reinterpret_cast<const uint32_t*>(a.frame + fi * 4);
+        else src = a.frame[fi * 3] | (a.frame[fi * 3 + 1] << 8) | (a.frame[fi * 3 + 2] << 16) | 0xff000000u;
+    }
+    if (full && !a.use_blend) {
+        c = src;
+    } else {
+        if (a.has_clear && (full || (x >= a.px && x < a.px + a.pw && y >= a.py && y < a.py + a.ph)))
+            c = a.clear[0] | (a.clear[1] << 8) | (a.clear[2] << 16) | ((uint32_t)a.clear[3] << 24);
+        if (in_frame) {
+            if (a.frame_has_alpha && a.use_blend) {
+                const uint32_t sa = src >> 24;
+                if (sa != 0) {
+                    const uint32_t da = c >> 24;
+                    const uint32_t dfa = div255(da * (255 - sa));
+                    const uint32_t ba = sa + dfa;
+                    const uint32_t scale = (1u << 24) / ba;
+                    const uint32_t dfa8 = dfa & 0xff;
+                    uint32_t o = ba << 24;
+                    for (int k = 0; k < 3; k++) {
+                        const uint32_t sc = (src >> (8 * k)) & 0xff, dc = (c >> (8 * k)) & 0xff;
+                        o |= (((sc * sa + dc * dfa8) * scale) >> 24 & 0xff) << (8 * k);
+                    }
+                    c = o;
+                }
+            } else {
+                c = src;
+            }
+        }
+    }
+    *reinterpret_cast<uint32_t*>(a.canvas + ci) = c;
+    if (a.out) {
+        if (a.out_bpp == 4) {
+            *reinterpret_cast<uint32_t*>(a.out + ci) = c;
+        } else {
+            uint8_t* o = a.out + ((size_t)y * a.canvas_w + x) * 3;
+            o[0] = (uint8_t)c; o[1] = (uint8_t)(c >> 8); o[2] = (uint8_t)(c >> 16);
+        }
+    }
+}
+
+int blocks_for(const void* kernel, int threads, int sm_count) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
+    if (per_sm < 1) per_sm = 1;
+    return per_sm * sm_count;
+}
+
+}  // namespace
+
+cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
+    PredictArgs a;
+    a.frames = b.frames; a.mbs = b.mbs; a.levels = b.levels; a.planes = b.planes;
+    a.ticket = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off);
+    a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
+    a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_pred_off);
+    a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
+    a.mbinfo = b.scratch + b.lay.mbinfo_off;
+    a.total_rows = b.total_rows;
+    static int blocks = 0;
+    if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_predict), kThreads, b.sm_count);
+    int grid = blocks;
+    const int need = (int)((b.total_rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    k_predict<<<grid, kThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
+    FilterArgs a;
+    a.frames = b.frames; a.mbs = b.mbs; a.planes = b.planes;
+    a.ticket = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 1;
+    a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
+    a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_lf_off);
+    a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
+    a.mbinfo = b.scratch + b.lay.mbinfo_off;
+    a.total_rows = b.total_rows;
+    static int blocks = 0;
+    if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_loopfilter), kThreads, b.sm_count);
+    int grid = blocks;
+    const int need = (int)((b.total_rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+    k_loopfilter<<<grid, kThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
+    RgbArgs a;
+    a.frames = b.frames; a.planes = b.planes; a.out = b.out;
+    dim3 grid((b.max_w + 511) / 512, b.max_h, b.n_frames);
+    k_yuv2rgb<<<grid, 128, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches) {
+    // frames grouped by ALPH filter method; the index lists were uploaded with the batch
+    const int* const counts = b.alpha_counts;
+    if (counts[0] + counts[1] + counts[2] + counts[3] == 0) return cudaSuccess;
+    AlphaArgs a;
+    a.frames = b.frames; a.alpha = b.alpha; a.out = b.out;
+    if (counts[0]) {
+        a.list = b.alpha_lists;
+        k_alpha_none<<<dim3(b.sm_count * 2, counts[0]), 256, 0, s>>>(a);
+        ++*launches;
+    }
+    if (counts[1]) {
+        a.list = b.alpha_lists + b.n_frames;
+        k_alpha_seed<<<counts[1], 32, 0, s>>>(a, 0);
+        k_alpha_rows<<<dim3((b.alpha_maxh[1] + 7) / 8, counts[1]), 256, 0, s>>>(a);
+        *launches += 2;
+    }
+    if (counts[2]) {
+        a.list = b.alpha_lists + 2 * b.n_frames;
+        k_alpha_seed<<<counts[2], 32, 0, s>>>(a, 1);
+        k_alpha_cols<<<dim3((b.alpha_maxw[2] + 127) / 128, counts[2]), 128, 0, s>>>(a);
+        *launches += 2;
+    }
+    if (counts[3]) {
+        a.list = b.alpha_lists + 3 * b.n_frames;
+        k_alpha_gradient<<<counts[3], 32, 0, s>>>(a);
+        ++*launches;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_composite(const CompositeArgs& a, cudaStream_t s) {
+    dim3 grid((a.canvas_w + 255) / 256, a.canvas_h);
+    k_composite<<<grid, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace webpb200

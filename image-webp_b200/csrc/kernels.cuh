@@ -1,0 +1,68 @@
+// kernels.cuh -- launch interface of the sm_100a reconstruction kernels (kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "../../include/webpb200.h"
+
+namespace webpb200 {
+
+// Scratch words at the head of the scratch arena (must be zero before a reconstruct pass).
+//   [0] ticket counter of the prediction wavefront   [1] ticket counter of the loop filter
+//   [2] watchdog abort word (non-zero after a pass = a wavefront wait timed out)
+// followed by two int arrays of `total_rows` row-progress counters (prediction, loop filter),
+// then `total_rows` uint32 ticket -> image map, then one byte per macroblock (non_zero_dct).
+struct ScratchLayout {
+    uint64_t tickets_off, progress_pred_off, progress_lf_off, rowmap_off, mbinfo_off, total;
+    uint64_t zero_bytes;  // prefix that must be cleared before every pass
+};
+ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs);
+
+struct BatchDev {
+    const webpb200_frame_desc* frames;  // device
+    const webpb200_mb_desc* mbs;
+    const int16_t* levels;
+    const uint8_t* alpha;  // alpha residual planes (may be null)
+    uint8_t* planes;
+    uint8_t* out;
+    uint8_t* scratch;
+    ScratchLayout lay;
+    int n_frames;
+    uint32_t total_rows;
+    uint32_t max_w, max_h;  // largest frame of the batch (grid sizing)
+    int sm_count;
+    // frames with an ALPH plane, grouped by filter method m: alpha_lists[m * n_frames + k]
+    const int* alpha_lists;  // device
+    int alpha_counts[4];
+    uint32_t alpha_maxw[4], alpha_maxh[4];
+};
+
+void upload_tables_once();  // prediction tables -> __constant__ (per device, call with it current)
+
+// dequant + IWHT/IDCT + intra prediction, row-per-warp macroblock wavefront
+cudaError_t launch_predict(const BatchDev& b, cudaStream_t s);
+// simple / normal loop filter, same wavefront
+cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s);
+// fancy / simple upsampling + YUV -> RGB(A)
+cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s);
+// ALPH un-filter + merge into byte 3 of the RGBA output; adds its launch count to *launches
+cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches);
+
+struct CompositeArgs {  // one composite_frame call, reference extended.rs:30-129
+    uint8_t* canvas;       // canvas_w * canvas_h * 4, device
+    const uint8_t* frame;  // frame pixels, device (3 or 4 bytes per pixel)
+    uint8_t* out;          // canvas copy handed to the caller after this frame, device
+    uint32_t canvas_w, canvas_h;
+    uint32_t fx, fy, fw, fh;
+    uint32_t px, py, pw, ph;  // previous frame rectangle
+    uint8_t clear[4];
+    int has_clear, frame_has_alpha, use_blend, out_bpp;
+};
+cudaError_t launch_composite(const CompositeArgs& a, cudaStream_t s);
+
+// CPU evaluation of the B_PRED lookup table (for the table's unit test; no GPU needed):
+// edge = {P, A0..A7, L0..L3}, out = 16 predicted pixels, mode = IntraMode 1..9
+void bpred_table_eval(int mode, const uint8_t edge[13], uint8_t out[16]);
+
+}  // namespace webpb200

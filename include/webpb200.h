@@ -1,0 +1,228 @@
+/* include/webpb200.h -- C ABI of libwebpb200.so: B200-native lossy WebP (VP8) reconstruction.
+ *
+ * The reference (image-rs/image-webp v0.2.4) is a Rust crate with no FFI of its own; this
+ * header is the C-ABI seam a Rust `extern "C"` block (or cgo / ctypes) binds to replace the
+ * crate's lossy decode path.  Each entry point cites the reference item it stands in for.
+ * Plain pointers and sizes only; no CUDA or torch types.  All functions return a status
+ * (0 = ok, else a WEBPB200_ERR_* value mirroring DecodingError, decoder.rs:14-168) unless
+ * stated otherwise.  The library has NO CPU fallback: without a CUDA device every decode
+ * call fails with WEBPB200_ERR_NO_DEVICE.
+ */
+#ifndef WEBPB200_H
+#define WEBPB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    WEBPB200_OK = 0,
+    WEBPB200_ERR_IO = 1,                 /* IoError / unexpected end of data      */
+    WEBPB200_ERR_RIFF_SIGNATURE = 2,     /* ChunkHeaderInvalid("RIFF")            */
+    WEBPB200_ERR_WEBP_SIGNATURE = 3,     /* WebpSignatureInvalid                  */
+    WEBPB200_ERR_CHUNK_MISSING = 4,      /* ChunkMissing                          */
+    WEBPB200_ERR_CHUNK_HEADER = 5,       /* ChunkHeaderInvalid(fourcc)            */
+    WEBPB200_ERR_VP8_MAGIC = 6,          /* Vp8MagicInvalid                       */
+    WEBPB200_ERR_UNSUPPORTED = 7,        /* UnsupportedFeature                    */
+    WEBPB200_ERR_COLOR_SPACE = 8,        /* ColorSpaceInvalid                     */
+    WEBPB200_ERR_BITSTREAM = 9,          /* BitStreamError                        */
+    WEBPB200_ERR_INCONSISTENT_SIZE = 10, /* InconsistentImageSizes                */
+    WEBPB200_ERR_IMAGE_TOO_LARGE = 11,   /* ImageTooLarge (also wrong buffer len) */
+    WEBPB200_ERR_FRAME_OUTSIDE = 12,     /* FrameOutsideImage                     */
+    WEBPB200_ERR_LOSSLESS_SIG = 13,      /* LosslessSignatureInvalid              */
+    WEBPB200_ERR_VERSION = 14,           /* VersionNumberInvalid                  */
+    WEBPB200_ERR_COLOR_CACHE = 15,       /* InvalidColorCacheBits                 */
+    WEBPB200_ERR_HUFFMAN = 16,           /* HuffmanError                          */
+    WEBPB200_ERR_TRANSFORM = 17,         /* TransformError                        */
+    WEBPB200_ERR_ALPHA_PREPROC = 18,     /* InvalidAlphaPreprocessing             */
+    WEBPB200_ERR_COMPRESSION = 19,       /* InvalidCompressionMethod              */
+    WEBPB200_ERR_NO_MORE_FRAMES = 20,    /* NoMoreFrames                          */
+    WEBPB200_ERR_CHUNK_SIZE = 21,        /* InvalidChunkSize                      */
+    WEBPB200_ERR_NOT_ANIMATED = 22,      /* reference panics, decoder.rs:753      */
+    WEBPB200_ERR_INVALID_PARAM = 23,     /* InvalidParameter                      */
+    WEBPB200_ERR_NOMEM = 24,
+    WEBPB200_ERR_NOT_LOSSY = 25,         /* VP8L still/animation frame: outside this library's path */
+    WEBPB200_ERR_NO_DEVICE = 100,        /* no usable CUDA device                 */
+    WEBPB200_ERR_CUDA = 101              /* a CUDA call failed (see webpb200_last_cuda_error) */
+};
+
+enum { WEBPB200_UPSAMPLING_BILINEAR = 0, WEBPB200_UPSAMPLING_SIMPLE = 1 }; /* decoder.rs:297-309 */
+
+/* ---------------------------------------------------------------------------------------
+ * Packed arrays at the host -> device boundary.  The host entropy decoder fills them; the
+ * kernels read them.  All little-endian, naturally aligned.
+ * ------------------------------------------------------------------------------------- */
+
+/* One quantiser/loop-filter segment, common.rs:718-733 (quantisers already resolved per
+ * lossy/mod.rs:397-451). */
+typedef struct {
+    int16_t ydc, yac, y2dc, y2ac, uvdc, uvac;
+    int8_t lf_level;       /* Segment::loopfilter_level */
+    uint8_t delta_values;  /* Segment::delta_values     */
+    uint8_t pad[2];
+} webpb200_segment;        /* 16 bytes */
+
+/* One VP8 keyframe of the batch (Frame + the header fields reconstruction needs,
+ * lossy/mod.rs:132-167, 262-268). */
+typedef struct {
+    uint16_t width, height, mbw, mbh;
+    uint8_t filter_type;       /* 1 = simple, 0 = normal (mod.rs:164)  */
+    uint8_t filter_level;      /* frame level 0..63                    */
+    uint8_t sharpness;         /* 0..7                                 */
+    uint8_t segments_enabled;
+    uint8_t lf_adj_enabled;    /* loop_filter_adjustments_enabled      */
+    int8_t ref_delta0;         /* ref_delta[0]  (mod.rs:1211)          */
+    int8_t mode_delta0;        /* mode_delta[0] (mod.rs:1213)          */
+    uint8_t out_bpp;           /* 3 = RGB, 4 = RGBA                    */
+    uint8_t upsampling;        /* WEBPB200_UPSAMPLING_*                */
+    uint8_t alpha_mode;        /* 0 none | 1 ALPH plane present (filter in alpha_filter) */
+    uint8_t alpha_filter;      /* FilteringMethod 0..3 (extended.rs:245-251) */
+    uint8_t pad0;
+    webpb200_segment seg[4];
+    uint32_t mb_base;          /* first macroblock in the MbDesc / level arrays      */
+    uint32_t row_base;         /* first macroblock row in the row-progress arrays    */
+    uint64_t y_off, u_off, v_off; /* byte offsets of the planes in the plane arena   */
+    uint64_t out_off;          /* byte offset of the output image in the output arena */
+    uint64_t alpha_off;        /* byte offset of the w*h alpha residual plane        */
+} webpb200_frame_desc;         /* 136 bytes */
+
+/* One macroblock as decoded by the host (MacroBlock, lossy/mod.rs:112-120). */
+typedef struct {
+    uint8_t ymode;      /* LumaMode: 0 DC 1 V 2 H 3 TM 4 B (common.rs:44-61)            */
+    uint8_t uvmode;     /* ChromaMode: 0 DC 1 V 2 H 3 TM                                */
+    uint8_t segment;    /* segmentid 0..3                                               */
+    uint8_t flags;      /* bit0 = coeffs_skipped                                        */
+    uint32_t nflags;    /* bit b: read_coefficients returned true for block b; 24 = Y2  */
+    uint8_t bpred[8];   /* 16 IntraMode nibbles (common.rs:115-129): sub-block k in
+                           bits 4*(k&1).. of byte k>>1                                 */
+} webpb200_mb_desc;     /* 16 bytes */
+
+/* Levels: int16 [macroblock][25][16], raw token values before dequantisation, de-zigzagged
+ * (raster inside a 4x4 block); blocks 0-15 Y, 16-19 U, 20-23 V, 24 Y2. 800 bytes per MB. */
+#define WEBPB200_LEVELS_PER_MB 400
+
+/* ---------------------------------------------------------------------------------------
+ * WebPDecoder surface (decoder.rs:312-940).  `data` is borrowed and must outlive the
+ * decoder.  One decoder is single-threaded; separate decoders are independent.
+ * ------------------------------------------------------------------------------------- */
+typedef struct webpb200_decoder webpb200_decoder;
+
+/* WebPDecoder::new_with_options, decoder.rs:342-363 (container scan only, no pixel work) */
+int webpb200_open(const uint8_t* data, size_t len, int upsampling, webpb200_decoder** out);
+void webpb200_close(webpb200_decoder* d);
+void webpb200_dimensions(const webpb200_decoder* d, uint32_t* w, uint32_t* h); /* decoder.rs:580 */
+int webpb200_has_alpha(const webpb200_decoder* d);        /* decoder.rs:586 */
+int webpb200_is_animated(const webpb200_decoder* d);      /* decoder.rs:591 */
+int webpb200_is_lossy(const webpb200_decoder* d);         /* decoder.rs:599 */
+uint32_t webpb200_num_frames(const webpb200_decoder* d);  /* decoder.rs:605 */
+uint32_t webpb200_loop_count(const webpb200_decoder* d);  /* decoder.rs:610; 0 = forever */
+uint64_t webpb200_loop_duration(const webpb200_decoder* d); /* decoder.rs:618 */
+size_t webpb200_output_buffer_size(const webpb200_decoder* d); /* decoder.rs:659-664 */
+int webpb200_set_background_color(webpb200_decoder* d, const uint8_t rgba[4]); /* decoder.rs:568 */
+void webpb200_set_lossy_upsampling(webpb200_decoder* d, int upsampling);       /* decoder.rs:938 */
+/* WebPDecoder::read_image, decoder.rs:669-741: tightly packed RGB8 / RGBA8 into buf;
+ * len must equal output_buffer_size() else WEBPB200_ERR_IMAGE_TOO_LARGE. */
+int webpb200_read_image(webpb200_decoder* d, uint8_t* buf, size_t len);
+/* WebPDecoder::read_frame, decoder.rs:752-922: next composited canvas + its duration. */
+int webpb200_read_frame(webpb200_decoder* d, uint8_t* buf, size_t len, uint32_t* duration_ms);
+int webpb200_reset_animation(webpb200_decoder* d);        /* decoder.rs:929-935 */
+/* vp8::Vp8Decoder::decode_frame, lossy/mod.rs:1247 (lib.rs:34-36): the loop-filtered,
+ * macroblock-padded planes of one VP8 chunk payload.  y: mbw*16 x mbh*16, u/v: mbw*8 x mbh*8.
+ * Pass NULL planes to query the sizes only. */
+int webpb200_vp8_decode_frame(const uint8_t* vp8, size_t len, uint16_t* width, uint16_t* height,
+                              uint8_t* y, uint8_t* u, uint8_t* v);
+
+/* ---------------------------------------------------------------------------------------
+ * Batched path (new; the reference decodes one image per call).  A context owns one CUDA
+ * device's stream, pinned staging and device arenas; they grow on demand and are reused.
+ * ------------------------------------------------------------------------------------- */
+typedef struct webpb200_ctx webpb200_ctx;
+
+int webpb200_device_count(void);                       /* 0 when no CUDA device is usable */
+int webpb200_ctx_create(int device, webpb200_ctx** out);
+void webpb200_ctx_destroy(webpb200_ctx* c);
+const char* webpb200_last_cuda_error(const webpb200_ctx* c);
+/* Page-locked host memory for input/output buffers (copies to and from it run asynchronously
+ * at full PCIe rate; pageable buffers work too, only slower).  NULL on failure. */
+void* webpb200_host_alloc(size_t bytes);
+void webpb200_host_free(void* p);
+
+/* N x (WebPDecoder::new + read_image) for still lossy files: host parse and entropy decode
+ * on `host_threads` threads, upload, reconstruct, download into outs[i] (out_lens[i] must be
+ * width*height*(3|4)).  status[i] gets each file's own code; a bad file does not poison the
+ * batch.  Returns the number of failed files, or a negative WEBPB200_ERR_* for a batch-level
+ * failure (no device, CUDA error). */
+int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n,
+                          uint8_t* const* outs, const size_t* out_lens, int* status,
+                          int upsampling, int host_threads);
+
+/* The same in stages, so the device-resident part can be timed alone:
+ *   prepare  = host side of decode_frame (header + per-macroblock entropy decode,
+ *              lossy/mod.rs:510-671, 785-963) into pinned packed arrays
+ *   upload   = one async copy per array to the device
+ *   reconstruct = everything after entropy decoding, on the device (see below)
+ *   download = output arena back to outs[]                                             */
+int webpb200_batch_prepare(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n,
+                           int* status, int upsampling, int host_threads);
+int webpb200_batch_upload(webpb200_ctx* c);
+/* stages: bit0 dequant+IWHT/IDCT+intra prediction (mod.rs:673-783, 866, 898-952),
+ * bit1 loop filter (mod.rs:966-1244), bit2 YUV->RGB(A) (mod.rs:184-241, yuv.rs),
+ * bit3 alpha un-filter + merge (decoder.rs:718-734); 0xF = all.  Asynchronous. */
+int webpb200_batch_reconstruct(webpb200_ctx* c, unsigned stages);
+int webpb200_batch_sync(webpb200_ctx* c);
+int webpb200_batch_download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens);
+/* Runs reconstruct(stages) `iters` times back to back and returns the mean device time of
+ * one pass in milliseconds, measured with CUDA events on the context's stream.  If
+ * flush_l2 != 0 a buffer larger than L2 is overwritten between passes (outside the
+ * timed spans).  kernel_ms (may be NULL) receives per-kernel mean times [4]. */
+int webpb200_batch_time(webpb200_ctx* c, unsigned stages, int iters, int flush_l2, float* ms_per_pass,
+                        float* kernel_ms);
+/* introspection for tests and bench */
+int webpb200_batch_size(const webpb200_ctx* c, int* n_images, uint64_t* n_macroblocks,
+                        uint64_t* n_pixels, uint64_t* in_bytes, uint64_t* out_bytes);
+/* planes of image i as they are on the device now (after stage bit0: unfiltered, after
+ * bit1: loop-filtered); macroblock-padded sizes as for webpb200_vp8_decode_frame. */
+int webpb200_batch_get_planes(webpb200_ctx* c, int image, uint8_t* y, uint8_t* u, uint8_t* v);
+/* host-side packed arrays of image i (pointers into pinned staging, valid until the next
+ * prepare): lets tests diff the boundary arrays against the oracle. */
+int webpb200_batch_get_packed(webpb200_ctx* c, int image, const webpb200_frame_desc** frame,
+                              const webpb200_mb_desc** mbs, const int16_t** levels);
+/* number of kernel launches issued by this context so far (bench.py's gpu_launches) */
+uint64_t webpb200_launch_count(const webpb200_ctx* c);
+
+/* The host half alone, without touching CUDA: container walk + everything Vp8Decoder reads
+ * from the bitstream (lossy/mod.rs:510-671, 785-963) for one still lossy file, into caller
+ * arrays; also the ALPH residual plane (extended.rs:253-308) when the file has one.  Call with
+ * mbs = NULL to learn the sizes (fd->mbw * fd->mbh macroblocks, width*height alpha bytes). */
+int webpb200_host_entropy_decode(const uint8_t* file, size_t len, webpb200_frame_desc* fd,
+                                 webpb200_mb_desc* mbs, size_t mbs_cap, int16_t* levels, size_t levels_cap,
+                                 uint8_t* alpha, size_t alpha_cap);
+/* Evaluates the kernels' 4x4 sub-block prediction table on the CPU (table self-test):
+ * edge13 = {P, A0..A7, L0..L3} (prediction.rs:290-337), mode = IntraMode 1..9. */
+void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8_t* out16);
+
+/* Device-resident seam: reconstruct a batch whose packed arrays the caller already holds
+ * in device memory (all pointers are device pointers; d_planes / d_out / d_scratch sized
+ * from the frame descriptors by webpb200_workspace_sizes).  `stream` is a cudaStream_t
+ * passed as void*.  Replaces, for n frames at once, the device half of
+ * Vp8Decoder::decode_frame + Frame::fill_rgb/fill_rgba (+ the ALPH merge loop). */
+int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n, uint64_t* plane_bytes,
+                             uint64_t* out_bytes, uint64_t* scratch_bytes);
+int webpb200_reconstruct_device(const webpb200_frame_desc* h_frames, const webpb200_frame_desc* d_frames,
+                                int n, const webpb200_mb_desc* d_mbs, const int16_t* d_levels,
+                                const uint8_t* d_alpha, uint8_t* d_planes, uint8_t* d_out,
+                                void* d_scratch, unsigned stages, void* stream);
+
+/* All frames of one animated lossy file, composited (extended.rs:30-129), as read_frame
+ * would return them one after another: frames reconstruct as one batch, compositing runs
+ * frame by frame on the device.  outs[f] = canvas after frame f. */
+int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs,
+                              size_t out_len, uint32_t* durations_ms, int max_frames, int upsampling,
+                              int host_threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
