@@ -200,18 +200,22 @@ static int read_data(ora_decoder* d) {
     const uint8_t* p = d->r + start;
     size_t avail = d->len - (size_t)start;
     if (kind == CK_VP8) {
-        if (avail < 10) return ORA_ERR_IO;
+        /* sequential reads, decoder.rs:380-396: each can hit the end of the data on its own */
+        if (avail < 3) return ORA_ERR_IO;
         uint32_t tag = rd24(p);
         if (tag & 1) return ORA_ERR_UNSUPPORTED;
+        if (avail < 6) return ORA_ERR_IO;
         if (p[3] != 0x9d || p[4] != 0x01 || p[5] != 0x2a) return ORA_ERR_VP8_MAGIC;
+        if (avail < 10) return ORA_ERR_IO;
         d->width = (p[6] | (p[7] << 8)) & 0x3FFF;
         d->height = (p[8] | (p[9] << 8)) & 0x3FFF;
         if (d->width == 0 || d->height == 0) return ORA_ERR_INCONSISTENT_SIZE;
         chunk_insert(d, CK_VP8, start, start + csize);
         d->kind = 0; d->is_lossy = 1;
     } else if (kind == CK_VP8L) {
-        if (avail < 5) return ORA_ERR_IO;
+        if (avail < 1) return ORA_ERR_IO;
         if (p[0] != 0x2f) return ORA_ERR_LOSSLESS_SIG;
+        if (avail < 5) return ORA_ERR_IO;
         uint32_t header = p[1] | (p[2] << 8) | (p[3] << 16) | ((uint32_t)p[4] << 24);
         if (header >> 29) return ORA_ERR_VERSION;
         d->width = (header & 0x3FFF) + 1;

@@ -1,0 +1,157 @@
+"""Host half of the product (no GPU needed): the shared library loads and exports every symbol
+include/webpb200.h declares, the entropy decoder's packed arrays equal the oracle's, truncated
+streams get the same verdict, the kernels' B_PRED table equals the oracle's predictors."""
+import ctypes as C
+import re
+
+import numpy as np
+import pytest
+
+from util import LOSSY_STILL, ROOT, SYNTH_CASES, chunk_payload, product, vp8_payload
+
+
+@pytest.fixture(scope="module")
+def W():
+    w = product()
+    w.build()
+    return w
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from harness import synth as S
+    S.build()
+    return S
+
+
+def test_library_exports_every_declared_symbol(W):
+    header = open(ROOT + "/include/webpb200.h").read()
+    declared = sorted(set(re.findall(r"\b(webpb200_[a-z0-9_]+)\s*\(", header)))
+    assert declared == sorted(W.SYMBOLS)
+    raw = C.CDLL(W._SO)
+    for name in declared:
+        assert hasattr(raw, name), name
+
+
+def test_struct_sizes(W):
+    assert C.sizeof(W.FrameDesc) == 136 and C.sizeof(W.MbDesc) == 16
+
+
+def test_no_device_fails_loudly(W):
+    """No CPU fallback: without a CUDA device decode calls return NoCudaDevice."""
+    if W.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(W.DecodingError) as e:
+        W.BatchDecoder(0)
+    assert e.value.code == 100
+
+
+def _compare_packed(W, oracle, data):
+    fd, mbs, levels, alpha = W.host_entropy_decode(data)
+    fr = oracle.Vp8Frame(vp8_payload(data), keep=True)
+    f = fr.f
+    assert (fd.width, fd.height, fd.mbw, fd.mbh) == (fr.width, fr.height, fr.mbw, fr.mbh)
+    assert (fd.filter_type, fd.filter_level, fd.sharpness) == (f.filter_type, f.filter_level, f.sharpness_level)
+    assert (fd.segments_enabled, fd.lf_adj_enabled) == (f.segments_enabled, f.lf_adj_enabled)
+    assert (fd.ref_delta0, fd.mode_delta0) == (f.ref_delta[0], f.mode_delta[0])
+    for i in range(4 if f.segments_enabled else 1):
+        a, b = fd.seg[i], f.segment[i]
+        assert (a.ydc, a.yac, a.y2dc, a.y2ac, a.uvdc, a.uvac) == (b.ydc, b.yac, b.y2dc, b.y2ac, b.uvdc, b.uvac)
+    for i in range(4):
+        assert fd.seg[i].lf_level == f.segment[i].loopfilter_level
+        assert fd.seg[i].delta_values == f.segment[i].delta_values
+    om = fr.mbs
+    ym = np.array([m.luma_mode for m in om])
+    assert (mbs["ymode"] == ym).all()
+    assert (mbs["uvmode"] == np.array([m.chroma_mode for m in om])).all()
+    assert (mbs["segment"] == np.array([m.segmentid for m in om])).all()
+    assert ((mbs["flags"] & 1) == np.array([m.coeffs_skipped for m in om])).all()
+    assert (mbs["nflags"] == np.array([m.nflags for m in om], dtype=np.uint32)).all()
+    want = np.array([list(m.bpred) for m in om], dtype=np.uint8)
+    mine = np.stack([(mbs["bpred"][:, k >> 1] >> (4 * (k & 1))) & 15 for k in range(16)], axis=1)
+    assert (mine[ym == 4] == want[ym == 4]).all()
+    assert (mine[ym != 4] == 0).all()
+    assert np.array_equal(levels, fr.levels)
+    return fd, alpha
+
+
+@pytest.mark.parametrize("key", LOSSY_STILL)
+def test_packed_arrays_on_fixtures(W, oracle, fixtures, key):
+    data = fixtures["webp/" + key]
+    fd, alpha = _compare_packed(W, oracle, data)
+    if "_webp_a" in key:  # VP8L-compressed ALPH: the product's own VP8L decoder against the oracle's
+        ch = np.frombuffer(chunk_payload(data, b"ALPH"), np.uint8)
+        want = np.zeros((fd.height, fd.width), np.uint8)
+        flt = C.c_int()
+        assert oracle.lib().ora_read_alpha_chunk(ch.ctypes.data, ch.size, fd.width, fd.height, want.ctypes.data, C.byref(flt)) == 0
+        assert fd.alpha_filter == flt.value
+        assert np.array_equal(alpha, want)
+
+
+@pytest.mark.parametrize("name", sorted(SYNTH_CASES))
+def test_packed_arrays_on_synthetic(W, oracle, synth, name):
+    _compare_packed(W, oracle, synth.webp_simple(synth.vp8_frame(**SYNTH_CASES[name])))
+
+
+def test_truncated_streams_same_verdict(W, oracle, synth):
+    """arithmetic_decoder.rs:249-276: one byte past the end of a partition is fine, more is BitStreamError"""
+    vp8 = synth.vp8_frame(width=64, height=48, seed=77, filter_type=0, filter_level=10, log2_parts=1)
+    for cut in list(range(len(vp8) - 1, 11, -5)) + [10, 9, 5, 3, 1]:
+        try:
+            W.host_entropy_decode(synth.webp_simple(vp8[:cut]))
+            a = 0
+        except W.DecodingError as e:
+            a = e.code
+        try:
+            oracle.WebPDecoder(synth.webp_simple(vp8[:cut])).read_image()
+            b = 0
+        except oracle.OracleError as e:
+            b = e.code
+        assert a == b, cut
+
+
+def test_container_errors(W, oracle, fixtures):
+    good = bytes(fixtures["webp/gallery1/1"])
+    cases = [good[:3], b"RIFX" + good[4:], good[:8] + b"WEBQ" + good[12:], good[:12] + b"ABCD" + good[16:],
+             good[:23] + b"\x00" + good[24:],               # VP8 start code broken
+             good[:20] + bytes([good[20] | 1]) + good[21:]]  # inter frame
+    for data in cases:
+        try:
+            oracle.WebPDecoder(data)
+            a = 0
+        except oracle.OracleError as e:
+            a = e.code
+        h = C.c_void_p()
+        buf = np.frombuffer(data, np.uint8)
+        b = W.lib().webpb200_open(buf.ctypes.data, buf.size, 0, C.byref(h))
+        if h:
+            W.lib().webpb200_close(h)
+        assert a == b and a != 0
+
+
+def test_container_getters_match_oracle(W, oracle, fixtures):
+    for key in LOSSY_STILL + ["animated/random_lossy", "animated/random_lossless", "gallery2/1_webp_ll"]:
+        data = fixtures["webp/" + key]
+        a, b = oracle.WebPDecoder(data), W.WebPDecoder(data)
+        for name in ("dimensions", "has_alpha", "is_animated", "is_lossy", "num_frames", "loop_count", "loop_duration", "output_buffer_size"):
+            assert getattr(a, name)() == getattr(b, name)(), (key, name)
+
+
+def test_bpred_table_matches_oracle(W, oracle):
+    """The kernels' sub-block prediction table, evaluated on the CPU, against the oracle's
+    predictors (prediction.rs:238-499) on random edges."""
+    rng = np.random.default_rng(1)
+    for mode in range(1, 10):
+        for _ in range(200):
+            e = rng.integers(0, 256, 13, dtype=np.uint8)
+            got = np.zeros(16, np.uint8)
+            W.lib().webpb200_debug_bpred_eval(mode, e.ctypes.data, got.ctypes.data)
+            ws = np.zeros(16 + 6 * 32, np.uint8)
+            o = 16 + 32 + 4
+            ws[o - 33] = e[0]
+            ws[o - 32:o - 24] = e[1:9]
+            for j in range(4):
+                ws[o + 32 * j - 1] = e[9 + j]
+            oracle.lib().ora_predict_bmode(ws.ctypes.data + 16, 32, 4, 1, mode)
+            want = np.array([ws[o + 32 * y + x] for y in range(4) for x in range(4)])
+            assert np.array_equal(got, want), mode
