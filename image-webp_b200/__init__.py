@@ -34,6 +34,7 @@ ERROR_NAMES = {
     16: "HuffmanError", 17: "TransformError", 18: "InvalidAlphaPreprocessing",
     19: "InvalidCompressionMethod", 20: "NoMoreFrames", 21: "InvalidChunkSize", 22: "NotAnimated",
     23: "InvalidParameter", 24: "OutOfMemory", 25: "NotLossy", 100: "NoCudaDevice", 101: "CudaError",
+    102: "StaticScratchLimit",
 }
 
 
@@ -85,6 +86,7 @@ SYMBOLS = [
     "webpb200_batch_time", "webpb200_batch_size", "webpb200_batch_get_planes", "webpb200_batch_get_packed",
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
+    "webpb200_predict_device_static",
 ]
 
 
@@ -144,6 +146,7 @@ def lib():
     L.webpb200_workspace_sizes.argtypes = [vp, i32] + [C.POINTER(C.c_uint64)] * 3
     L.webpb200_reconstruct_device.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, C.c_uint, vp]
     L.webpb200_decode_animation.argtypes = [vp, vp, sz, pp, sz, C.POINTER(u32), i32, i32, i32]
+    L.webpb200_predict_device_static.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
     _lib = L
     return L
 
