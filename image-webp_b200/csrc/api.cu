@@ -120,7 +120,7 @@ struct webpb200_ctx {
     std::vector<WorkItem> items;
     uint64_t total_mbs = 0, total_rows = 0, total_px = 0;
     uint64_t plane_bytes = 0, out_bytes = 0, alpha_bytes = 0;
-    size_t aux_rowmap_off = 0, aux_lists_off = 0, aux_bytes = 0;
+    size_t aux_rowmap_off = 0, aux_order_off = 0, aux_lists_off = 0, aux_bytes = 0;
     BatchDev bd{};
     bool uploaded = false;
 
@@ -137,6 +137,19 @@ namespace {
     do {                                       \
         if ((c)->fail((call), what)) return -WEBPB200_ERR_CUDA; \
     } while (0)
+
+// Ticket order of the wavefront kernels: macroblock row 0 of every image, then row 1 of every
+// image, ...  A row only ever waits for the row above it in the same image, which in this order
+// was handed out a whole batch of rows earlier and is (nearly always) far ahead or finished, so
+// resident warps work instead of waiting.  (Image-major order keeps 2/3 of the warps spinning.)
+void fill_row_order(const webpb200_frame_desc* frames, int n, uint32_t* order) {
+    uint32_t max_h = 0;
+    for (int i = 0; i < n; i++) max_h = std::max<uint32_t>(max_h, frames[i].mbh);
+    size_t k = 0;
+    for (uint32_t r = 0; r < max_h; r++)
+        for (int i = 0; i < n; i++)
+            if (frames[i].mbh > r) order[k++] = frames[i].row_base + r;
+}
 
 // Host side of a batch: probe sizes, lay the arenas out, entropy-decode into pinned staging.
 int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
@@ -204,7 +217,8 @@ int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampl
     CU(c, c->h_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(mbs, 1)), "pinned levels");
     CU(c, c->h_alpha.reserve((size_t)std::max<uint64_t>(aoff, 1)), "pinned alpha");
     c->aux_rowmap_off = 0;
-    c->aux_lists_off = (size_t)align256(4 * rows);
+    c->aux_order_off = (size_t)align256(4 * rows);
+    c->aux_lists_off = c->aux_order_off + (size_t)align256(4 * rows);
     c->aux_bytes = c->aux_lists_off + (size_t)align256(16 * (uint64_t)std::max(n, 1));
     CU(c, c->h_aux.reserve(c->aux_bytes), "pinned aux");
     webpb200_mb_desc* hm = reinterpret_cast<webpb200_mb_desc*>(c->h_mbs.p);
@@ -242,7 +256,9 @@ int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampl
 
     // ticket -> image map and the ALPH lists by filter method
     uint32_t* rowmap = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
+    uint32_t* order = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off);
     int* lists = reinterpret_cast<int*>(c->h_aux.p + c->aux_lists_off);
+    fill_row_order(frames, n, order);
     BatchDev& bd = c->bd;
     std::memset(&bd, 0, sizeof(bd));
     for (int i = 0; i < n; i++) {
@@ -284,8 +300,10 @@ int upload(webpb200_ctx* c) {
     if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
     CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
     // the row map lives in the scratch arena next to the counters it is used with
-    if (c->total_rows)
+    if (c->total_rows) {
         CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
+    }
     BatchDev& bd = c->bd;
     bd.frames = reinterpret_cast<const webpb200_frame_desc*>(c->d_frames.p);
     bd.mbs = reinterpret_cast<const webpb200_mb_desc*>(c->d_mbs.p);
@@ -658,8 +676,17 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     }
     bd.lay = scratch_layout(rows, mbs);
     // row map and ALPH lists are built on the host and copied into the caller's scratch arena
-    std::vector<uint32_t> rowmap((size_t)rows, 0);
+    std::vector<uint32_t> rowmap((size_t)rows, 0), order((size_t)rows, 0);
     std::vector<int> lists((size_t)4 * n, 0);
+    {
+        size_t k = 0;  // rows in use may be fewer than `rows` if the caller left gaps; fill those with valid ids
+        uint32_t max_h = 0;
+        for (int i = 0; i < n; i++) max_h = std::max<uint32_t>(max_h, hf[i].mbh);
+        for (uint32_t r = 0; r < max_h; r++)
+            for (int i = 0; i < n; i++)
+                if (hf[i].mbh > r) order[k++] = hf[i].row_base + r;
+        rows = k;  // tickets handed out = rows that exist
+    }
     for (int i = 0; i < n; i++) {
         for (uint32_t r = 0; r < hf[i].mbh; r++) rowmap[hf[i].row_base + r] = (uint32_t)i;
         if (hf[i].alpha_mode && hf[i].out_bpp == 4) {
@@ -670,7 +697,8 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
         }
     }
     uint8_t* scratch = static_cast<uint8_t*>(d_scratch);
-    CU(c, cudaMemcpyAsync(scratch + bd.lay.rowmap_off, rowmap.data(), 4 * (size_t)rows, cudaMemcpyHostToDevice, s), "rowmap");
+    CU(c, cudaMemcpyAsync(scratch + bd.lay.rowmap_off, rowmap.data(), 4 * rowmap.size(), cudaMemcpyHostToDevice, s), "rowmap");
+    CU(c, cudaMemcpyAsync(scratch + bd.lay.order_off, order.data(), 4 * order.size(), cudaMemcpyHostToDevice, s), "row order");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.total, lists.data(), sizeof(int) * lists.size(), cudaMemcpyHostToDevice, s), "lists");
     CU(c, cudaStreamSynchronize(s), "sync");  // the host vectors go away
     bd.frames = d_frames; bd.mbs = d_mbs; bd.levels = d_levels; bd.alpha = d_alpha;

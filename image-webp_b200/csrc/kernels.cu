@@ -30,7 +30,8 @@ ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs) {
     l.progress_lf_off = up(l.progress_pred_off + 4 * total_rows);
     l.zero_bytes = up(l.progress_lf_off + 4 * total_rows);
     l.rowmap_off = l.zero_bytes;
-    l.mbinfo_off = up(l.rowmap_off + 4 * total_rows);
+    l.order_off = up(l.rowmap_off + 4 * total_rows);
+    l.mbinfo_off = up(l.order_off + 4 * total_rows);
     l.total = up(l.mbinfo_off + total_mbs);
     return l;
 }
@@ -55,6 +56,11 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ int ld_relaxed(const int* p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -66,16 +72,19 @@ __device__ __forceinline__ void st_release(int* p, int v) {
 __device__ __forceinline__ bool wait_row(const int* prog, int need, int& seen, int lane, unsigned int* abort_word) {
     if (seen >= need) return true;
     if (lane == 0) {
-        int v = ld_acquire(prog);
+        // poll with relaxed loads (an acquire load would invalidate L1 on every spin), then one
+        // fence: it pairs with the fence inside the producer's release store
+        int v = ld_relaxed(prog);
         unsigned spins = 0;
         while (v < need) {
-            __nanosleep(64);
-            v = ld_acquire(prog);
+            __nanosleep(100);
+            v = ld_relaxed(prog);
             if ((++spins & 0x3ff) == 0) {
                 if (spins > (1u << 24)) atomicExch(abort_word, 1u);
                 if (*reinterpret_cast<volatile unsigned int*>(abort_word)) { v = -1; break; }
             }
         }
+        __threadfence();
         seen = v;
     }
     seen = __shfl_sync(kFull, seen, 0);
@@ -86,10 +95,7 @@ __device__ __forceinline__ bool wait_row(const int* prog, int need, int& seen, i
 // Publish "macroblocks 0..done-1 of my row are finished": all lanes' global writes first.
 __device__ __forceinline__ void publish_row(int* prog, int done, int lane) {
     __syncwarp();
-    if (lane == 0) {
-        __threadfence();
-        st_release(prog, done);
-    }
+    if (lane == 0) st_release(prog, done);  // release = fence + store; the warp barrier orders the other lanes' writes before it
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -305,6 +311,7 @@ struct PredictArgs {
     unsigned int* abort_word;
     int* progress;
     const uint32_t* rowmap;
+    const uint32_t* order;
     uint8_t* mbinfo;
     uint32_t total_rows;
 };
@@ -326,16 +333,17 @@ __global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
         if (lane == 0) t = atomicAdd(A.ticket, 1u);
         t = __shfl_sync(kFull, t, 0);
         if (t >= A.total_rows) break;
-        const uint32_t img = __ldg(A.rowmap + t);
+        const uint32_t rid = __ldg(A.order + t);  // row id = image's row_base + macroblock row
+        const uint32_t img = __ldg(A.rowmap + rid);
         const webpb200_frame_desc* fd = A.frames + img;
         const int mbw = fd->mbw;
-        const int mby = (int)(t - fd->row_base);
+        const int mby = (int)(rid - fd->row_base);
         const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
         uint8_t* Y = A.planes + fd->y_off;
         uint8_t* U = A.planes + fd->u_off;
         uint8_t* V = A.planes + fd->v_off;
-        const int* prog_above = A.progress + t - 1;
-        int* prog_mine = A.progress + t;
+        const int* prog_above = A.progress + rid - 1;
+        int* prog_mine = A.progress + rid;
         int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
 
@@ -633,6 +641,7 @@ struct FilterArgs {
     unsigned int* abort_word;
     int* progress;
     const uint32_t* rowmap;
+    const uint32_t* order;
     const uint8_t* mbinfo;
     uint32_t total_rows;
 };
@@ -648,21 +657,22 @@ __global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
         if (lane == 0) t = atomicAdd(A.ticket, 1u);
         t = __shfl_sync(kFull, t, 0);
         if (t >= A.total_rows) break;
-        const uint32_t img = __ldg(A.rowmap + t);
+        const uint32_t rid = __ldg(A.order + t);
+        const uint32_t img = __ldg(A.rowmap + rid);
         const webpb200_frame_desc* fd = A.frames + img;
         const int frame_level = fd->filter_level;
         if (frame_level == 0) {  // mod.rs:1195-1198: nothing is filtered in this frame
-            if (lane == 0) st_release(A.progress + t, (int)fd->mbw);
+            if (lane == 0) st_release(A.progress + rid, (int)fd->mbw);
             continue;
         }
         const int mbw = fd->mbw;
-        const int mby = (int)(t - fd->row_base);
+        const int mby = (int)(rid - fd->row_base);
         const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
         uint8_t* Y = A.planes + fd->y_off;
         uint8_t* const CPu = A.planes + fd->u_off;
         uint8_t* const CPv = A.planes + fd->v_off;
-        const int* prog_above = A.progress + t - 1;
-        int* prog_mine = A.progress + t;
+        const int* prog_above = A.progress + rid - 1;
+        int* prog_mine = A.progress + rid;
         int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
         const bool simple = fd->filter_type != 0;
@@ -1072,6 +1082,7 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
     a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_pred_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
+    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
     static int blocks = 0;
@@ -1091,6 +1102,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
     a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_lf_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
+    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
     static int blocks = 0;

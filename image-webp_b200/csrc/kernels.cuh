@@ -12,9 +12,12 @@ namespace webpb200 {
 //   [0] ticket counter of the prediction wavefront   [1] ticket counter of the loop filter
 //   [2] watchdog abort word (non-zero after a pass = a wavefront wait timed out)
 // followed by two int arrays of `total_rows` row-progress counters (prediction, loop filter),
-// then `total_rows` uint32 ticket -> image map, then one byte per macroblock (non_zero_dct).
+// indexed by row id = frame.row_base + macroblock row; then `total_rows` uint32 row id -> image,
+// then `total_rows` uint32 ticket -> row id (the order rows are handed out in: any order in which
+// row y of an image comes after its row y-1 is valid; across images, row-major is the fast one),
+// then one byte per macroblock (non_zero_dct).
 struct ScratchLayout {
-    uint64_t tickets_off, progress_pred_off, progress_lf_off, rowmap_off, mbinfo_off, total;
+    uint64_t tickets_off, progress_pred_off, progress_lf_off, rowmap_off, order_off, mbinfo_off, total;
     uint64_t zero_bytes;  // prefix that must be cleared before every pass
 };
 ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs);

@@ -33,7 +33,7 @@ constexpr uint64_t kMaxRows = WEBPB200_STATIC_MAX_ROWS;
 constexpr uint64_t kMaxMbs = WEBPB200_STATIC_MAX_MBS;
 constexpr uint64_t up256(uint64_t v) { return (v + 255) & ~uint64_t(255); }
 // same arithmetic as scratch_layout() in kernels.cu, evaluated for the largest batch accepted
-constexpr uint64_t kScratchBytes = up256(up256(up256(256 + 4 * kMaxRows) + 4 * kMaxRows) + 4 * kMaxRows) + up256(kMaxMbs);
+constexpr uint64_t kScratchBytes = up256(up256(up256(up256(256 + 4 * kMaxRows) + 4 * kMaxRows) + 4 * kMaxRows) + 4 * kMaxRows) + up256(kMaxMbs);
 
 // The working memory.  In host code this name is only a handle for cudaGetSymbolAddress; the
 // address kernels must use is the one that call returns.
@@ -48,12 +48,16 @@ DeviceSlot g_slots[64];
 std::mutex g_slots_mu;
 
 // row -> image map, written straight into the static array (device code may name it)
-__global__ void k_static_rowmap(const webpb200_frame_desc* frames, int n, unsigned long long rowmap_off) {
+__global__ void k_static_rowmap(const webpb200_frame_desc* frames, int n, unsigned long long rowmap_off, unsigned long long order_off) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint32_t* rowmap = reinterpret_cast<uint32_t*>(g_wavefront_scratch + rowmap_off);
+    uint32_t* order = reinterpret_cast<uint32_t*>(g_wavefront_scratch + order_off);
     const uint32_t base = frames[i].row_base;
-    for (uint32_t r = 0; r < frames[i].mbh; r++) rowmap[base + r] = (uint32_t)i;
+    for (uint32_t r = 0; r < frames[i].mbh; r++) {
+        rowmap[base + r] = (uint32_t)i;
+        order[base + r] = base + r;  // rows handed out image by image: valid, and needs no sort
+    }
 }
 
 // One-time set-up for the current device: resolve the array's device address.
@@ -88,11 +92,12 @@ extern "C" int webpb200_predict_device_static(const webpb200_frame_desc* h_frame
                                               uint8_t* d_nonzero, void* stream) {
     if (n <= 0) return 0;
     if (!h_frames || !d_frames || !d_mbs || !d_levels || !d_planes) return WEBPB200_ERR_INVALID_PARAM;
-    uint64_t rows = 0, mbs = 0;
+    uint64_t rows = 0, mbs = 0, rows_present = 0;
     BatchDev bd;
     std::memset(&bd, 0, sizeof(bd));
     for (int i = 0; i < n; i++) {
         const uint64_t m = (uint64_t)h_frames[i].mbw * h_frames[i].mbh;
+        rows_present += h_frames[i].mbh;
         if ((uint64_t)h_frames[i].row_base + h_frames[i].mbh > rows) rows = (uint64_t)h_frames[i].row_base + h_frames[i].mbh;
         if ((uint64_t)h_frames[i].mb_base + m > mbs) mbs = (uint64_t)h_frames[i].mb_base + m;
         if (h_frames[i].width > bd.max_w) bd.max_w = h_frames[i].width;
@@ -101,6 +106,9 @@ extern "C" int webpb200_predict_device_static(const webpb200_frame_desc* h_frame
     // the fixed array cannot grow: refuse what does not fit instead of overrunning it
     if (rows > kMaxRows || mbs > kMaxMbs) return WEBPB200_ERR_STATIC_SCRATCH_LIMIT;
     if (rows == 0) return 0;
+    // row ids must be dense (row_base of each frame = sum of the earlier frames' mbh): a hole
+    // would be a ticket that points at nothing
+    if (rows_present != rows) return WEBPB200_ERR_INVALID_PARAM;
 
     DeviceSlot* slot = nullptr;
     int st = slot_for_current_device(&slot);
@@ -112,7 +120,7 @@ extern "C" int webpb200_predict_device_static(const webpb200_frame_desc* h_frame
     // the array still holds the previous call's counters: the ticket counter, the watchdog word and
     // every row's progress counter must start at zero (the map and the flags are rewritten in full)
     if (cudaMemsetAsync(slot->scratch, 0, (size_t)bd.lay.zero_bytes, s) != cudaSuccess) return WEBPB200_ERR_CUDA;
-    k_static_rowmap<<<(n + 127) / 128, 128, 0, s>>>(d_frames, n, (unsigned long long)bd.lay.rowmap_off);
+    k_static_rowmap<<<(n + 127) / 128, 128, 0, s>>>(d_frames, n, (unsigned long long)bd.lay.rowmap_off, (unsigned long long)bd.lay.order_off);
     if (cudaGetLastError() != cudaSuccess) return WEBPB200_ERR_CUDA;
 
     bd.frames = d_frames;
