@@ -21,7 +21,8 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libwebpb200.so")
+# WEBPB200_SO: developer override to A/B-test another build of the same library (tools/ab_build.sh)
+_SO = os.environ.get("WEBPB200_SO") or os.path.join(_HERE, "libwebpb200.so")
 _lib = None
 
 BILINEAR, SIMPLE = 0, 1
