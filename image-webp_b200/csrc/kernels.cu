@@ -65,6 +65,12 @@ __device__ __forceinline__ void st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // Wait until the row above has finished `need` macroblocks.  `seen` caches the last value read.
 // Watchdog: a wait that lasts absurdly long (a scheduling bug, never a data property) raises the
 // abort word; every waiter sees it, the kernel drains and the host reports an error instead of
@@ -300,6 +306,8 @@ struct __align__(16) PredictSmem {
     uint8_t vw[9 * 16];
     int16_t res[24 * 16];  // residuals of the 24 blocks, raster inside a block
     int32_t wht[16];
+    int16_t lv[WEBPB200_LEVELS_PER_MB];  // next macroblock's levels, prefetched with cp.async
+    uint4 desc;                          // and its descriptor
 };
 
 struct PredictArgs {
@@ -314,9 +322,27 @@ struct PredictArgs {
     const uint32_t* order;
     uint8_t* mbinfo;
     uint32_t total_rows;
+    int publish_every;  // progress is published every this many macroblocks (and at the row end)
 };
 
-__global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
+#ifndef PREDICT_MIN_BLOCKS
+#define PREDICT_MIN_BLOCKS 4
+#endif
+
+// levels (800 B) + descriptor (16 B) of macroblock `mbi` -> the warp's staging buffer, asynchronously
+__device__ __forceinline__ void prefetch_mb(PredictSmem& S, const PredictArgs& A, size_t mbi, int lane) {
+    if (lane < 25) {
+        const char* src = reinterpret_cast<const char*>(A.levels + mbi * WEBPB200_LEVELS_PER_MB) + lane * 32;
+        char* dst = reinterpret_cast<char*>(S.lv) + lane * 32;
+        cp_async16(dst, src);
+        cp_async16(dst + 16, src + 16);
+    } else if (lane == 25) {
+        cp_async16(&S.desc, A.mbs + mbi);
+    }
+    cp_async_commit();
+}
+
+__global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(PredictArgs A) {
     __shared__ PredictSmem smem[kWarpsPerBlock];
     __shared__ uint32_t s_bpred[160];
     for (int i = threadIdx.x; i < 160; i += kThreads) s_bpred[i] = c_bpred.w[i];
@@ -347,9 +373,20 @@ __global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
         int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
 
+        prefetch_mb(S, A, mb_row0, lane);
         for (int mbx = 0; mbx < mbw; mbx++) {
             const size_t mbi = mb_row0 + mbx;
-            const uint4 mbw4 = __ldg(reinterpret_cast<const uint4*>(A.mbs + mbi));
+            cp_async_wait_all();
+            __syncwarp();
+            const uint4 mbw4 = S.desc;
+            uint4 lv_lo = make_uint4(0, 0, 0, 0), lv_hi = lv_lo;
+            if (lane < 25) {
+                const uint4* lp = reinterpret_cast<const uint4*>(S.lv + lane * 16);
+                lv_lo = lp[0];
+                lv_hi = lp[1];
+            }
+            __syncwarp();
+            if (mbx + 1 < mbw) prefetch_mb(S, A, mbi + 1, lane);
             const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff, segment = (mbw4.x >> 16) & 3;
             const bool skipped = (mbw4.x >> 24) & 1;
             const uint32_t nflags = mbw4.y;
@@ -360,12 +397,8 @@ __global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
             bool nzdct = false;
             if (!skipped) {
                 int c[16];
-                if (lane < 25) {
-                    const uint4* lp = reinterpret_cast<const uint4*>(A.levels + mbi * WEBPB200_LEVELS_PER_MB + lane * 16);
-                    const uint4 lo = __ldg(lp), hi = __ldg(lp + 1);
-                    unpack8(lo, c);
-                    unpack8(hi, c + 8);
-                }
+                unpack8(lv_lo, c);
+                unpack8(lv_hi, c + 8);
                 const webpb200_segment* sg = fd->seg + segment;
                 if (ymode != 4) {
                     if (lane == 24) {
@@ -450,31 +483,32 @@ __global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
             if (ymode == 4) {
                 // predict_4x4 (prediction.rs:159-183) as a 10-step sx + 2*sy wavefront over the
                 // 16 sub-blocks; half-warp h works on sub-block row sy_lo + h, one lane per pixel
-                const int half = lane >> 4, p = lane & 15, px = p & 3, py = p >> 2;
-                const unsigned hmask = half ? 0xffff0000u : 0x0000ffffu;
-#pragma unroll 1
+                const int half = lane >> 4, p = lane & 15;
+                const int pix = (p >> 2) * 32 + (p & 3);                            // my pixel inside a sub-block
+                const int dcoff = (p & 4) ? (p & 3) * 32 - 1 : (p & 3) - 32;       // the edge pixel I add up for B_DC
+                const unsigned long long bp = ((unsigned long long)bpred_hi << 32) | bpred_lo;
+#pragma unroll
                 for (int s = 0; s < 10; s++) {
-                    const int sy_lo = max(0, (s - 2) >> 1), sy_hi = min(3, s >> 1);
-                    const int sy = sy_lo + half, sx = s - 2 * sy;
-                    if (sy <= sy_hi) {
-                        const int sb = sy * 4 + sx;
-                        const int mode = ((sb < 8 ? bpred_lo : bpred_hi) >> (4 * (sb & 7))) & 15;
-                        const int org = (1 + 4 * sy) * 32 + 4 + 4 * sx;
-                        int pred;
-                        if (mode == 0) {  // predict_bdcpred, prediction.rs:271-288
-                            const int off = (p & 4) ? org + (p & 3) * 32 - 1 : org - 32 + (p & 3);
-                            const int sum = __reduce_add_sync(hmask, (unsigned)S.yw[off]);  // each edge pixel twice
-                            pred = (sum + 8) >> 4;
-                        } else {
-                            const uint32_t w = s_bpred[mode * 16 + p];
-                            const int a = S.yw[org + (int)(int8_t)(w & 0xff)];
-                            const int b = S.yw[org + (int)(int8_t)((w >> 8) & 0xff)];
-                            const int cc = S.yw[org + (int)(int8_t)((w >> 16) & 0xff)];
-                            pred = (w >> 24) ? clamp255(a + b - cc) : (a + 2 * b + cc + 2) >> 2;
-                        }
-                        const int r = S.res[sb * 16 + p];
-                        S.yw[org + py * 32 + px] = (uint8_t)clamp255(pred + r);  // add_residue
-                    }
+                    // steps with a single sub-block (0, 1, 8, 9): both half-warps compute it and store
+                    // the same bytes, which keeps the step free of divergence
+                    const int sy_lo = s < 2 ? 0 : (s - 2) >> 1, sy_hi = (s >> 1) < 3 ? (s >> 1) : 3;
+                    const int sy = sy_hi > sy_lo ? sy_lo + half : sy_lo, sx = s - 2 * sy;
+                    const int sb = sy * 4 + sx;
+                    const int mode = (int)(bp >> (4 * sb)) & 15;
+                    const int org = (1 + 4 * sy) * 32 + 4 + 4 * sx;
+                    // B_DC, predict_bdcpred prediction.rs:271-288: lanes p and p^8 hold the same edge pixel
+                    int dc = S.yw[org + dcoff];
+                    dc += __shfl_xor_sync(kFull, dc, 1);
+                    dc += __shfl_xor_sync(kFull, dc, 2);
+                    dc += __shfl_xor_sync(kFull, dc, 4);
+                    const uint32_t w = s_bpred[mode * 16 + p];
+                    const int a = S.yw[org + (int)(int8_t)(w & 0xff)];
+                    const int b = S.yw[org + (int)(int8_t)((w >> 8) & 0xff)];
+                    const int cc = S.yw[org + (int)(int8_t)((w >> 16) & 0xff)];
+                    int pred = (w >> 24) ? clamp255(a + b - cc) : (a + 2 * b + cc + 2) >> 2;
+                    if (mode == 0) pred = (dc + 4) >> 3;
+                    const int r = S.res[sb * 16 + p];
+                    S.yw[org + pix] = (uint8_t)clamp255(pred + r);  // add_residue
                     __syncwarp();
                 }
             } else {
@@ -567,7 +601,8 @@ __global__ void __launch_bounds__(kThreads) k_predict(PredictArgs A) {
             if (lane < 16) S.yw[(1 + lane) * 32 + 3] = S.yw[(1 + lane) * 32 + 19];
             else if (lane < 24) S.uw[(1 + lane - 16) * 16 + 3] = S.uw[(1 + lane - 16) * 16 + 11];
             else S.vw[(1 + lane - 24) * 16 + 3] = S.vw[(1 + lane - 24) * 16 + 11];
-            publish_row(prog_mine, mbx + 1, lane);
+            if (mbx + 1 == mbw || (mbx + 1) % A.publish_every == 0) publish_row(prog_mine, mbx + 1, lane);
+            else __syncwarp();
         }
     }
 }
@@ -1085,6 +1120,9 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
+    // many images: the row above is usually long finished, so publish progress (a release fence each
+    // time) only every 4th macroblock; few images: rows really wait on each other, publish every one
+    a.publish_every = b.n_frames >= 64 ? 4 : 1;
     static int blocks = 0;
     if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_predict), kThreads, b.sm_count);
     int grid = blocks;
