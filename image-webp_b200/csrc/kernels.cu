@@ -659,13 +659,15 @@ __device__ __forceinline__ void lf_line(uint8_t* p, int st, int kind, int edge_l
     }
 }
 
-// Per-warp tile: luma rows -4..15 x columns -4..15 of the macroblock (20 x 20, stride 20),
-// chroma 12 x 12 (stride 12) per plane.  The 4 left columns are carried over from the previous
-// macroblock of the row (they are written back one iteration late, after this macroblock's left
-// edge has been filtered); the 4 top rows belong to the row above and are re-read from L2.
+// Per-warp tile: luma rows -4..15 of the macroblock row, two 16-column panels side by side
+// (32-byte rows): the previous macroblock of the row on the left, the current one on the right.
+// Chroma: 12 rows, two 8-column panels (16-byte rows), per plane.  The previous panel is written
+// back (one 16-byte store per row) only after the current macroblock's left edge has been filtered,
+// then the current panel slides left.  The 4 top rows belong to the row above and are re-read
+// from L2 (they were written by the warp that owns that row).
 struct __align__(16) FilterSmem {
-    uint8_t y[20 * 20];
-    uint8_t c[2][12 * 12];
+    uint8_t y[20 * 32];
+    uint8_t c[2][12 * 16];
 };
 
 struct FilterArgs {
@@ -679,13 +681,17 @@ struct FilterArgs {
     const uint32_t* order;
     const uint8_t* mbinfo;
     uint32_t total_rows;
+    int publish_every;
 };
 
-__global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
+#ifndef FILTER_MIN_BLOCKS
+#define FILTER_MIN_BLOCKS 4
+#endif
+
+__global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(FilterArgs A) {
     __shared__ FilterSmem smem[kWarpsPerBlock];
     const int lane = threadIdx.x & 31;
     FilterSmem& S = smem[threadIdx.x >> 5];
-    uint32_t* y32 = reinterpret_cast<uint32_t*>(S.y);
 
     for (;;) {
         unsigned int t = 0;
@@ -703,9 +709,6 @@ __global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
         const int mbw = fd->mbw;
         const int mby = (int)(rid - fd->row_base);
         const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
-        uint8_t* Y = A.planes + fd->y_off;
-        uint8_t* const CPu = A.planes + fd->u_off;
-        uint8_t* const CPv = A.planes + fd->v_off;
         const int* prog_above = A.progress + rid - 1;
         int* prog_mine = A.progress + rid;
         int seen = 0;
@@ -713,25 +716,22 @@ __global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
         const bool simple = fd->filter_type != 0;
         const int sharp = fd->sharpness;
         const int row_lo = mby > 0 ? 0 : 4;  // tile rows that exist in the plane
+        // my row of the tile in the planes: lanes 0..19 luma rows, lanes 0..23 chroma (plane, row)
+        uint8_t* const yrow = A.planes + fd->y_off + (size_t)(mby * 16 - 4 + lane) * ystride;
+        const int cpl = lane >= 12, crow = lane - 12 * cpl;
+        uint8_t* const crow_ptr = A.planes + (cpl ? fd->v_off : fd->u_off) + (size_t)(mby * 8 - 4 + crow) * cstride;
+        const bool ylane = lane < 20 && lane >= row_lo;
+        const bool clane = !simple && lane < 24 && crow >= row_lo;
+        uint4* const ytile = reinterpret_cast<uint4*>(S.y + lane * 32);            // [0] previous, [1] current panel
+        uint2* const ctile = reinterpret_cast<uint2*>(S.c[cpl] + crow * 16);
 
         for (int mbx = 0; mbx < mbw; mbx++) {
             const size_t mbi = mb_row0 + mbx;
             if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
 
-            // ---- load the 16 new columns (rows -4..15) ----
-            if (lane < 20 && lane >= row_lo) {
-                const uint4 v = ld_cg_u128(Y + (size_t)(mby * 16 - 4 + lane) * ystride + (size_t)mbx * 16);
-                uint32_t* d = y32 + lane * 5 + 1;
-                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-            }
-            if (!simple && lane < 24) {
-                const int pl = lane / 12, r = lane % 12;
-                if (r >= row_lo) {
-                    const uint2 v = ld_cg_u64((pl ? CPv : CPu) + (size_t)(mby * 8 - 4 + r) * cstride + (size_t)mbx * 8);
-                    uint32_t* d = reinterpret_cast<uint32_t*>(S.c[pl]) + r * 3 + 1;
-                    d[0] = v.x; d[1] = v.y;
-                }
-            }
+            // ---- load the 16 new columns (rows -4..15) into the current panel ----
+            if (ylane) ytile[1] = ld_cg_u128(yrow + (size_t)mbx * 16);
+            if (clane) ctile[1] = ld_cg_u64(crow_ptr + (size_t)mbx * 8);
 
             // ---- calculate_filter_parameters, mod.rs:1191-1244 ----
             const uint32_t mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mbi));
@@ -761,73 +761,62 @@ __global__ void __launch_bounds__(kThreads) k_loopfilter(FilterArgs A) {
 
             // ---- loop_filter, mod.rs:966-1188: four edge groups in the reference's order ----
             if (level > 0) {
+                uint8_t* const y0 = S.y + 4 * 32 + 16;  // pixel (0, 0) of the current macroblock
                 if (simple) {
                     // the simple filter reads 4 and writes 2 pixels per line, so the parallel
                     // edges of one direction do not touch each other's pixels: do them together
-                    for (int k = lane; k < 64; k += 32) {  // vertical edges x = 0, 4, 8, 12
-                        const int e = k >> 4, r = k & 15;
-                        if (e == 0 ? mbx > 0 : do_sub) lf_line(S.y + (4 + r) * 20 + 4 + 4 * e, 1, 0, e == 0 ? mbedge : subedge, 0, 0);
-                    }
+                    const int r = lane & 15, e0 = (lane >> 4) * 2;  // my line, my two edges (e0, e0 + 1)
+                    if (e0 == 0 ? mbx > 0 : do_sub) lf_line(y0 + r * 32 + 4 * e0, 1, 0, e0 == 0 ? mbedge : subedge, 0, 0);
+                    if (do_sub) lf_line(y0 + r * 32 + 4 * e0 + 4, 1, 0, subedge, 0, 0);
                     __syncwarp();
-                    for (int k = lane; k < 64; k += 32) {  // horizontal edges y = 0, 4, 8, 12
-                        const int e = k >> 4, cidx = k & 15;
-                        if (e == 0 ? mby > 0 : do_sub) lf_line(S.y + (4 + 4 * e) * 20 + 4 + cidx, 20, 0, e == 0 ? mbedge : subedge, 0, 0);
-                    }
+                    if (e0 == 0 ? mby > 0 : do_sub) lf_line(y0 + (4 * e0) * 32 + r, 32, 0, e0 == 0 ? mbedge : subedge, 0, 0);
+                    if (do_sub) lf_line(y0 + (4 * e0 + 4) * 32 + r, 32, 0, subedge, 0, 0);
                     __syncwarp();
                 } else {
                     // lanes 0..15: luma lines; 16..23: U lines; 24..31: V lines
                     uint8_t* base;
-                    int st_row, st_col, idx;
-                    if (lane < 16) { base = S.y + 4 * 20 + 4; st_row = 20; st_col = 1; idx = lane; }
-                    else { base = S.c[(lane - 16) >> 3] + 4 * 12 + 4; st_row = 12; st_col = 1; idx = (lane - 16) & 7; }
-                    if (mbx > 0) lf_line(base + idx * st_row, st_col, 2, mbedge, interior, hev_thr);
+                    int st_row, idx;
+                    if (lane < 16) { base = y0; st_row = 32; idx = lane; }
+                    else { base = S.c[(lane - 16) >> 3] + 4 * 16 + 8; st_row = 16; idx = (lane - 16) & 7; }
+                    if (mbx > 0) lf_line(base + idx * st_row, 1, 2, mbedge, interior, hev_thr);
                     __syncwarp();
                     if (do_sub) {
-                        lf_line(base + idx * st_row + 4 * st_col, st_col, 1, subedge, interior, hev_thr);
+                        lf_line(base + idx * st_row + 4, 1, 1, subedge, interior, hev_thr);
                         __syncwarp();
                         if (lane < 16) lf_line(base + idx * st_row + 8, 1, 1, subedge, interior, hev_thr);
                         __syncwarp();
                         if (lane < 16) lf_line(base + idx * st_row + 12, 1, 1, subedge, interior, hev_thr);
                         __syncwarp();
                     }
-                    if (mby > 0) lf_line(base + idx * st_col, st_row, 2, mbedge, interior, hev_thr);
+                    if (mby > 0) lf_line(base + idx, st_row, 2, mbedge, interior, hev_thr);
                     __syncwarp();
                     if (do_sub) {
-                        lf_line(base + idx * st_col + 4 * st_row, st_row, 1, subedge, interior, hev_thr);
+                        lf_line(base + idx + 4 * st_row, st_row, 1, subedge, interior, hev_thr);
                         __syncwarp();
-                        if (lane < 16) lf_line(base + idx + 8 * 20, 20, 1, subedge, interior, hev_thr);
+                        if (lane < 16) lf_line(base + idx + 8 * 32, 32, 1, subedge, interior, hev_thr);
                         __syncwarp();
-                        if (lane < 16) lf_line(base + idx + 12 * 20, 20, 1, subedge, interior, hev_thr);
+                        if (lane < 16) lf_line(base + idx + 12 * 32, 32, 1, subedge, interior, hev_thr);
                         __syncwarp();
                     }
                 }
             }
 
-            // ---- write back columns -4..11 (and 12..15 on the last macroblock) ----
+            // ---- the previous macroblock is final now: write it back, slide the current one left ----
             const bool last = mbx == mbw - 1;
-            const int wlo = mbx > 0 ? 0 : 1, whi = last ? 5 : 4;  // word columns of the tile row
-            for (int k = lane; k < 100; k += 32) {
-                const int r = k / 5, wc = k % 5;
-                if (r >= row_lo && wc >= wlo && wc < whi)
-                    *reinterpret_cast<uint32_t*>(Y + (size_t)(mby * 16 - 4 + r) * ystride + (size_t)mbx * 16 - 4 + 4 * wc) = y32[r * 5 + wc];
+            if (ylane) {
+                const uint4 cur = ytile[1];
+                if (mbx > 0) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16 - 16) = ytile[0];
+                if (last) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16) = cur;
+                ytile[0] = cur;
             }
-            if (!simple) {
-                const int cwhi = last ? 3 : 2;
-                for (int k = lane; k < 72; k += 32) {
-                    const int pl = k / 36, r = (k % 36) / 3, wc = k % 3;
-                    if (r >= row_lo && wc >= wlo && wc < cwhi)
-                        *reinterpret_cast<uint32_t*>((pl ? CPv : CPu) + (size_t)(mby * 8 - 4 + r) * cstride + (size_t)mbx * 8 - 4 + 4 * wc) =
-                            reinterpret_cast<uint32_t*>(S.c[pl])[r * 3 + wc];
-                }
+            if (clane) {
+                const uint2 cur = ctile[1];
+                if (mbx > 0) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8 - 8) = ctile[0];
+                if (last) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8) = cur;
+                ctile[0] = cur;
             }
-            __syncwarp();
-            // ---- carry the 4 right columns over as the next macroblock's left strip ----
-            if (lane < 20) y32[lane * 5] = y32[lane * 5 + 4];
-            if (!simple && lane < 24) {
-                uint32_t* c32 = reinterpret_cast<uint32_t*>(S.c[lane / 12]);
-                c32[(lane % 12) * 3] = c32[(lane % 12) * 3 + 2];
-            }
-            publish_row(prog_mine, mbx + 1, lane);
+            if (last || (mbx + 1) % A.publish_every == 0) publish_row(prog_mine, mbx + 1, lane);
+            else __syncwarp();
         }
     }
 }
@@ -1143,6 +1132,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
+    a.publish_every = b.n_frames >= 64 ? 4 : 1;
     static int blocks = 0;
     if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_loopfilter), kThreads, b.sm_count);
     int grid = blocks;
