@@ -822,16 +822,18 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
 }
 
 // ---------------------------------------------------------------------------------------------
-// k_yuv2rgb: one thread = 4 horizontally adjacent pixels of one row
+// k_yuv2rgb: one thread = 8 horizontally adjacent pixels of the two rows (2q-1, 2q) that share
+// their pair of chroma rows (q = 0: row 0 alone)
 // ---------------------------------------------------------------------------------------------
 // yuv.rs:30-71
 __device__ __forceinline__ int mulhi8(int v, int coeff) { return (v * coeff) >> 8; }
 __device__ __forceinline__ int clip6(int v) { return min(max(v >> 6, 0), 255); }
-__device__ __forceinline__ void yuv_to_rgb(int y, int u, int v, int& r, int& g, int& b) {
+__device__ __forceinline__ uint32_t yuv_to_rgb(int y, int u, int v) {  // r | g << 8 | b << 16
     const int yy = mulhi8(y, 19077);
-    r = clip6(yy + mulhi8(v, 26149) - 14234);
-    g = clip6(yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708);
-    b = clip6(yy + mulhi8(u, 33050) - 17685);
+    const int r = clip6(yy + mulhi8(v, 26149) - 14234);
+    const int g = clip6(yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708);
+    const int b = clip6(yy + mulhi8(u, 33050) - 17685);
+    return (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16);
 }
 
 struct RgbArgs {
@@ -840,74 +842,118 @@ struct RgbArgs {
     uint8_t* out;
 };
 
+// Horizontal half of the fancy upsampler for 8 pixels of one chroma row.  c[0..5] are the chroma
+// samples at columns 4k-1 .. 4k+4 (clamped to the visible chroma width, which is how yuv.rs:163-170
+// and 204-219 treat the first and last pixel).  Pixel i uses main column cm and second column cs
+// (cm, cs = same, left / same, right alternating); h[i] = 3*c[cm] + c[cs] + 2, so that
+// (3*h_main + h_second) >> 4 == (9*a + 3*b + 3*c + d + 8) >> 4 of yuv.rs:276-282.
+__device__ __forceinline__ void chroma_row8(const uint8_t* row, int k4, int lim, int* h) {
+    const uint32_t wd = __ldg(reinterpret_cast<const uint32_t*>(row + k4));
+    int c[6];
+    c[0] = __ldg(row + max(k4 - 1, 0));
+    c[1] = wd & 0xff; c[2] = (wd >> 8) & 0xff; c[3] = (wd >> 16) & 0xff; c[4] = wd >> 24;
+    c[5] = __ldg(row + k4 + min(4, lim));
+    if (lim < 3) {  // the row's last thread: columns past the visible width repeat the last one
+        if (lim < 1) c[2] = c[1];
+        if (lim < 2) c[3] = c[2];
+        c[4] = c[3];
+    }
+    h[0] = 3 * c[1] + c[0] + 2; h[1] = 3 * c[1] + c[2] + 2;
+    h[2] = 3 * c[2] + c[1] + 2; h[3] = 3 * c[2] + c[3] + 2;
+    h[4] = 3 * c[3] + c[2] + 2; h[5] = 3 * c[3] + c[4] + 2;
+    h[6] = 3 * c[4] + c[3] + 2; h[7] = 3 * c[4] + c[5] + 2;
+}
+
+// 8 pixels -> tightly packed RGB8 / RGBA8 (yuv.rs:285-289; byte 3 of RGBA belongs to the ALPH merge
+// that always follows, decoder.rs:704-734: 255 until then)
+__device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int n, int bpp) {
+    if (bpp == 4) {
+        if (n == 8 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+            uint4* o = reinterpret_cast<uint4*>(out);
+            o[0] = make_uint4(px[0] | 0xff000000u, px[1] | 0xff000000u, px[2] | 0xff000000u, px[3] | 0xff000000u);
+            o[1] = make_uint4(px[4] | 0xff000000u, px[5] | 0xff000000u, px[6] | 0xff000000u, px[7] | 0xff000000u);
+        } else {
+            for (int i = 0; i < n; i++) reinterpret_cast<uint32_t*>(out)[i] = px[i] | 0xff000000u;
+        }
+        return;
+    }
+    if (n == 8 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+        uint32_t wv[6];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const uint32_t a = px[4 * j], b = px[4 * j + 1], c = px[4 * j + 2], d = px[4 * j + 3];
+            wv[3 * j] = a | (b << 24);
+            wv[3 * j + 1] = (b >> 8) | (c << 16);
+            wv[3 * j + 2] = (c >> 16) | (d << 8);
+        }
+        if ((reinterpret_cast<uintptr_t>(out) & 7) == 0) {
+            uint2* o = reinterpret_cast<uint2*>(out);
+            o[0] = make_uint2(wv[0], wv[1]); o[1] = make_uint2(wv[2], wv[3]); o[2] = make_uint2(wv[4], wv[5]);
+        } else {
+            uint32_t* o = reinterpret_cast<uint32_t*>(out);
+#pragma unroll
+            for (int j = 0; j < 6; j++) o[j] = wv[j];
+        }
+    } else {
+        for (int i = 0; i < n; i++) { out[3 * i] = (uint8_t)px[i]; out[3 * i + 1] = (uint8_t)(px[i] >> 8); out[3 * i + 2] = (uint8_t)(px[i] >> 16); }
+    }
+}
+
 __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
     const webpb200_frame_desc* fd = A.frames + blockIdx.z;
     const int w = fd->width, h = fd->height;
-    const int y = blockIdx.y;
-    const int x0 = (blockIdx.x * 128 + threadIdx.x) * 4;
-    if (y >= h || x0 >= w) return;
+    const int q = blockIdx.y * 2 + threadIdx.y;
+    const int x0 = (blockIdx.x * 64 + threadIdx.x) * 8;
+    const int ya = q == 0 ? 0 : 2 * q - 1, yb = 2 * q;
+    if (x0 >= w || ya >= h) return;
+    const bool has_b = q > 0 && yb < h;
     const int ystride = fd->mbw * 16, cstride = fd->mbw * 8;
-    const uint8_t* Y = A.planes + fd->y_off + (size_t)y * ystride;
-    const uint8_t* U = A.planes + fd->u_off;
-    const uint8_t* V = A.planes + fd->v_off;
     const int bpp = fd->out_bpp;
-    uint8_t* out = A.out + fd->out_off + ((size_t)y * w + x0) * bpp;
-    const uint32_t yw = __ldg(reinterpret_cast<const uint32_t*>(Y + x0));
-    const int n = min(4, w - x0);
-    int uu[4], vv[4];
+    const int n = min(8, w - x0);
+    const int k4 = x0 >> 1;  // first chroma column of this thread
+    const uint8_t* Y = A.planes + fd->y_off + x0;
+    const uint2 ywa = __ldg(reinterpret_cast<const uint2*>(Y + (size_t)ya * ystride));
+    uint2 ywb = make_uint2(0, 0);
+    if (has_b) ywb = __ldg(reinterpret_cast<const uint2*>(Y + (size_t)yb * ystride));
+    int ua[8], va[8], ub[8], vb[8];
     if (fd->upsampling == WEBPB200_UPSAMPLING_SIMPLE) {  // fill_rgb_buffer_simple, yuv.rs:293-382
-        const uint8_t* ur = U + (size_t)(y >> 1) * cstride + (x0 >> 1);
-        const uint8_t* vr = V + (size_t)(y >> 1) * cstride + (x0 >> 1);
-        uu[0] = uu[1] = ur[0]; uu[2] = uu[3] = ur[1];
-        vv[0] = vv[1] = vr[0]; vv[2] = vv[3] = vr[1];
-    } else {
-        // fill_rgb_buffer_fancy, yuv.rs:76-282, as a per-pixel rule: main chroma row rm and
-        // second row rs; main column cm and second column cs; 9:3:3:1 blend
-        int rm, rs;
-        if (y == 0) { rm = 0; rs = 0; }
-        else if (y & 1) { rm = (y - 1) >> 1; rs = rm + 1; }
-        else { rm = y >> 1; rs = rm - 1; }
-        if (y == h - 1 && !(h & 1)) rs = rm;
-        const uint8_t* um = U + (size_t)rm * cstride; const uint8_t* us = U + (size_t)rs * cstride;
-        const uint8_t* vm = V + (size_t)rm * cstride; const uint8_t* vs = V + (size_t)rs * cstride;
+        const uint32_t u0 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->u_off + (size_t)(ya >> 1) * cstride + k4));
+        const uint32_t v0 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->v_off + (size_t)(ya >> 1) * cstride + k4));
+        const int rb = min(yb >> 1, ((h + 1) >> 1) - 1);  // row 2q may not exist: stay inside the plane
+        const uint32_t u1 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->u_off + (size_t)rb * cstride + k4));
+        const uint32_t v1 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->v_off + (size_t)rb * cstride + k4));
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int x = x0 + i;
-            int cm, cs;
-            if (x == 0) { cm = 0; cs = 0; }
-            else if (x & 1) { cm = (x - 1) >> 1; cs = cm + 1; }
-            else { cm = x >> 1; cs = cm - 1; }
-            if (x == w - 1 && !(w & 1)) cs = cm;
-            if (i < n) {
-                uu[i] = (9 * um[cm] + 3 * um[cs] + 3 * us[cm] + us[cs] + 8) >> 4;
-                vv[i] = (9 * vm[cm] + 3 * vm[cs] + 3 * vs[cm] + vs[cs] + 8) >> 4;
-            } else { uu[i] = 0; vv[i] = 0; }
+        for (int i = 0; i < 8; i++) {
+            ua[i] = (u0 >> (8 * (i >> 1))) & 0xff; va[i] = (v0 >> (8 * (i >> 1))) & 0xff;
+            ub[i] = (u1 >> (8 * (i >> 1))) & 0xff; vb[i] = (v1 >> (8 * (i >> 1))) & 0xff;
         }
+    } else {
+        // fill_rgb_buffer_fancy, yuv.rs:76-282.  Row 2q-1 takes chroma row q-1 as main and q as second,
+        // row 2q the other way round; row 0 and an even-height image's last row use one chroma row
+        // for both (yuv.rs:94, 137-151) -- which the clamp of the second row's index gives.
+        const int cw = (w + 1) >> 1, chh = (h + 1) >> 1;
+        const int ca = q == 0 ? 0 : q - 1, cb = min(q, chh - 1);
+        const int lim = cw - 1 - k4;  // last visible chroma column relative to k4
+        int ha[8], hb[8];
+        const uint8_t* U = A.planes + fd->u_off;
+        chroma_row8(U + (size_t)ca * cstride, k4, lim, ha);
+        chroma_row8(U + (size_t)cb * cstride, k4, lim, hb);
+#pragma unroll
+        for (int i = 0; i < 8; i++) { ua[i] = (3 * ha[i] + hb[i]) >> 4; ub[i] = (3 * hb[i] + ha[i]) >> 4; }
+        const uint8_t* V = A.planes + fd->v_off;
+        chroma_row8(V + (size_t)ca * cstride, k4, lim, ha);
+        chroma_row8(V + (size_t)cb * cstride, k4, lim, hb);
+#pragma unroll
+        for (int i = 0; i < 8; i++) { va[i] = (3 * ha[i] + hb[i]) >> 4; vb[i] = (3 * hb[i] + ha[i]) >> 4; }
     }
-    int r[4], g[4], b[4];
+    uint32_t px[8];
 #pragma unroll
-    for (int i = 0; i < 4; i++) yuv_to_rgb((yw >> (8 * i)) & 0xff, uu[i], vv[i], r[i], g[i], b[i]);
-    if (bpp == 4) {
-        // byte 3 is the ALPH merge's (yuv.rs:285-289 leaves it alone; decoder.rs:704-734
-        // always fills it afterwards); 255 until then
-        if (n == 4) {
-            uint4 o;
-            o.x = r[0] | (g[0] << 8) | (b[0] << 16) | 0xff000000u; o.y = r[1] | (g[1] << 8) | (b[1] << 16) | 0xff000000u;
-            o.z = r[2] | (g[2] << 8) | (b[2] << 16) | 0xff000000u; o.w = r[3] | (g[3] << 8) | (b[3] << 16) | 0xff000000u;
-            if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) { *reinterpret_cast<uint4*>(out) = o; }
-            else { uint32_t* o32 = reinterpret_cast<uint32_t*>(out); o32[0] = o.x; o32[1] = o.y; o32[2] = o.z; o32[3] = o.w; }
-        } else {
-            for (int i = 0; i < n; i++) reinterpret_cast<uint32_t*>(out)[i] = r[i] | (g[i] << 8) | (b[i] << 16) | 0xff000000u;
-        }
-    } else {
-        if (n == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
-            uint32_t* o32 = reinterpret_cast<uint32_t*>(out);
-            o32[0] = r[0] | (g[0] << 8) | (b[0] << 16) | (r[1] << 24);
-            o32[1] = g[1] | (b[1] << 8) | (r[2] << 16) | (g[2] << 24);
-            o32[2] = b[2] | (r[3] << 8) | (g[3] << 16) | (b[3] << 24);
-        } else {
-            for (int i = 0; i < n; i++) { out[3 * i] = (uint8_t)r[i]; out[3 * i + 1] = (uint8_t)g[i]; out[3 * i + 2] = (uint8_t)b[i]; }
-        }
+    for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(((i < 4 ? ywa.x : ywa.y) >> (8 * (i & 3))) & 0xff, ua[i], va[i]);
+    store_row8(A.out + fd->out_off + ((size_t)ya * w + x0) * bpp, px, n, bpp);
+    if (has_b) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(((i < 4 ? ywb.x : ywb.y) >> (8 * (i & 3))) & 0xff, ub[i], vb[i]);
+        store_row8(A.out + fd->out_off + ((size_t)yb * w + x0) * bpp, px, n, bpp);
     }
 }
 
@@ -1146,8 +1192,9 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
 cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
     RgbArgs a;
     a.frames = b.frames; a.planes = b.planes; a.out = b.out;
-    dim3 grid((b.max_w + 511) / 512, b.max_h, b.n_frames);
-    k_yuv2rgb<<<grid, 128, 0, s>>>(a);
+    // thread = 8 pixels x 2 rows; block = 64 x 2 threads = 512 pixels x 4 rows; row pairs: h/2 + 1
+    dim3 grid((b.max_w + 511) / 512, (b.max_h / 2 + 1 + 1) / 2, b.n_frames);
+    k_yuv2rgb<<<grid, dim3(64, 2), 0, s>>>(a);
     return cudaGetLastError();
 }
 
