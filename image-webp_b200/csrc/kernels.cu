@@ -226,9 +226,12 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // Inverse transforms (one lane = one 4x4 block, values in registers)
 // ---------------------------------------------------------------------------------------------
-// transform.rs:1-4, 20-25: MUL2(x) = (x*35468)>>16, MUL1(x) = x + ((x*20091)>>16), 64-bit products
-__device__ __forceinline__ int mul_c2(int x) { return (int)(((long long)x * 35468LL) >> 16); }
-__device__ __forceinline__ int mul_c1(int x) { return x + (int)(((long long)x * 20091LL) >> 16); }
+// transform.rs:1-4, 20-25: MUL2(x) = (x*35468)>>16 and MUL1(x) = x + ((x*20091)>>16) with 64-bit
+// products.  As high halves of 32x32 products: (x*20091)>>16 = mulhi(x, 20091<<16), and because
+// 35468<<16 does not fit a signed word, (x*35468)>>16 = mulhi(x, (35468<<16) - 2^32) + x.  Exact
+// for every int32 x (floor((x*K)/2^32) with K a multiple of 2^16).
+__device__ __forceinline__ int mul_c2(int x) { return __mulhi(x, (int)0x8A8C0000u) + x; }
+__device__ __forceinline__ int mul_c1(int x) { return __mulhi(x, 0x4E7B0000) + x; }
 
 // transform.rs:7-51.  Vertical pass first (no rounding), then rows with (x + 4) >> 3.  Sums stay
 // far inside int32 for every level the bitstream can carry (|level| <= 2114, quantisers <= 440);
@@ -306,7 +309,7 @@ struct __align__(16) PredictSmem {
     uint8_t vw[9 * 16];
     int16_t res[24 * 16];  // residuals of the 24 blocks, raster inside a block
     int32_t wht[16];
-    int16_t lv[WEBPB200_LEVELS_PER_MB];  // next macroblock's levels, prefetched with cp.async
+    int16_t lv[32 * 16];                 // next macroblock's levels (25 x 16 used), prefetched with cp.async
     uint4 desc;                          // and its descriptor
 };
 
@@ -322,7 +325,7 @@ struct PredictArgs {
     const uint32_t* order;
     uint8_t* mbinfo;
     uint32_t total_rows;
-    int publish_every;  // progress is published every this many macroblocks (and at the row end)
+    int publish_every;  // progress is published every this many macroblocks (a power of two) and at the row end
 };
 
 #ifndef PREDICT_MIN_BLOCKS
@@ -353,6 +356,14 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
     uint32_t* yw32 = reinterpret_cast<uint32_t*>(S.yw);
     uint32_t* uw32 = reinterpret_cast<uint32_t*>(S.uw);
     uint32_t* vw32 = reinterpret_cast<uint32_t*>(S.vw);
+    // border roles, fixed per lane.  Lanes 0..11 each fetch one word of the row above: 0 = the word
+    // ending in the luma corner, 1..4 = the 16 pixels above, 5 = above-right, 6..8 = U (corner word,
+    // 8 pixels), 9..11 = V.  Every lane moves one byte of the right column to the left border.
+    const int trole = lane < 6 ? lane : (lane - 6) % 3;            // position inside its plane's group
+    const bool tcorner = lane < 12 && trole == 0;
+    uint32_t* const top_dst = lane < 6 ? yw32 + lane : lane < 9 ? uw32 + (lane - 6) : vw32 + (lane - 9);
+    uint8_t* const lb_dst = lane < 16 ? S.yw + (1 + lane) * 32 + 3 : lane < 24 ? S.uw + (lane - 15) * 16 + 3 : S.vw + (lane - 23) * 16 + 3;
+    const int lb_gap = lane < 16 ? 16 : 8;  // right column = left border + gap
 
     for (;;) {
         unsigned int t = 0;
@@ -372,6 +383,12 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         int* prog_mine = A.progress + rid;
         int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
+        // where my border word of macroblock 0 lives in the row above, and what my pixels go to
+        const uint8_t* top_ptr = lane < 6 ? Y + (size_t)(mby * 16 - 1) * ystride + 4 * (lane - 1)
+                                          : (lane < 9 ? U : V) + (size_t)(mby * 8 - 1) * cstride + 4 * (trole - 1);
+        const int top_step = lane < 6 ? 16 : 8;
+        uint8_t* const yout = Y + (size_t)(mby * 16 + (lane >> 1)) * ystride + (lane & 1) * 8;
+        uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
 
         prefetch_mb(S, A, mb_row0, lane);
         for (int mbx = 0; mbx < mbw; mbx++) {
@@ -379,12 +396,8 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
             cp_async_wait_all();
             __syncwarp();
             const uint4 mbw4 = S.desc;
-            uint4 lv_lo = make_uint4(0, 0, 0, 0), lv_hi = lv_lo;
-            if (lane < 25) {
-                const uint4* lp = reinterpret_cast<const uint4*>(S.lv + lane * 16);
-                lv_lo = lp[0];
-                lv_hi = lp[1];
-            }
+            const uint4* lp = reinterpret_cast<const uint4*>(S.lv + lane * 16);  // lanes 25..31 read padding
+            const uint4 lv_lo = lp[0], lv_hi = lp[1];
             __syncwarp();
             if (mbx + 1 < mbw) prefetch_mb(S, A, mbi + 1, lane);
             const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff, segment = (mbw4.x >> 16) & 3;
@@ -448,35 +461,22 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
             // create_border_luma / create_border_chroma, prediction.rs:13-123
             if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
             if (lane < 12) {
-                uint32_t w;
-                if (mby == 0) {
-                    w = 0x7f7f7f7fu;
-                } else if (lane < 6) {
-                    const uint8_t* row = Y + (size_t)(mby * 16 - 1) * ystride + (size_t)mbx * 16;
-                    if (lane == 0) w = mbx > 0 ? ld_cg_u32(row - 4) : 0x81818181u;
-                    else if (lane < 5) w = ld_cg_u32(row + 4 * (lane - 1));
-                    else w = mbx < mbw - 1 ? ld_cg_u32(row + 16) : (ld_cg_u32(row + 12) >> 24) * 0x01010101u;
-                } else {
-                    const int k = lane - 6;  // 0..2 U, 3..5 V
-                    const uint8_t* row = (k < 3 ? U : V) + (size_t)(mby * 8 - 1) * cstride + (size_t)mbx * 8;
-                    const int j = k % 3;
-                    if (j == 0) w = mbx > 0 ? ld_cg_u32(row - 4) : 0x81818181u;
-                    else w = ld_cg_u32(row + 4 * (j - 1));
+                uint32_t w = 0x7f7f7f7fu;  // first macroblock row: 127 everywhere, corner included
+                if (mby > 0) {
+                    const bool last = mbx == mbw - 1;
+                    if (tcorner && mbx == 0) {
+                        w = 0x81818181u;  // no macroblock to the left: corner = 129
+                    } else {
+                        // above-right of the last macroblock: its own last pixel above, four times
+                        const uint32_t v = ld_cg_u32(top_ptr + (lane == 5 && last ? -4 : 0));
+                        w = lane == 5 && last ? (v >> 24) * 0x01010101u : v;
+                    }
                 }
-                if (lane < 6) {
-                    yw32[lane] = w;
-                    if (lane == 5) { yw32[4 * 8 + 5] = w; yw32[8 * 8 + 5] = w; yw32[12 * 8 + 5] = w; }
-                } else if (lane < 9) {
-                    uw32[lane - 6] = w;
-                } else {
-                    vw32[lane - 9] = w;
-                }
+                *top_dst = w;
+                if (lane == 5) { yw32[4 * 8 + 5] = w; yw32[8 * 8 + 5] = w; yw32[12 * 8 + 5] = w; }
             }
-            if (mbx == 0) {  // left border 129 (prediction.rs:54-57, 104-107)
-                if (lane < 16) S.yw[(1 + lane) * 32 + 3] = 129;
-                else if (lane < 24) S.uw[(1 + lane - 16) * 16 + 3] = 129;
-                else S.vw[(1 + lane - 24) * 16 + 3] = 129;
-            }
+            top_ptr += top_step;
+            if (mbx == 0) *lb_dst = 129;  // left border 129 (prediction.rs:54-57, 104-107)
             __syncwarp();
 
             // ---- luma ----
@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 uint2 o;
                 o.x = yw32[(1 + row) * 8 + 1 + (x0 >> 2)];
                 o.y = yw32[(1 + row) * 8 + 2 + (x0 >> 2)];
-                *reinterpret_cast<uint2*>(Y + (size_t)(mby * 16 + row) * ystride + (size_t)mbx * 16 + x0) = o;
+                *reinterpret_cast<uint2*>(yout + (size_t)mbx * 16) = o;
             }
 
             // ---- chroma (intra_predict_chroma, mod.rs:723-783): lane = (plane, row, 4-pixel half)
@@ -593,15 +593,12 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
 #pragma unroll
                 for (int i = 0; i < 4; i++) o |= (uint32_t)clamp255(pr[i] + rr[i]) << (8 * i);
                 cw32[(1 + row) * 4 + 1 + (x0 >> 2)] = o;
-                uint8_t* P = plane ? V : U;
-                *reinterpret_cast<uint32_t*>(P + (size_t)(mby * 8 + row) * cstride + (size_t)mbx * 8 + x0) = o;
+                *reinterpret_cast<uint32_t*>(cout + (size_t)mbx * 8) = o;
             }
             __syncwarp();
             // right column becomes the next macroblock's left border (mod.rs:700-704, 1309-1314)
-            if (lane < 16) S.yw[(1 + lane) * 32 + 3] = S.yw[(1 + lane) * 32 + 19];
-            else if (lane < 24) S.uw[(1 + lane - 16) * 16 + 3] = S.uw[(1 + lane - 16) * 16 + 11];
-            else S.vw[(1 + lane - 24) * 16 + 3] = S.vw[(1 + lane - 24) * 16 + 11];
-            if (mbx + 1 == mbw || (mbx + 1) % A.publish_every == 0) publish_row(prog_mine, mbx + 1, lane);
+            *lb_dst = lb_dst[lb_gap];
+            if (mbx + 1 == mbw || ((mbx + 1) & (A.publish_every - 1)) == 0) publish_row(prog_mine, mbx + 1, lane);
             else __syncwarp();
         }
     }
@@ -815,7 +812,7 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                 if (last) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8) = cur;
                 ctile[0] = cur;
             }
-            if (last || (mbx + 1) % A.publish_every == 0) publish_row(prog_mine, mbx + 1, lane);
+            if (last || ((mbx + 1) & (A.publish_every - 1)) == 0) publish_row(prog_mine, mbx + 1, lane);
             else __syncwarp();
         }
     }
