@@ -6,8 +6,11 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -142,17 +145,20 @@ namespace {
 // image, ...  A row only ever waits for the row above it in the same image, which in this order
 // was handed out a whole batch of rows earlier and is (nearly always) far ahead or finished, so
 // resident warps work instead of waiting.  (Image-major order keeps 2/3 of the warps spinning.)
-void fill_row_order(const webpb200_frame_desc* frames, int n, uint32_t* order) {
+// Frames [i0, i1) only: their rows are contiguous in row-id space, so the order of a chunk of the
+// batch can be written in place at order[row_base(i0) ...].
+void fill_row_order(const webpb200_frame_desc* frames, int i0, int i1, uint32_t* order) {
     uint32_t max_h = 0;
-    for (int i = 0; i < n; i++) max_h = std::max<uint32_t>(max_h, frames[i].mbh);
-    size_t k = 0;
+    for (int i = i0; i < i1; i++) max_h = std::max<uint32_t>(max_h, frames[i].mbh);
+    size_t k = i0 < i1 ? frames[i0].row_base : 0;
     for (uint32_t r = 0; r < max_h; r++)
-        for (int i = 0; i < n; i++)
+        for (int i = i0; i < i1; i++)
             if (frames[i].mbh > r) order[k++] = frames[i].row_base + r;
 }
 
-// Host side of a batch: probe sizes, lay the arenas out, entropy-decode into pinned staging.
-int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
+// Host side of a batch, part 1: probe sizes, lay the arenas out, size the pinned staging, build
+// the row -> image map.  Nothing here depends on the entropy-coded data.
+int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
     cudaSetDevice(c->device);
     c->items = std::move(in_items);
     c->n = (int)c->items.size();
@@ -221,12 +227,27 @@ int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampl
     c->aux_lists_off = c->aux_order_off + (size_t)align256(4 * rows);
     c->aux_bytes = c->aux_lists_off + (size_t)align256(16 * (uint64_t)std::max(n, 1));
     CU(c, c->h_aux.reserve(c->aux_bytes), "pinned aux");
+    uint32_t* rowmap = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
+    for (int i = 0; i < n; i++)
+        for (uint32_t r = 0; r < frames[i].mbh; r++) rowmap[frames[i].row_base + r] = (uint32_t)i;
+    BatchDev& bd = c->bd;
+    std::memset(&bd, 0, sizeof(bd));
+    bd.n_frames = n;
+    bd.total_rows = (uint32_t)rows;
+    bd.max_w = max_w;
+    bd.max_h = max_h;
+    bd.sm_count = c->sm_count;
+    bd.lay = scratch_layout(rows, mbs);
+    return 0;
+}
+
+// Part 2, per image (any host thread): the serial entropy decode into the pinned staging arrays.
+void entropy_one(webpb200_ctx* c, int i) {
+    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     webpb200_mb_desc* hm = reinterpret_cast<webpb200_mb_desc*>(c->h_mbs.p);
     int16_t* hl = reinterpret_cast<int16_t*>(c->h_levels.p);
-
-    // entropy decode (the serial-per-image part) on the host threads
-    parallel_for(n, threads, [&](int i) {
-        WorkItem& it = items[i];
+    {
+        WorkItem& it = c->items[i];
         if (it.status) return;
         webpb200_frame_desc& fd = frames[i];
         const size_t m = (size_t)fd.mbw * fd.mbh;
@@ -252,18 +273,19 @@ int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampl
             fd.filter_level = 0;
             fd.alpha_mode = 0;
         }
-    });
+    }
+}
 
-    // ticket -> image map and the ALPH lists by filter method
-    uint32_t* rowmap = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
-    uint32_t* order = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off);
+// Part 3, after every image is decoded: the ALPH lists by filter method (the filter method is in
+// the ALPH chunk header, so it is only known now).
+void finish_items(webpb200_ctx* c) {
+    const webpb200_frame_desc* frames = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
     int* lists = reinterpret_cast<int*>(c->h_aux.p + c->aux_lists_off);
-    fill_row_order(frames, n, order);
     BatchDev& bd = c->bd;
-    std::memset(&bd, 0, sizeof(bd));
+    const int n = c->n;
+    for (int m = 0; m < 4; m++) bd.alpha_counts[m] = 0, bd.alpha_maxw[m] = 0, bd.alpha_maxh[m] = 0;
     for (int i = 0; i < n; i++) {
         const webpb200_frame_desc& fd = frames[i];
-        for (uint32_t r = 0; r < fd.mbh; r++) rowmap[fd.row_base + r] = (uint32_t)i;
         if (fd.alpha_mode && fd.out_bpp == 4) {
             const int m = fd.alpha_filter & 3;
             lists[m * n + bd.alpha_counts[m]++] = i;
@@ -271,16 +293,20 @@ int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampl
             bd.alpha_maxh[m] = std::max<uint32_t>(bd.alpha_maxh[m], fd.height);
         }
     }
-    bd.n_frames = n;
-    bd.total_rows = (uint32_t)rows;
-    bd.max_w = max_w;
-    bd.max_h = max_h;
-    bd.sm_count = c->sm_count;
-    bd.lay = scratch_layout(rows, mbs);
+}
+
+// The three parts in one go, tickets ordered over the whole batch.
+int prepare_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
+    int rc = layout_items(c, std::move(in_items), upsampling, threads);
+    if (rc) return rc;
+    parallel_for(c->n, threads, [&](int i) { entropy_one(c, i); });
+    fill_row_order(reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p), 0, c->n,
+                   reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
+    finish_items(c);
     return 0;
 }
 
-int upload(webpb200_ctx* c) {
+int reserve_device(webpb200_ctx* c) {
     cudaSetDevice(c->device);
     const int n = c->n;
     CU(c, c->d_frames.reserve(sizeof(webpb200_frame_desc) * (size_t)std::max(n, 1)), "device frames");
@@ -291,19 +317,6 @@ int upload(webpb200_ctx* c) {
     CU(c, c->d_planes.reserve((size_t)std::max<uint64_t>(c->plane_bytes, 1)), "device planes");
     CU(c, c->d_out.reserve((size_t)std::max<uint64_t>(c->out_bytes, 1)), "device out");
     CU(c, c->d_scratch.reserve((size_t)c->bd.lay.total), "device scratch");
-    cudaStream_t s = c->stream;
-    CU(c, cudaMemcpyAsync(c->d_frames.p, c->h_frames.p, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
-    if (c->total_mbs) {
-        CU(c, cudaMemcpyAsync(c->d_mbs.p, c->h_mbs.p, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D mbs");
-        CU(c, cudaMemcpyAsync(c->d_levels.p, c->h_levels.p, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D levels");
-    }
-    if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
-    CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
-    // the row map lives in the scratch arena next to the counters it is used with
-    if (c->total_rows) {
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
-    }
     BatchDev& bd = c->bd;
     bd.frames = reinterpret_cast<const webpb200_frame_desc*>(c->d_frames.p);
     bd.mbs = reinterpret_cast<const webpb200_mb_desc*>(c->d_mbs.p);
@@ -313,6 +326,27 @@ int upload(webpb200_ctx* c) {
     bd.out = c->d_out.p;
     bd.scratch = c->d_scratch.p;
     bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + c->aux_lists_off);
+    return 0;
+}
+
+int upload(webpb200_ctx* c) {
+    int rc = reserve_device(c);
+    if (rc) return rc;
+    const int n = c->n;
+    cudaStream_t s = c->stream;
+    CU(c, cudaMemcpyAsync(c->d_frames.p, c->h_frames.p, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
+    if (c->total_mbs) {
+        CU(c, cudaMemcpyAsync(c->d_mbs.p, c->h_mbs.p, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D mbs");
+        CU(c, cudaMemcpyAsync(c->d_levels.p, c->h_levels.p, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D levels");
+    }
+    if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+    CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
+    // the row map lives in the scratch arena next to the counters it is used with
+    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
+    if (c->total_rows) {
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
+    }
     c->uploaded = true;
     return 0;
 }
@@ -320,7 +354,10 @@ int upload(webpb200_ctx* c) {
 // events: optional array of 5 events recorded before/after each stage (timing runs)
 int reconstruct(webpb200_ctx* c, const BatchDev& bd, unsigned stages, cudaStream_t s, cudaEvent_t* events) {
     if (bd.total_rows == 0) return 0;
-    CU(c, cudaMemsetAsync(bd.scratch, 0, (size_t)bd.lay.zero_bytes, s), "clear counters");
+    // ticket counters and row progress start at zero; the watchdog word (offset 8) is cleared once
+    // per batch, not per pass, so that a trip in any pass is still there when the host looks
+    CU(c, cudaMemsetAsync(bd.scratch, 0, 8, s), "clear tickets");
+    CU(c, cudaMemsetAsync(bd.scratch + bd.lay.progress_pred_off, 0, (size_t)(bd.lay.zero_bytes - bd.lay.progress_pred_off), s), "clear progress");
     if (events) cudaEventRecord(events[0], s);
     if (stages & 1) { CU(c, launch_predict(bd, s), "k_predict"); c->launches++; }
     if (events) cudaEventRecord(events[1], s);
@@ -351,11 +388,10 @@ int check_abort(webpb200_ctx* c) {
 
 // D2H of the output arena into caller buffers; neighbouring images are sent as one copy when
 // both sides are contiguous
-int download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens) {
-    cudaSetDevice(c->device);
+int download_range(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens, int i0, int i1) {
     const webpb200_frame_desc* frames = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
-    const int n = c->n;
-    int i = 0;
+    const int n = i1;
+    int i = i0;
     while (i < n) {
         if (c->items[i].status) { i++; continue; }
         const size_t len = (size_t)frames[i].width * frames[i].height * frames[i].out_bpp;
@@ -372,6 +408,13 @@ int download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens) {
         CU(c, cudaMemcpyAsync(dst, c->d_out.p + src, run, cudaMemcpyDeviceToHost, c->stream), "D2H out");
         i = j;
     }
+    return 0;
+}
+
+int download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens) {
+    cudaSetDevice(c->device);
+    int rc = download_range(c, outs, out_lens, 0, c->n);
+    if (rc) return rc;
     CU(c, cudaStreamSynchronize(c->stream), "sync");
     return check_abort(c);
 }
@@ -581,14 +624,112 @@ extern "C" int webpb200_batch_get_packed(webpb200_ctx* c, int image, const webpb
     return 0;
 }
 
+// Pipelined: the batch is cut into chunks of about kChunkMbs macroblocks; host threads entropy-
+// decode images in order, and as soon as a chunk is complete its packed arrays go to the device,
+// its kernels run and its pixels come back, all on the context's stream, while the host threads
+// are already decoding the following chunks.  The copies and kernels hide behind the entropy decode.
 extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
                                      const size_t* out_lens, int* status, int upsampling, int host_threads) {
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
-    int rc = webpb200_batch_prepare(c, files, lens, n, nullptr, upsampling, host_threads);
-    if (rc < 0) return rc;
-    if ((rc = upload(c)) != 0) return rc;
-    if ((rc = reconstruct(c, c->bd, 0xF, c->stream, nullptr)) != 0) return rc;
-    if ((rc = download(c, outs, out_lens)) != 0) return rc;
+    if (n < 0) return -WEBPB200_ERR_INVALID_PARAM;
+    cudaSetDevice(c->device);
+    const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<WorkItem> items;
+    items_from_files(files, lens, n, host_threads, &items);
+    int rc = layout_items(c, std::move(items), upsampling, host_threads);
+    if (rc) return rc;
+    if ((rc = reserve_device(c)) != 0) return rc;
+    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
+    cudaStream_t s = c->stream;
+
+    // chunks by macroblock count; ticket order row-major inside each chunk
+    const uint64_t kChunkMbs = 96 * 1024;
+    std::vector<int> chunk_end;
+    std::vector<int> chunk_of((size_t)n, 0);
+    {
+        uint64_t acc = 0;
+        for (int i = 0; i < n; i++) {
+            chunk_of[i] = (int)chunk_end.size();
+            acc += (uint64_t)frames[i].mbw * frames[i].mbh;
+            if (acc >= kChunkMbs || i == n - 1) {
+                chunk_end.push_back(i + 1);
+                acc = 0;
+            }
+        }
+    }
+    const int nchunks = (int)chunk_end.size();
+    uint32_t* order = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off);
+    for (int k = 0; k < nchunks; k++) fill_row_order(frames, k ? chunk_end[k - 1] : 0, chunk_end[k], order);
+    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
+    if (c->total_rows) {
+        const uint32_t* rowmap = reinterpret_cast<const uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, rowmap, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "rowmap");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, order, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "row order");
+    }
+    c->uploaded = true;
+
+    // host threads: images in order, one at a time each
+    std::unique_ptr<std::atomic<int>[]> left(new std::atomic<int>[(size_t)std::max(nchunks, 1)]);
+    for (int k = 0; k < nchunks; k++) left[k].store(chunk_end[k] - (k ? chunk_end[k - 1] : 0));
+    std::atomic<int> next{0};
+    auto worker = [&]() {
+        for (;;) {
+            const int i = next.fetch_add(1);
+            if (i >= n) return;
+            entropy_one(c, i);
+            left[chunk_of[i]].fetch_sub(1, std::memory_order_release);
+        }
+    };
+    int nthreads = std::max(1, std::min(host_threads, n));
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthreads; t++) pool.emplace_back(worker);
+
+    const bool any_alpha = c->alpha_bytes != 0;
+    int err = 0;
+    for (int k = 0; k < nchunks && !err; k++) {
+        while (left[k].load(std::memory_order_acquire) > 0) std::this_thread::sleep_for(std::chrono::microseconds(50));
+        const int i0 = k ? chunk_end[k - 1] : 0, i1 = chunk_end[k];
+        const uint64_t mb0 = frames[i0].mb_base;
+        const uint64_t mb1 = i1 < n ? frames[i1].mb_base : c->total_mbs;
+        const uint32_t row0 = frames[i0].row_base, row1 = i1 < n ? frames[i1].row_base : (uint32_t)c->total_rows;
+        auto fail = [&](cudaError_t e, const char* what) { if (!err && c->fail(e, what)) err = -WEBPB200_ERR_CUDA; };
+        fail(cudaMemcpyAsync(c->d_frames.p + sizeof(webpb200_frame_desc) * (size_t)i0, frames + i0, sizeof(webpb200_frame_desc) * (size_t)(i1 - i0), cudaMemcpyHostToDevice, s), "H2D frames");
+        if (mb1 > mb0) {
+            fail(cudaMemcpyAsync(c->d_mbs.p + sizeof(webpb200_mb_desc) * mb0, c->h_mbs.p + sizeof(webpb200_mb_desc) * mb0, sizeof(webpb200_mb_desc) * (mb1 - mb0), cudaMemcpyHostToDevice, s), "H2D mbs");
+            const size_t lb = sizeof(int16_t) * WEBPB200_LEVELS_PER_MB;
+            fail(cudaMemcpyAsync(c->d_levels.p + lb * mb0, c->h_levels.p + lb * mb0, lb * (mb1 - mb0), cudaMemcpyHostToDevice, s), "H2D levels");
+        }
+        if (row1 > row0 && !err) {
+            BatchDev bd = c->bd;
+            bd.frame_first = i0;
+            bd.n_frames = i1 - i0;
+            bd.order_first = row0;
+            bd.total_rows = row1 - row0;
+            if (int r = reconstruct(c, bd, 0x7, s, nullptr)) err = r;
+        }
+        if (!any_alpha && !err)
+            if (int r = download_range(c, outs, out_lens, i0, i1)) err = r;
+    }
+    for (auto& t : pool) t.join();
+    if (err) {
+        cudaStreamSynchronize(s);
+        return err;
+    }
+    if (any_alpha) {  // the ALPH filter methods are known now: merge alpha for the whole batch, then fetch
+        finish_items(c);
+        CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+        CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
+        CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
+        int l = 0;
+        CU(c, launch_alpha(c->bd, s, &l), "k_alpha");
+        c->launches += (uint64_t)l;
+        if ((rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
+    }
+    CU(c, cudaStreamSynchronize(s), "sync");
+    if ((rc = check_abort(c)) != 0) return rc;
+    if (trace) std::fprintf(stderr, "[webpb200] decode_batch n=%d in %d chunks: %.1f ms\n", n, nchunks,
+                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     int bad = 0;
     for (int i = 0; i < n; i++) {
         if (status) status[i] = c->items[i].status;
@@ -697,6 +838,7 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
         }
     }
     uint8_t* scratch = static_cast<uint8_t*>(d_scratch);
+    CU(c, cudaMemsetAsync(scratch, 0, 256, s), "clear watchdog");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.rowmap_off, rowmap.data(), 4 * rowmap.size(), cudaMemcpyHostToDevice, s), "rowmap");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.order_off, order.data(), 4 * order.size(), cudaMemcpyHostToDevice, s), "row order");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.total, lists.data(), sizeof(int) * lists.size(), cudaMemcpyHostToDevice, s), "lists");

@@ -1149,7 +1149,7 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
     a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_pred_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
-    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
+    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
     // many images: the row above is usually long finished, so publish progress (a release fence each
@@ -1172,7 +1172,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
     a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_lf_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
-    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off);
+    a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
     a.publish_every = b.n_frames >= 64 ? 4 : 1;
@@ -1188,7 +1188,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
 
 cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
     RgbArgs a;
-    a.frames = b.frames; a.planes = b.planes; a.out = b.out;
+    a.frames = b.frames + b.frame_first; a.planes = b.planes; a.out = b.out;
     // thread = 8 pixels x 2 rows; block = 64 x 2 threads = 512 pixels x 4 rows; row pairs: h/2 + 1
     dim3 grid((b.max_w + 511) / 512, (b.max_h / 2 + 1 + 1) / 2, b.n_frames);
     k_yuv2rgb<<<grid, dim3(64, 2), 0, s>>>(a);

@@ -31,8 +31,10 @@ struct BatchDev {
     uint8_t* out;
     uint8_t* scratch;
     ScratchLayout lay;
-    int n_frames;
-    uint32_t total_rows;
+    int n_frames;           // frames covered by this launch ...
+    int frame_first;        // ... starting at this index of `frames` (a chunk of the batch; 0 = all)
+    uint32_t total_rows;    // macroblock rows (tickets) of those frames ...
+    uint32_t order_first;   // ... whose tickets start at this index of the order array
     uint32_t max_w, max_h;  // largest frame of the batch (grid sizing)
     int sm_count;
     // frames with an ALPH plane, grouped by filter method m: alpha_lists[m * n_frames + k]
