@@ -10,7 +10,12 @@ files = S.make_batch(S.cfg2_image, n, threads=os.cpu_count())
 bd = W.BatchDecoder(0)
 pin = W.PinnedBuffer(n * 512 * 512 * 3)
 outs = [pin.array[i * 786432:(i + 1) * 786432] for i in range(n)]
-for th in (os.cpu_count(), os.cpu_count() // 2):
+th = os.cpu_count()
+best = 1e9
+for _ in range(4):
+    t = time.perf_counter(); bd.prepare(files, host_threads=th); best = min(best, time.perf_counter() - t)
+print("host stage alone (parse + entropy, %d threads): %.1f ms" % (th, best * 1e3), flush=True)
+for th in (os.cpu_count(),):
     for _ in range(3):
         t = time.perf_counter(); bd.decode(files, outs=outs, host_threads=th); dt = time.perf_counter() - t
         print("threads %d: %.1f ms -> %.0f MPix/s" % (th, dt * 1e3, n * 512 * 512 / dt / 1e6), flush=True)
