@@ -309,6 +309,7 @@ struct __align__(16) PredictSmem {
     uint8_t vw[9 * 16];
     int16_t res[24 * 16];  // residuals of the 24 blocks, raster inside a block
     int32_t wht[16];
+    uint32_t quant[16];                  // this frame's quantisers: [segment * 4 + class] = dc | ac << 16
     int16_t lv[32 * 16];                 // next macroblock's levels (25 x 16 used), prefetched with cp.async
     uint4 desc;                          // and its descriptor
 };
@@ -391,6 +392,17 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
 
         prefetch_mb(S, A, mb_row0, lane);
+        // the frame's quantisers, once per row (class 0 = Y, 1 = U/V, 2 = Y2): descriptor loads would
+        // miss L1 on every macroblock because the acquire fences keep invalidating it
+        if (lane < 16) {
+            const webpb200_segment* sg = fd->seg + (lane >> 2);
+            const int cls = lane & 3;
+            const int dc = cls == 0 ? sg->ydc : cls == 1 ? sg->uvdc : sg->y2dc;
+            const int ac = cls == 0 ? sg->yac : cls == 1 ? sg->uvac : sg->y2ac;
+            S.quant[lane] = (uint32_t)(dc & 0xffff) | ((uint32_t)ac << 16);
+        }
+        __syncwarp();
+        const int qcls = lane < 16 ? 0 : lane < 24 ? 1 : 2;
         for (int mbx = 0; mbx < mbw; mbx++) {
             const size_t mbi = mb_row0 + mbx;
             cp_async_wait_all();
@@ -412,10 +424,10 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 int c[16];
                 unpack8(lv_lo, c);
                 unpack8(lv_hi, c + 8);
-                const webpb200_segment* sg = fd->seg + segment;
+                const uint32_t qw = S.quant[segment * 4 + qcls];
+                const int dcq = qw & 0xffff, acq = qw >> 16;  // quantisers are positive and below 2^15
                 if (ymode != 4) {
                     if (lane == 24) {
-                        const int dcq = sg->y2dc, acq = sg->y2ac;
                         c[0] *= dcq;
 #pragma unroll
                         for (int i = 1; i < 16; i++) c[i] *= acq;
@@ -427,7 +439,6 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 }
                 bool nz = false;
                 if (lane < 24) {
-                    const int dcq = lane < 16 ? sg->ydc : sg->uvdc, acq = lane < 16 ? sg->yac : sg->uvac;
                     c[0] *= dcq;
 #pragma unroll
                     for (int i = 1; i < 16; i++) c[i] *= acq;
@@ -665,6 +676,7 @@ __device__ __forceinline__ void lf_line(uint8_t* p, int st, int kind, int edge_l
 struct __align__(16) FilterSmem {
     uint8_t y[20 * 32];
     uint8_t c[2][12 * 16];
+    uint4 ynext[20];     // the next macroblock's luma columns, prefetched with cp.async (L2 path) while this one is filtered
 };
 
 struct FilterArgs {
@@ -722,29 +734,60 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
         uint4* const ytile = reinterpret_cast<uint4*>(S.y + lane * 32);            // [0] previous, [1] current panel
         uint2* const ctile = reinterpret_cast<uint2*>(S.c[cpl] + crow * 16);
 
-        for (int mbx = 0; mbx < mbw; mbx++) {
-            const size_t mbi = mb_row0 + mbx;
-            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
-
-            // ---- load the 16 new columns (rows -4..15) into the current panel ----
-            if (ylane) ytile[1] = ld_cg_u128(yrow + (size_t)mbx * 16);
-            if (clane) ctile[1] = ld_cg_u64(crow_ptr + (size_t)mbx * 8);
-
-            // ---- calculate_filter_parameters, mod.rs:1191-1244 ----
-            const uint32_t mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mbi));
-            const int ymode = mbword & 0xff, segment = (mbword >> 16) & 3;
-            const bool skipped = (mbword >> 24) & 1;
+        // calculate_filter_parameters, mod.rs:1191-1217, once per row: the level of a macroblock
+        // depends only on its segment and on whether it is B_PRED -> 2 x 4 bytes
+        uint32_t lvl_plain = 0, lvl_bpred = 0;
+        for (int sgi = 0; sgi < 4; sgi++) {
             int level = frame_level;
             if (fd->segments_enabled) {
-                const int sl = fd->seg[segment].lf_level;
-                level = fd->seg[segment].delta_values ? level + sl : sl;
+                const int sl = fd->seg[sgi].lf_level;
+                level = fd->seg[sgi].delta_values ? level + sl : sl;
             }
             level = min(max(level, 0), 63);
+            int lb = level;
             if (fd->lf_adj_enabled) {
                 level += fd->ref_delta0;
-                if (ymode == 4) level += fd->mode_delta0;
+                lb = level + fd->mode_delta0;
             }
-            level = min(max(level, 0), 63);
+            lvl_plain |= (uint32_t)min(max(level, 0), 63) << (8 * sgi);
+            lvl_bpred |= (uint32_t)min(max(lb, 0), 63) << (8 * sgi);
+        }
+
+        // prefetch of macroblock x + 1: only when the row above is already far enough (it usually
+        // is); otherwise the next iteration loads synchronously after its wait
+        bool have_next = false;
+        uint2 cnext = make_uint2(0, 0);  // chroma of the next macroblock (8-byte cp.async would go through L1, which may be stale)
+        uint32_t mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mb_row0));
+        uint32_t mbnz = A.mbinfo[mb_row0];
+
+        for (int mbx = 0; mbx < mbw; mbx++) {
+            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
+
+            // ---- the 16 new columns (rows -4..15) into the current panel ----
+            if (have_next) {
+                cp_async_wait_all();
+                if (ylane) ytile[1] = S.ynext[lane];
+                if (clane) ctile[1] = cnext;
+            } else {
+                if (ylane) ytile[1] = ld_cg_u128(yrow + (size_t)mbx * 16);
+                if (clane) ctile[1] = ld_cg_u64(crow_ptr + (size_t)mbx * 8);
+            }
+            have_next = mbx + 1 < mbw && (mby == 0 || seen >= min(mbx + 3, mbw));
+            if (have_next) {
+                if (ylane) cp_async16(&S.ynext[lane], yrow + (size_t)(mbx + 1) * 16);
+                if (clane) cnext = ld_cg_u64(crow_ptr + (size_t)(mbx + 1) * 8);
+                cp_async_commit();
+            }
+
+            const int ymode = mbword & 0xff, segment = (mbword >> 16) & 3;
+            const bool skipped = (mbword >> 24) & 1;
+            const bool do_sub = ymode == 4 || (!skipped && mbnz != 0);  // mod.rs:977-978
+            const int level = ((ymode == 4 ? lvl_bpred : lvl_plain) >> (8 * segment)) & 0xff;
+            if (mbx + 1 < mbw) {  // next macroblock's descriptor word and non_zero_dct flag, early
+                mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mb_row0 + mbx + 1));
+                mbnz = A.mbinfo[mb_row0 + mbx + 1];
+            }
+            // interior limit and thresholds, mod.rs:1219-1243
             int interior = level;
             if (sharp > 0) {
                 interior >>= sharp > 4 ? 2 : 1;
@@ -753,7 +796,6 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
             if (interior == 0) interior = 1;
             const int hev_thr = level >= 40 ? 2 : level >= 15 ? 1 : 0;
             const int mbedge = (level + 2) * 2 + interior, subedge = level * 2 + interior;
-            const bool do_sub = ymode == 4 || (!skipped && A.mbinfo[mbi] != 0);  // mod.rs:977-978
             __syncwarp();
 
             // ---- loop_filter, mod.rs:966-1188: four edge groups in the reference's order ----
