@@ -1075,48 +1075,74 @@ __global__ void k_alpha_cols(AlphaArgs A) {
     const uint8_t* a = A.alpha + fd->alpha_off;
     uint8_t* o = A.out + fd->out_off;
     unsigned v = o[(size_t)x * 4 + 3];
-    for (int y = 1; y < h; y++) {
-        v = (v + a[(size_t)y * w + x]) & 0xff;
-        o[((size_t)y * w + x) * 4 + 3] = (uint8_t)v;
+    for (int y0 = 1; y0 < h; y0 += 8) {  // 8 independent loads in flight, then the serial sums
+        unsigned r[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) r[i] = y0 + i < h ? a[(size_t)(y0 + i) * w + x] : 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (y0 + i < h) {
+                v = (v + r[i]) & 0xff;
+                o[((size_t)(y0 + i) * w + x) * 4 + 3] = (uint8_t)v;
+            }
+        }
     }
 }
 
-// gradient: one warp per image; 32 rows at a time, lane j = row r0 + j running j columns
-// behind the lane above, so T and TL arrive by shuffle; the row above the group is re-read
-// from the output
-__global__ void k_alpha_gradient(AlphaArgs A) {
+// gradient: one block per image, one thread per row (1024 rows at a time), the whole block
+// walking the anti-diagonals in lock step: at step t row y does column t - y, so its left, top
+// and top-left neighbours were finished one and two steps earlier.  The value of the row above
+// travels through a double-buffered shared array; top-left is the top of the step before.
+__global__ void __launch_bounds__(1024) k_alpha_gradient(AlphaArgs A) {
+    __shared__ uint8_t val[2][1024];
     const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.x];
     const int w = fd->width, h = fd->height;
     const uint8_t* a = A.alpha + fd->alpha_off;
     uint8_t* o = A.out + fd->out_off;
-    const int lane = threadIdx.x;
-    for (int r0 = 0; r0 < h; r0 += 32) {
-        const int y = r0 + lane;
-        int cur = 0, prev = 0;  // my alpha at column x-1 (cur after update) and the one before
-        for (int t = 0; t < w + 31; t++) {
-            const int x = t - lane;
-            // the lane above finished column x in the previous step (its cur) and x-1 before that
-            int T = __shfl_up_sync(kFull, cur, 1), TL = __shfl_up_sync(kFull, prev, 1);
-            const bool active = x >= 0 && x < w && y < h;
-            if (lane == 0 && active && y > 0) {
-                T = o[((size_t)(y - 1) * w + x) * 4 + 3];
-                TL = x > 0 ? o[((size_t)(y - 1) * w + x - 1) * 4 + 3] : 0;
-            }
-            if (active) {
-                const int L = cur;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    for (int r0 = 0; r0 < h; r0 += nthr) {
+        const int y = r0 + tid;
+        const int nrows = min(nthr, h - r0);
+        const bool row_ok = tid < nrows;
+        const uint8_t* arow = a + (size_t)y * w;
+        uint8_t* orow = o + (size_t)y * w * 4 + 3;
+        const uint8_t* above = o + (size_t)(y - 1) * w * 4 + 3;  // previous group's last row (thread 0 only)
+        int cur = 0, tprev = 0;
+        // residuals of my row for the next steps, 8 per 64-bit word, fetched 8..16 steps ahead of use;
+        // the refill happens at the same step for every thread (no divergence)
+        auto load8 = [&](int c0) {
+            unsigned long long q = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (row_ok && c0 + i >= 0 && c0 + i < w) q |= (unsigned long long)arow[c0 + i] << (8 * i);
+            return q;
+        };
+        unsigned long long curq = load8(-tid), nxtq = load8(8 - tid);
+        const int steps = w + nrows - 1;
+        for (int t = 0; t < steps; t++) {
+            const int x = t - tid;
+            const bool act = row_ok && x >= 0 && x < w;
+            int T = 0;
+            if (tid > 0) T = val[(t + 1) & 1][tid - 1];
+            else if (act && y > 0) T = above[(size_t)x * 4];
+            if (act) {
                 int pred;
-                if (x == 0 && y == 0) pred = 0;
-                else if (x == 0) pred = T;        // (val, val, val) from above
-                else if (y == 0) pred = L;
-                else pred = min(max(L + T - TL, 0), 255);
-                const int v = (pred + a[(size_t)y * w + x]) & 0xff;
-                o[((size_t)y * w + x) * 4 + 3] = (uint8_t)v;
-                prev = cur;
-                cur = v;
+                if (x == 0) pred = y == 0 ? 0 : T;   // extended.rs:163-170: (val, val, val) from above
+                else if (y == 0) pred = cur;         // first row: from the left
+                else pred = min(max(cur + T - tprev, 0), 255);
+                cur = (pred + (int)((curq >> (8 * (t & 7))) & 0xff)) & 0xff;
+                orow[(size_t)x * 4] = (uint8_t)cur;
+                val[t & 1][tid] = (uint8_t)cur;
             }
+            if ((t & 7) == 7) {
+                curq = nxtq;
+                nxtq = load8(x + 9);
+            }
+            tprev = T;
+            __syncthreads();
         }
         __threadfence_block();
-        __syncwarp();
+        __syncthreads();
     }
 }
 
@@ -1262,7 +1288,7 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches) {
     }
     if (counts[3]) {
         a.list = b.alpha_lists + 3 * b.n_frames;
-        k_alpha_gradient<<<counts[3], 32, 0, s>>>(a);
+        k_alpha_gradient<<<counts[3], (int)min(1024u, (b.alpha_maxh[3] + 31) & ~31u), 0, s>>>(a);
         ++*launches;
     }
     return cudaGetLastError();

@@ -131,7 +131,7 @@ def test_vp8_decode_frame_planes(W, oracle, synth):
 
 
 @pytest.mark.parametrize("filtering", [0, 1, 2, 3])
-@pytest.mark.parametrize("size", [(37, 23), (1, 9), (9, 1), (64, 48), (131, 77)])
+@pytest.mark.parametrize("size", [(37, 23), (1, 9), (9, 1), (64, 48), (131, 77), (24, 1100)])
 def test_alpha_filters(W, bd, oracle, synth, filtering, size):
     """ALPH un-filter + merge, decoder.rs:718-734 / extended.rs:131-191, raw alpha, every method"""
     w, h = size
