@@ -116,7 +116,7 @@ struct webpb200_ctx {
     uint64_t launches = 0;
 
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux;
-    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out;
+    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff;
 
     // current batch
     int n = 0;
@@ -317,6 +317,7 @@ int reserve_device(webpb200_ctx* c) {
     CU(c, c->d_planes.reserve((size_t)std::max<uint64_t>(c->plane_bytes, 1)), "device planes");
     CU(c, c->d_out.reserve((size_t)std::max<uint64_t>(c->out_bytes, 1)), "device out");
     CU(c, c->d_scratch.reserve((size_t)c->bd.lay.total), "device scratch");
+    if (c->alpha_bytes) CU(c, c->d_handoff.reserve((size_t)alpha_handoff_size(c->alpha_bytes)), "device alpha handoff");
     BatchDev& bd = c->bd;
     bd.frames = reinterpret_cast<const webpb200_frame_desc*>(c->d_frames.p);
     bd.mbs = reinterpret_cast<const webpb200_mb_desc*>(c->d_mbs.p);
@@ -326,6 +327,8 @@ int reserve_device(webpb200_ctx* c) {
     bd.out = c->d_out.p;
     bd.scratch = c->d_scratch.p;
     bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + c->aux_lists_off);
+    bd.alpha_handoff = c->alpha_bytes ? reinterpret_cast<uint16_t*>(c->d_handoff.p) : nullptr;
+    bd.alpha_handoff_bytes = c->alpha_bytes ? alpha_handoff_size(c->alpha_bytes) : 0;
     return 0;
 }
 
@@ -501,7 +504,7 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux}) b->release();
-    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out})
+    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff})
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
@@ -784,9 +787,10 @@ extern "C" void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8
 // ------------------------------------------------------------------------------------------------
 extern "C" int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n, uint64_t* plane_bytes, uint64_t* out_bytes,
                                         uint64_t* scratch_bytes) {
-    uint64_t p = 0, o = 0, rows = 0, mbs = 0;
+    uint64_t p = 0, o = 0, rows = 0, mbs = 0, alpha_end = 0;
     for (int i = 0; i < n; i++) {
         const uint64_t m = (uint64_t)frames[i].mbw * frames[i].mbh;
+        if (frames[i].alpha_mode) alpha_end = std::max(alpha_end, frames[i].alpha_off + (uint64_t)frames[i].width * frames[i].height);
         p = std::max(p, align256(frames[i].v_off + m * 64));
         o = std::max(o, align256(frames[i].out_off + (uint64_t)frames[i].width * frames[i].height * frames[i].out_bpp));
         rows = std::max<uint64_t>(rows, (uint64_t)frames[i].row_base + frames[i].mbh);
@@ -794,7 +798,8 @@ extern "C" int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n
     }
     if (plane_bytes) *plane_bytes = p;
     if (out_bytes) *out_bytes = o;
-    if (scratch_bytes) *scratch_bytes = scratch_layout(rows, mbs).total + align256(16 * (uint64_t)std::max(n, 1));
+    if (scratch_bytes)
+        *scratch_bytes = scratch_layout(rows, mbs).total + align256(16 * (uint64_t)std::max(n, 1)) + (alpha_end ? alpha_handoff_size(alpha_end) : 0);
     return 0;
 }
 
@@ -806,10 +811,11 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     webpb200_ctx* c = default_ctx(&st);
     if (!c) return -st;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    uint64_t rows = 0, mbs = 0;
+    uint64_t rows = 0, mbs = 0, alpha_end = 0;
     BatchDev bd;
     std::memset(&bd, 0, sizeof(bd));
     for (int i = 0; i < n; i++) {
+        if (hf[i].alpha_mode) alpha_end = std::max(alpha_end, hf[i].alpha_off + (uint64_t)hf[i].width * hf[i].height);
         rows = std::max<uint64_t>(rows, (uint64_t)hf[i].row_base + hf[i].mbh);
         mbs = std::max<uint64_t>(mbs, (uint64_t)hf[i].mb_base + (uint64_t)hf[i].mbw * hf[i].mbh);
         bd.max_w = std::max<uint32_t>(bd.max_w, hf[i].width);
@@ -847,6 +853,10 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     bd.planes = d_planes; bd.out = d_out; bd.scratch = scratch;
     bd.n_frames = n; bd.total_rows = (uint32_t)rows; bd.sm_count = c->sm_count;
     bd.alpha_lists = reinterpret_cast<const int*>(scratch + bd.lay.total);
+    if (alpha_end) {
+        bd.alpha_handoff = reinterpret_cast<uint16_t*>(scratch + bd.lay.total + align256(16 * (uint64_t)n));
+        bd.alpha_handoff_bytes = alpha_handoff_size(alpha_end);
+    }
     return reconstruct(c, bd, stages, s, nullptr);
 }
 

@@ -1089,60 +1089,139 @@ __global__ void k_alpha_cols(AlphaArgs A) {
     }
 }
 
-// gradient: one block per image, one thread per row (1024 rows at a time), the whole block
-// walking the anti-diagonals in lock step: at step t row y does column t - y, so its left, top
-// and top-left neighbours were finished one and two steps earlier.  The value of the row above
-// travels through a double-buffered shared array; top-left is the top of the step before.
-__global__ void __launch_bounds__(1024) k_alpha_gradient(AlphaArgs A) {
-    __shared__ uint8_t val[2][1024];
-    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.x];
-    const int w = fd->width, h = fd->height;
-    const uint8_t* a = A.alpha + fd->alpha_off;
-    uint8_t* o = A.out + fd->out_off;
-    const int tid = threadIdx.x, nthr = blockDim.x;
-    for (int r0 = 0; r0 < h; r0 += nthr) {
-        const int y = r0 + tid;
-        const int nrows = min(nthr, h - r0);
-        const bool row_ok = tid < nrows;
-        const uint8_t* arow = a + (size_t)y * w;
-        uint8_t* orow = o + (size_t)y * w * 4 + 3;
-        const uint8_t* above = o + (size_t)(y - 1) * w * 4 + 3;  // previous group's last row (thread 0 only)
-        int cur = 0, tprev = 0;
-        // residuals of my row for the next steps, 8 per 64-bit word, fetched 8..16 steps ahead of use;
-        // the refill happens at the same step for every thread (no divergence)
-        auto load8 = [&](int c0) {
-            unsigned long long q = 0;
+// gradient: clamp(L + T - TL) is a recurrence in both directions.  A warp owns a band of 32 rows,
+// lane j = row j running j columns behind lane j-1, so T and TL arrive by shuffle (anti-diagonal
+// order).  Bands are pipelined down the image: lane 31 hands each finished pixel of the band's
+// last row to the band below through the hand-off array, as a 16-bit word that carries its own
+// valid bit (alpha | 0x100, array cleared before the launch) -- one relaxed store, one relaxed
+// load, no fence, and the consumer trails the producer by about two tiles.  Bands are handed out
+// by a ticket counter, band-major across the images of the launch, so a band only ever waits for
+// a ticket drawn earlier.  Residuals and results are staged in 32x32-byte tiles: global traffic
+// is one coalesced row segment per instruction, not 32 scattered bytes.
+constexpr int kGradWarps = 4;
+
+struct GradArgs {
+    AlphaArgs a;
+    int n_img, max_bands;
+    uint16_t* handoff;
+    unsigned int* ticket;
+    unsigned int* abort_word;
+};
+
+struct __align__(16) GradSmem {
+    uint8_t tile[2][32 * 32];  // [tile & 1][row][column]: residual in, alpha out (in place)
+    uint8_t top[2][32];        // [tile & 1]: row above the band, columns 32c .. 32c+31
+};
+
+__device__ __forceinline__ unsigned ld_relaxed_u16(const uint16_t* p) {
+    unsigned short v;
+    asm volatile("ld.relaxed.gpu.global.u16 %0, [%1];" : "=h"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u16(uint16_t* p, unsigned v) {
+    asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p), "h"((unsigned short)v) : "memory");
+}
+
+__global__ void __launch_bounds__(kGradWarps * 32, 4) k_alpha_gradient(GradArgs G) {
+    __shared__ GradSmem sm[kGradWarps];
+    const int lane = threadIdx.x & 31;
+    GradSmem& S = sm[threadIdx.x >> 5];
+    const unsigned total = (unsigned)G.n_img * (unsigned)G.max_bands;
+
+    for (;;) {
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(G.ticket, 1u);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= total) return;
+        const int g = (int)(t / (unsigned)G.n_img);
+        const webpb200_frame_desc* fd = G.a.frames + G.a.list[t % (unsigned)G.n_img];
+        const int w = fd->width, h = fd->height;
+        const int nbands = (h + 31) >> 5, ntiles = (w + 31) >> 5;
+        if (g >= nbands) continue;
+        const uint8_t* a = G.a.alpha + fd->alpha_off;
+        uint8_t* o = G.a.out + fd->out_off;
+        uint16_t* hand = G.handoff + (fd->alpha_off >> 4);  // row g of it = last row of band g
+        const uint16_t* above = hand + (size_t)(g - 1) * w;
+        uint16_t* below = g + 1 < nbands ? hand + (size_t)g * w : nullptr;  // written by lane 31 only
+
+        const int y0 = g * 32, nrows = min(32, h - y0);
+        const unsigned wl = lane < nrows ? (unsigned)w : 0u;  // columns this lane works on (0 = idle row)
+        const bool hands = lane == 31 && below != nullptr;
+        // Zero start values make the edge rules of extended.rs:163-170 fall out of the general one:
+        // x == 0 -> L = TL = 0 -> pred = T (0 on the first row); y == 0 -> T = TL = 0 -> pred = L.
+        int cur = 0;       // my alpha at column x-1 (L)
+        int TL = 0;        // T of the previous step
+        int flushed = 0;   // tiles of this band already written out
+        unsigned nxt = 0;  // hand-off word of the next tile's column, fetched early
+        uint8_t pre[32];   // residual tile fetched one tile ahead (lane = column, index = row)
+
+        auto fetch = [&](int c) {
+            const int x = 32 * c + lane;
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (row_ok && c0 + i >= 0 && c0 + i < w) q |= (unsigned long long)arow[c0 + i] << (8 * i);
-            return q;
+            for (int r = 0; r < 32; r++) pre[r] = (r < nrows && x < w) ? a[(size_t)(y0 + r) * w + x] : 0;
         };
-        unsigned long long curq = load8(-tid), nxtq = load8(8 - tid);
-        const int steps = w + nrows - 1;
-        for (int t = 0; t < steps; t++) {
-            const int x = t - tid;
-            const bool act = row_ok && x >= 0 && x < w;
-            int T = 0;
-            if (tid > 0) T = val[(t + 1) & 1][tid - 1];
-            else if (act && y > 0) T = above[(size_t)x * 4];
-            if (act) {
-                int pred;
-                if (x == 0) pred = y == 0 ? 0 : T;   // extended.rs:163-170: (val, val, val) from above
-                else if (y == 0) pred = cur;         // first row: from the left
-                else pred = min(max(cur + T - tprev, 0), 255);
-                cur = (pred + (int)((curq >> (8 * (t & 7))) & 0xff)) & 0xff;
-                orow[(size_t)x * 4] = (uint8_t)cur;
-                val[t & 1][tid] = (uint8_t)cur;
+        auto flush = [&](int c) {  // finished tile c -> byte 3 of the output pixels
+            const int x = 32 * c + lane;
+            const uint8_t* tl = S.tile[c & 1];
+            if (x < w) {
+#pragma unroll 8
+                for (int r = 0; r < nrows; r++) o[((size_t)(y0 + r) * w + x) * 4 + 3] = tl[r * 32 + lane];
             }
-            if ((t & 7) == 7) {
-                curq = nxtq;
-                nxtq = load8(x + 9);
+        };
+
+        fetch(0);
+        if (g > 0 && lane < w) nxt = ld_relaxed_u16(above + lane);
+        if (g == 0) S.top[0][lane] = 0, S.top[1][lane] = 0;
+        const int last_tile = (w + 30) >> 5;  // lane 31 reaches column w-1 at step w+30
+        for (int c = 0; c <= last_tile; c++) {
+            // ---- lane 0 enters tile c
+            __syncwarp();
+            if (c >= 2) {
+                flush(c - 2);
+                flushed = c - 1;
             }
-            tprev = T;
-            __syncthreads();
+            if (c < ntiles) {
+                uint8_t* tl = S.tile[c & 1];
+#pragma unroll
+                for (int r = 0; r < 32; r++) tl[r * 32 + lane] = pre[r];
+                if (c + 1 < ntiles) fetch(c + 1);
+                if (g > 0) {  // the row above this tile, once the band above has produced it
+                    const int x = 32 * c + lane;
+                    unsigned v = x < w ? nxt : 0x100u;
+                    unsigned spins = 0;
+                    while (!__all_sync(kFull, v & 0x100u)) {
+                        __nanosleep(40);
+                        if (x < w && !(v & 0x100u)) v = ld_relaxed_u16(above + x);
+                        if ((++spins & 0x3ff) == 0) {
+                            if (spins > (1u << 24)) atomicExch(G.abort_word, 1u);
+                            if (*reinterpret_cast<volatile unsigned int*>(G.abort_word)) return;
+                        }
+                    }
+                    S.top[c & 1][lane] = (uint8_t)v;
+                    if (x + 32 < w) nxt = ld_relaxed_u16(above + x + 32);
+                }
+            }
+            __syncwarp();
+            // ---- 32 anti-diagonal steps
+            const uint8_t* top = S.top[c & 1];
+            uint8_t* const row = S.tile[0] + lane * 32;
+            int x = 32 * c - lane;
+#pragma unroll 4
+            for (int i = 0; i < 32; i++, x++) {
+                const int up = __shfl_up_sync(kFull, cur, 1);
+                const int T = lane == 0 ? (int)top[i] : up;
+                uint8_t* cell = row + (x & 31) + ((x & 32) << 5);
+                const int v = (min(max(cur + T - TL, 0), 255) + *cell) & 0xff;
+                TL = T;
+                if ((unsigned)x < wl) {
+                    *cell = (uint8_t)v;
+                    cur = v;
+                    if (hands) st_relaxed_u16(below + x, (unsigned)v | 0x100u);
+                }
+            }
         }
-        __threadfence_block();
-        __syncthreads();
+        __syncwarp();
+        for (int c = flushed; c < ntiles; c++) flush(c);
     }
 }
 
@@ -1288,7 +1367,19 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches) {
     }
     if (counts[3]) {
         a.list = b.alpha_lists + 3 * b.n_frames;
-        k_alpha_gradient<<<counts[3], (int)min(1024u, (b.alpha_maxh[3] + 31) & ~31u), 0, s>>>(a);
+        if (!b.alpha_handoff) return cudaErrorInvalidValue;
+        GradArgs g;
+        g.a = a;
+        g.n_img = counts[3];
+        g.max_bands = (int)((b.alpha_maxh[3] + 31) / 32);
+        g.handoff = b.alpha_handoff;
+        g.ticket = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 3;
+        g.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
+        cudaError_t e = cudaMemsetAsync(g.handoff, 0, b.alpha_handoff_bytes, s);
+        if (e == cudaSuccess) e = cudaMemsetAsync(g.ticket, 0, 4, s);
+        if (e != cudaSuccess) return e;
+        const unsigned want = ((unsigned)g.n_img * (unsigned)g.max_bands + kGradWarps - 1) / kGradWarps;
+        k_alpha_gradient<<<min(want, (unsigned)b.sm_count * 4u), kGradWarps * 32, 0, s>>>(g);
         ++*launches;
     }
     return cudaGetLastError();

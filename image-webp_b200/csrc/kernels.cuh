@@ -41,7 +41,13 @@ struct BatchDev {
     const int* alpha_lists;  // device
     int alpha_counts[4];
     uint32_t alpha_maxw[4], alpha_maxh[4];
+    // gradient ALPH filter: the last row of every 32-row band is handed to the band below through
+    // this array (uint16 = alpha | 0x100 once written; cleared before the launch).  The rows of
+    // frame f start at entry f.alpha_off >> 4; alpha_handoff_size(end of the alpha arena) bytes.
+    uint16_t* alpha_handoff;
+    uint64_t alpha_handoff_bytes;
 };
+inline uint64_t alpha_handoff_size(uint64_t alpha_bytes) { return ((alpha_bytes >> 3) + 511) & ~(uint64_t)255; }
 
 void upload_tables_once();  // prediction tables -> __constant__ (per device, call with it current)
 
