@@ -1204,20 +1204,24 @@ __global__ void __launch_bounds__(kGradWarps * 32, 4) k_alpha_gradient(GradArgs 
             __syncwarp();
             // ---- 32 anti-diagonal steps
             const uint8_t* top = S.top[c & 1];
-            uint8_t* const row = S.tile[0] + lane * 32;
+            const unsigned row = (unsigned)__cvta_generic_to_shared(S.tile[0] + lane * 32);
             int x = 32 * c - lane;
 #pragma unroll 4
             for (int i = 0; i < 32; i++, x++) {
                 const int up = __shfl_up_sync(kFull, cur, 1);
                 const int T = lane == 0 ? (int)top[i] : up;
-                uint8_t* cell = row + (x & 31) + ((x & 32) << 5);
-                const int v = (min(max(cur + T - TL, 0), 255) + *cell) & 0xff;
+                const unsigned cell = row + (x & 31) + ((x & 32) << 5);
+                unsigned res;
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(res) : "r"(cell));
+                const int v = (min(max(cur + T - TL, 0), 255) + (int)res) & 0xff;
                 TL = T;
-                if ((unsigned)x < wl) {
-                    *cell = (uint8_t)v;
-                    cur = v;
-                    if (hands) st_relaxed_u16(below + x, (unsigned)v | 0x100u);
-                }
+                const unsigned act = (unsigned)x < wl, hand = act & (unsigned)hands;
+                cur = act ? v : cur;
+                // predicated stores: a branch here would sit on the one-warp critical path
+                asm volatile("{ .reg .pred p, q; setp.ne.u32 p, %2, 0; setp.ne.u32 q, %3, 0;\n"
+                             "  @p st.shared.u8 [%0], %1;\n"
+                             "  @q st.relaxed.gpu.global.u16 [%4], %5; }"
+                             :: "r"(cell), "r"(v), "r"(act), "r"(hand), "l"(below + x), "h"((unsigned short)(v | 0x100)) : "memory");
             }
         }
         __syncwarp();
