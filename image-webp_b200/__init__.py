@@ -87,7 +87,7 @@ SYMBOLS = [
     "webpb200_batch_time", "webpb200_batch_size", "webpb200_batch_get_planes", "webpb200_batch_get_packed",
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
-    "webpb200_predict_device_static",
+    "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
 ]
 
 
@@ -139,6 +139,8 @@ def lib():
     L.webpb200_batch_time.argtypes = [vp, C.c_uint, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.webpb200_batch_size.argtypes = [vp, pi] + [C.POINTER(C.c_uint64)] * 4
     L.webpb200_batch_get_planes.argtypes = [vp, i32, vp, vp, vp]
+    L.webpb200_ctx_set_entropy.argtypes = [vp, i32]
+    L.webpb200_batch_download_packed.argtypes = [vp, i32, vp, vp]
     L.webpb200_batch_get_packed.argtypes = [vp, i32, C.POINTER(C.POINTER(FrameDesc)), C.POINTER(C.POINTER(MbDesc)),
                                             C.POINTER(C.POINTER(C.c_int16))]
     L.webpb200_launch_count.argtypes = [vp]; L.webpb200_launch_count.restype = C.c_uint64
@@ -383,6 +385,20 @@ class BatchDecoder:
         mbs = np.ctypeslib.as_array(C.cast(m, C.POINTER(C.c_uint8)), shape=(n * 16,)).view(MB_DTYPE).copy() if n else np.zeros(0, MB_DTYPE)
         levels = np.ctypeslib.as_array(l, shape=(n, 25, 16)).copy() if n else np.zeros((0, 25, 16), np.int16)
         return fd, mbs, levels
+
+    ENTROPY_HOST, ENTROPY_DEVICE = 0, 1
+
+    def set_entropy(self, where):
+        """Where decode() runs the boolean-entropy decode: ENTROPY_HOST (threads) or ENTROPY_DEVICE (k_entropy)."""
+        self._check(lib().webpb200_ctx_set_entropy(self._h, where))
+
+    def device_packed(self, image, frame_desc):
+        """Macroblock descriptors and levels of one image as the device holds them (after decode/upload)."""
+        n = frame_desc.mbw * frame_desc.mbh
+        mbs = np.zeros(n, dtype=MB_DTYPE)
+        levels = np.zeros((n, 25, 16), dtype=np.int16)
+        self._check(lib().webpb200_batch_download_packed(self._h, image, mbs.ctypes.data, levels.ctypes.data))
+        return mbs, levels
 
     def launch_count(self):
         return lib().webpb200_launch_count(self._h)

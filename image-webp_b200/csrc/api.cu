@@ -115,8 +115,9 @@ struct webpb200_ctx {
     std::string err;
     uint64_t launches = 0;
 
-    PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux;
-    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff;
+    PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
+    int entropy_where = 0;  // WEBPB200_ENTROPY_HOST / _DEVICE: where decode_batch runs the boolean decode
+    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status;
 
     // current batch
     int n = 0;
@@ -158,7 +159,7 @@ void fill_row_order(const webpb200_frame_desc* frames, int i0, int i1, uint32_t*
 
 // Host side of a batch, part 1: probe sizes, lay the arenas out, size the pinned staging, build
 // the row -> image map.  Nothing here depends on the entropy-coded data.
-int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads) {
+int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampling, int threads, bool host_staging = true) {
     cudaSetDevice(c->device);
     c->items = std::move(in_items);
     c->n = (int)c->items.size();
@@ -219,8 +220,10 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
     c->total_mbs = mbs; c->total_rows = rows; c->total_px = px;
     c->plane_bytes = poff; c->out_bytes = ooff; c->alpha_bytes = aoff;
 
-    CU(c, c->h_mbs.reserve(sizeof(webpb200_mb_desc) * (size_t)std::max<uint64_t>(mbs, 1)), "pinned mbs");
-    CU(c, c->h_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(mbs, 1)), "pinned levels");
+    if (host_staging) {
+        CU(c, c->h_mbs.reserve(sizeof(webpb200_mb_desc) * (size_t)std::max<uint64_t>(mbs, 1)), "pinned mbs");
+        CU(c, c->h_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(mbs, 1)), "pinned levels");
+    }
     CU(c, c->h_alpha.reserve((size_t)std::max<uint64_t>(aoff, 1)), "pinned alpha");
     c->aux_rowmap_off = 0;
     c->aux_order_off = (size_t)align256(4 * rows);
@@ -241,6 +244,24 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
     return 0;
 }
 
+// ALPH chunk of item i into the pinned alpha arena (extended.rs:253-308); host work in both entropy modes
+int alpha_one(webpb200_ctx* c, int i, webpb200_frame_desc& fd) {
+    WorkItem& it = c->items[i];
+    int filter = 0;
+    bool compressed = false;
+    int st = parse_alph_header(it.alph, it.alph_len, &filter, &compressed);
+    uint8_t* dst = c->h_alpha.p + fd.alpha_off;
+    const size_t want = (size_t)it.alph_w * it.alph_h, have = (size_t)fd.width * fd.height;
+    if (!st && want != have) st = WEBPB200_ERR_INCONSISTENT_SIZE;
+    if (!st) {
+        fd.alpha_filter = (uint8_t)filter;
+        if (compressed) st = vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, dst);
+        else if (it.alph_len - 1 < want) st = WEBPB200_ERR_IO;
+        else std::memcpy(dst, it.alph + 1, want);
+    }
+    return st;
+}
+
 // Part 2, per image (any host thread): the serial entropy decode into the pinned staging arrays.
 void entropy_one(webpb200_ctx* c, int i) {
     webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
@@ -252,20 +273,7 @@ void entropy_one(webpb200_ctx* c, int i) {
         webpb200_frame_desc& fd = frames[i];
         const size_t m = (size_t)fd.mbw * fd.mbh;
         int st = vp8_entropy_decode(it.vp8, it.vp8_len, &fd, hm + fd.mb_base, hl + (size_t)fd.mb_base * WEBPB200_LEVELS_PER_MB);
-        if (!st && fd.alpha_mode) {
-            int filter = 0;
-            bool compressed = false;
-            st = parse_alph_header(it.alph, it.alph_len, &filter, &compressed);
-            uint8_t* dst = c->h_alpha.p + fd.alpha_off;
-            const size_t want = (size_t)it.alph_w * it.alph_h, have = (size_t)fd.width * fd.height;
-            if (!st && want != have) st = WEBPB200_ERR_INCONSISTENT_SIZE;
-            if (!st) {
-                fd.alpha_filter = (uint8_t)filter;
-                if (compressed) st = vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, dst);
-                else if (it.alph_len - 1 < want) st = WEBPB200_ERR_IO;
-                else std::memcpy(dst, it.alph + 1, want);
-            }
-        }
+        if (!st && fd.alpha_mode) st = alpha_one(c, i, fd);
         if (st) {  // keep the slot harmless for the kernels: all-DC, all-zero macroblocks
             it.status = st;
             std::memset(hm + fd.mb_base, 0, sizeof(webpb200_mb_desc) * m);
@@ -491,6 +499,8 @@ extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
     c->sm_count = prop.multiProcessorCount;
     for (auto& e : c->ev) cudaEventCreate(&e);
     upload_tables_once();
+    upload_entropy_tables_once();
+    if (const char* e = std::getenv("WEBPB200_ENTROPY")) c->entropy_where = std::strcmp(e, "device") == 0 ? WEBPB200_ENTROPY_DEVICE : WEBPB200_ENTROPY_HOST;
     if (cudaDeviceSynchronize() != cudaSuccess) {
         delete c;
         return WEBPB200_ERR_CUDA;
@@ -503,8 +513,8 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux}) b->release();
-    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff})
+    for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status}) b->release();
+    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status})
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
@@ -521,6 +531,26 @@ extern "C" void* webpb200_host_alloc(size_t bytes) {
 }
 extern "C" void webpb200_host_free(void* p) {
     if (p) cudaFreeHost(p);
+}
+
+extern "C" int webpb200_ctx_set_entropy(webpb200_ctx* c, int where) {
+    if (!c || (where != WEBPB200_ENTROPY_HOST && where != WEBPB200_ENTROPY_DEVICE)) return -WEBPB200_ERR_INVALID_PARAM;
+    c->entropy_where = where;
+    return 0;
+}
+
+extern "C" int webpb200_batch_download_packed(webpb200_ctx* c, int image, webpb200_mb_desc* mbs, int16_t* levels) {
+    if (!c || !c->uploaded || image < 0 || image >= c->n) return -WEBPB200_ERR_INVALID_PARAM;
+    cudaSetDevice(c->device);
+    const webpb200_frame_desc& fd = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p)[image];
+    const size_t m = (size_t)fd.mbw * fd.mbh;
+    CU(c, cudaStreamSynchronize(c->stream), "sync");
+    if (m == 0) return 0;
+    if (mbs) CU(c, cudaMemcpy(mbs, c->d_mbs.p + sizeof(webpb200_mb_desc) * (size_t)fd.mb_base, sizeof(webpb200_mb_desc) * m, cudaMemcpyDeviceToHost), "D2H mbs");
+    if (levels)
+        CU(c, cudaMemcpy(levels, c->d_levels.p + sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)fd.mb_base,
+                         sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * m, cudaMemcpyDeviceToHost), "D2H levels");
+    return 0;
 }
 
 extern "C" const char* webpb200_last_cuda_error(const webpb200_ctx* c) { return c ? c->err.c_str() : ""; }
@@ -627,6 +657,109 @@ extern "C" int webpb200_batch_get_packed(webpb200_ctx* c, int image, const webpb
     return 0;
 }
 
+namespace {
+// decode_batch with the entropy stage on the device: the host reads the frame headers and stages
+// the compressed VP8 chunks; the boolean decode of macroblock headers and tokens runs in k_entropy,
+// one warp per partition, all frames of the batch side by side; then the reconstruction kernels as
+// before.  The 800 bytes per macroblock of levels are produced in HBM and never cross PCIe.
+int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
+                                const size_t* out_lens, int* status, int upsampling, int host_threads) {
+    const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+    std::vector<WorkItem> items;
+    items_from_files(files, lens, n, host_threads, &items);
+    int rc = layout_items(c, std::move(items), upsampling, host_threads, false);
+    if (rc) return rc;
+    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
+    cudaStream_t s = c->stream;
+
+    // bitstream arena: the VP8 chunks back to back (16-byte aligned starts)
+    std::vector<uint64_t> bit_off((size_t)n + 1, 0);
+    for (int i = 0; i < n; i++) bit_off[i + 1] = bit_off[i] + (c->items[i].status ? 0 : ((uint64_t)c->items[i].vp8_len + 15) & ~uint64_t(15));
+    const uint64_t bits_bytes = std::max<uint64_t>(bit_off[n], 16);
+    CU(c, c->h_bits.reserve((size_t)bits_bytes), "pinned bitstreams");
+    CU(c, c->h_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "pinned entropy headers");
+    CU(c, c->h_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "pinned status");
+    if ((rc = reserve_device(c)) != 0) return rc;
+    CU(c, c->d_bits.reserve((size_t)bits_bytes), "device bitstreams");
+    CU(c, c->d_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "device entropy headers");
+    CU(c, c->d_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "device status");
+    Vp8EntropyHdr* hdrs = reinterpret_cast<Vp8EntropyHdr*>(c->h_ehdr.p);
+
+    // clear the outputs of the entropy stage while the host parses headers
+    if (c->total_mbs) {
+        CU(c, cudaMemsetAsync(c->d_mbs.p, 0, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, s), "clear mbs");
+        CU(c, cudaMemsetAsync(c->d_levels.p, 0, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, s), "clear levels");
+    }
+    CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * (size_t)std::max(n, 1), s), "clear status");
+
+    parallel_for(n, host_threads, [&](int i) {
+        WorkItem& it = c->items[i];
+        Vp8EntropyHdr& eh = hdrs[i];
+        std::memset(&eh, 0, sizeof(eh));
+        if (it.status) return;
+        webpb200_frame_desc& fd = frames[i];
+        int st = vp8_parse_header(it.vp8, it.vp8_len, &fd, &eh);
+        if (!st) {
+            eh.data_off = bit_off[i];
+            std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
+            if (fd.alpha_mode) st = alpha_one(c, i, fd);
+        }
+        if (st) {  // the frame stays in the batch as all-DC, all-zero macroblocks nobody looks at
+            it.status = st;
+            eh.num_parts = 0;
+            fd.filter_level = 0;
+            fd.alpha_mode = 0;
+        }
+    });
+    int max_parts = 1;
+    for (int i = 0; i < n; i++) max_parts = std::max<int>(max_parts, hdrs[i].num_parts);
+    fill_row_order(frames, 0, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
+    finish_items(c);
+    const double t_host = ms_since();
+
+    CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
+    CU(c, cudaMemcpyAsync(c->d_ehdr.p, hdrs, sizeof(Vp8EntropyHdr) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D entropy headers");
+    CU(c, cudaMemcpyAsync(c->d_bits.p, c->h_bits.p, (size_t)bits_bytes, cudaMemcpyHostToDevice, s), "H2D bitstreams");
+    if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+    CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
+    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
+    if (c->total_rows) {
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
+    }
+    c->uploaded = true;
+    if (c->total_mbs) {
+        CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
+                             reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
+                             reinterpret_cast<int*>(c->d_status.p), max_parts, s), "k_entropy");
+        c->launches++;
+    }
+    // which frames ran out of bits is known only now; their pixels are not handed out
+    int* dev_status = reinterpret_cast<int*>(c->h_status.p);
+    CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
+    if ((rc = reconstruct(c, c->bd, c->alpha_bytes ? 0xF : 0x7, s, nullptr)) != 0) return rc;
+    CU(c, cudaStreamSynchronize(s), "sync");
+    const double t_kernels = ms_since();
+    for (int i = 0; i < n; i++)
+        if (!c->items[i].status && dev_status[i]) c->items[i].status = dev_status[i];
+    if ((rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
+    CU(c, cudaStreamSynchronize(s), "sync");
+    if ((rc = check_abort(c)) != 0) return rc;
+    if (trace)
+        std::fprintf(stderr, "[webpb200] decode_batch(device entropy) n=%d: host %.1f ms, +kernels %.1f ms, +download %.1f ms\n", n, t_host,
+                     t_kernels, ms_since());
+    int bad = 0;
+    for (int i = 0; i < n; i++) {
+        if (status) status[i] = c->items[i].status;
+        bad += c->items[i].status != 0;
+    }
+    return bad;
+}
+
+}  // namespace
+
 // Pipelined: the batch is cut into chunks of about kChunkMbs macroblocks; host threads entropy-
 // decode images in order, and as soon as a chunk is complete its packed arrays go to the device,
 // its kernels run and its pixels come back, all on the context's stream, while the host threads
@@ -636,6 +769,7 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
     if (n < 0) return -WEBPB200_ERR_INVALID_PARAM;
     cudaSetDevice(c->device);
+    if (c->entropy_where == WEBPB200_ENTROPY_DEVICE) return decode_batch_device_entropy(c, files, lens, n, outs, out_lens, status, upsampling, host_threads);
     const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<WorkItem> items;

@@ -1,0 +1,382 @@
+// entropy.cu -- device entropy stage: macroblock headers and coefficient tokens of VP8 keyframes
+// decoded on the GPU (sm_100a).
+//
+// What is computed is exactly host_vp8.cc's macroblock loop (reference lossy/mod.rs:615-671
+// read_macroblock_header, 785-872 read_coefficients, 874-963 read_residual_data with its
+// neighbour contexts, 1255-1281 the partition-per-row loop and the skip rule; boolean decoder
+// lossy/arithmetic_decoder.rs) with the same outputs: webpb200_mb_desc and the raw levels.
+//
+// A boolean decoder is a serial chain (every symbol needs the range and value the previous one
+// left), so nothing inside one partition runs in parallel, here or anywhere.  What the GPU has is
+// room: one block per frame, warp 0 walks the first partition (modes), warps 1..P walk the P token
+// partitions, each with ONE working lane -- a divergent 32-lane decode would serialise anyway.  A
+// batch of a thousand frames keeps a thousand such chains in flight, against one per host core,
+// and the 800 bytes per macroblock of levels never cross PCIe.
+//
+//   modes warp  -> mb_desc in global memory, `modes_done` (shared) counts finished macroblocks
+//   token warp p-> rows p, p+P, ... ; waits for modes_done > its macroblock; with P > 1 row y also
+//                  waits for row y-1 to have passed the same column (the "top" non-zero context,
+//                  mod.rs:124-129), handed over in a shared-memory ring of P+1 context rows
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "entropy.h"
+#include "kernels.cuh"
+#include "vp8_constants.h"
+
+namespace webpb200 {
+namespace {
+
+__constant__ uint8_t c_bmode_probs[900];  // [top][left][node 9], common.rs KEYFRAME_BPRED_MODE_PROBS
+__constant__ uint8_t c_zigzag[16];
+__constant__ uint8_t c_bands[17];
+
+// trees as in host_vp8.cc (common.rs:20-42, 147-172): index > 0 = node, <= 0 = -leaf
+__constant__ int8_t c_segment_tree[6] = {2, 4, -0, -1, -2, -3};
+__constant__ int8_t c_ymode_tree[8] = {-4, 2, 4, 6, -0, -1, -2, -3};
+__constant__ int8_t c_bmode_tree[18] = {-0, 2, -1, 4, -2, 6, 8, 12, -3, 10, -5, -6, -4, 14, -7, 16, -8, -9};
+__constant__ int8_t c_uvmode_tree[6] = {-0, 2, -1, 4, -2, -3};
+__constant__ uint8_t c_ymode_probs[4] = {145, 156, 163, 128};
+__constant__ uint8_t c_uvmode_probs[3] = {142, 114, 183};
+__constant__ uint8_t c_cat_probs[4][12] = {{173, 148, 140, 0}, {176, 155, 140, 135, 0}, {180, 157, 141, 134, 130, 0},
+                                           {254, 254, 243, 230, 196, 177, 153, 140, 133, 130, 129, 0}};
+__constant__ int c_cat_base[4] = {11, 19, 35, 67};
+
+// Boolean decoder, 32-bit window: `bits` + 8 bits of `value` are valid; refilled with up to three
+// bytes when bits < 0.  Symbol for symbol the host reader of host_vp8.cc.
+struct DevBool {
+    const uint8_t* base;
+    uint32_t pos, len;
+    uint32_t value, range;
+    int bits;
+    bool phantom, eof;
+
+    __device__ __forceinline__ void init(const uint8_t* data, uint32_t n) {
+        base = data; pos = 0; len = n; value = 0; range = 255; bits = -8; phantom = false; eof = false;
+    }
+    __device__ __forceinline__ void load(const uint8_t* data, uint32_t n, const BoolState& s) {
+        base = data; len = n; pos = s.pos; value = s.value; range = s.range; bits = s.bits;
+        phantom = s.phantom != 0; eof = s.eof != 0;
+    }
+    __device__ __forceinline__ void refill() {
+        const uint32_t left = len - pos;
+        if (left >= 3) {
+            const uint32_t b0 = __ldg(base + pos), b1 = __ldg(base + pos + 1), b2 = __ldg(base + pos + 2);
+            value = (value << 24) | (b0 << 16) | (b1 << 8) | b2;
+            pos += 3;
+            bits += 24;
+        } else if (left > 0) {
+            value = (value << 8) | __ldg(base + pos);
+            pos += 1;
+            bits += 8;
+        } else if (!phantom && !eof) {
+            phantom = true;
+            value <<= 8;
+            bits += 8;
+        } else {
+            eof = true;
+        }
+    }
+    __device__ __forceinline__ int get(int prob) {
+        if (bits < 0) {
+            refill();
+            if (bits < 0) return 0;
+        }
+        const uint32_t split = 1 + (((range - 1) * (uint32_t)prob) >> 8);
+        const uint32_t big = split << bits;
+        const bool one = value >= big;
+        range = one ? range - split : split;
+        value = one ? value - big : value;
+        const int shift = __clz(range) - 24;
+        range <<= shift;
+        bits -= shift;
+        return one;
+    }
+    __device__ __forceinline__ int tree(const int8_t* t, const uint8_t* probs) {
+        int i = 0;
+        do {
+            i = t[i + get(probs[i >> 1])];
+        } while (i > 0);
+        return -i;
+    }
+};
+
+// Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  probs = the
+// plane's [band][ctx][node] table in shared memory.  Returns "has coefficients".
+__device__ __forceinline__ int read_block(DevBool& br, const uint8_t* probs, int ctx, int first, int16_t* out) {
+    int n = first;
+    const uint8_t* p = probs + (c_bands[n] * 3 + ctx) * 11;
+    if (!br.get(p[0])) return 0;
+    for (;;) {
+        while (!br.get(p[1])) {
+            if (++n == 16) return 1;
+            p = probs + c_bands[n] * 33;
+        }
+        int v;
+        if (!br.get(p[2])) {
+            v = 1;
+            ctx = 1;
+        } else {
+            if (!br.get(p[3])) {
+                v = !br.get(p[4]) ? 2 : 3 + br.get(p[5]);
+            } else if (!br.get(p[6])) {
+                if (!br.get(p[7])) {
+                    v = 5 + br.get(159);
+                } else {
+                    v = 7 + 2 * br.get(165);
+                    v += br.get(145);
+                }
+            } else {
+                const int b1 = br.get(p[8]);
+                const int b0 = br.get(p[9 + b1]);
+                const int cat = 2 * b1 + b0;
+                v = 0;
+                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + br.get(*t);
+                v += c_cat_base[cat];
+            }
+            ctx = 2;
+        }
+        if (br.get(128)) v = -v;
+        out[c_zigzag[n]] = (int16_t)v;
+        if (++n == 16) return 1;
+        p = probs + (c_bands[n] * 3 + ctx) * 11;
+        if (!br.get(p[0])) return 1;
+    }
+}
+
+struct EntropyArgs {
+    const webpb200_frame_desc* frames;
+    const Vp8EntropyHdr* hdrs;
+    const uint8_t* bits;
+    webpb200_mb_desc* mbs;
+    int16_t* levels;
+    int* status;  // per frame; written only on failure
+    int frame_first;
+    int max_parts;
+    int max_mbw;
+};
+
+struct EntropyCtl {
+    int modes_done;   // macroblocks whose descriptor is in global memory
+    int abort;        // some warp hit the end of its partition: the frame is a BitStreamError
+    int row_prog[9];  // ring slot -> (row << 16) | macroblocks finished, monotone per slot
+};
+
+// spin on a shared-memory word until it reaches `need` or the frame is aborted
+__device__ __forceinline__ bool wait_shared(volatile int* word, int need, volatile int* abort) {
+    unsigned spins = 0;
+    while (*word < need) {
+        if (*abort) return false;
+        __nanosleep(64);
+        if (++spins > (1u << 26)) return false;  // about a minute: a scheduling bug, not a data property
+    }
+    __threadfence_block();
+    return true;
+}
+
+__global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    // layout: probs[1056] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
+    uint8_t* s_probs = smem;
+    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + 1056);
+    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + 1056 + 64);
+    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + 1056 + 64 + 4 * (size_t)A.max_mbw);
+
+    const int f = A.frame_first + blockIdx.x;
+    const Vp8EntropyHdr& H = A.hdrs[f];
+    const int P = H.num_parts;
+    if (P == 0) return;  // failed on the host
+    const webpb200_frame_desc& fd = A.frames[f];
+    const int mbw = fd.mbw, mbh = fd.mbh;
+
+    for (int i = threadIdx.x; i < 1056; i += blockDim.x) s_probs[i] = H.probs[i];
+    for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(ctl)[i] = 0;
+    for (int i = threadIdx.x; i < mbw; i += blockDim.x) s_top_bpred[i] = 0;
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) != 0 || warp > P) return;  // one working lane per partition
+    const uint8_t* chunk = A.bits + H.data_off;
+    webpb200_mb_desc* mbs = A.mbs + fd.mb_base;
+    volatile int* v_abort = &ctl->abort;
+    volatile int* v_modes = &ctl->modes_done;
+
+    if (warp == 0) {
+        // ---------------- macroblock headers (read_macroblock_header, mod.rs:615-671) ----------------
+        DevBool b;
+        b.load(chunk + H.first_off, H.first_len, H.first);
+        const bool update_map = H.update_map, has_skip = H.has_prob_skip;
+        const int prob_skip = H.prob_skip;
+        const uint8_t seg_probs[3] = {H.seg_probs[0], H.seg_probs[1], H.seg_probs[2]};
+        int done = 0;
+        for (int mby = 0; mby < mbh; mby++) {
+            uint32_t left = 0;  // four B modes, one per byte (row y in byte y)
+            for (int mbx = 0; mbx < mbw; mbx++) {
+                uint32_t w0 = 0, bp0 = 0, bp1 = 0;  // the descriptor's 16 bytes: {w0, nflags = 0, bp0, bp1}
+                if (update_map) {
+                    int i = 0;
+                    do {
+                        i = c_segment_tree[i + b.get(seg_probs[i >> 1])];
+                    } while (i > 0);
+                    w0 |= (uint32_t)(-i) << 16;
+                }
+                const int skipped = has_skip ? b.get(prob_skip) : 0;
+                w0 |= (uint32_t)skipped << 24;
+                const int ymode = b.tree(c_ymode_tree, c_ymode_probs);
+                w0 |= (uint32_t)ymode;
+                uint32_t top = s_top_bpred[mbx];  // column x in byte x
+                if (ymode == 4) {
+                    uint32_t nt = 0;
+#pragma unroll 1
+                    for (int y = 0; y < 4; y++) {
+                        int l = (left >> (8 * y)) & 0xff;
+                        uint32_t row = 0;
+#pragma unroll 1
+                        for (int x = 0; x < 4; x++) {
+                            const int t = (top >> (8 * x)) & 0xff;
+                            const int bm = b.tree(c_bmode_tree, c_bmode_probs + (t * 10 + l) * 9);
+                            row |= (uint32_t)bm << (8 * x);
+                            l = bm;
+                        }
+                        top = row;
+                        if (y == 3) nt = row;
+                        left = (left & ~(0xffu << (8 * y))) | ((uint32_t)l << (8 * y));
+                        // nibbles of sub-blocks 4y..4y+3
+                        const uint32_t nib = (row & 0xf) | ((row >> 4) & 0xf0) | ((row >> 8) & 0xf00) | ((row >> 12) & 0xf000);
+                        if (y < 2) bp0 |= nib << (16 * y);
+                        else bp1 |= nib << (16 * (y - 2));
+                    }
+                    s_top_bpred[mbx] = nt;
+                } else {
+                    const uint32_t m = (0x01030200u >> (8 * ymode)) & 0xff;  // DC->B_DC V->B_VE H->B_HE TM->B_TM
+                    left = m * 0x01010101u;
+                    s_top_bpred[mbx] = left;
+                }
+                w0 |= (uint32_t)b.tree(c_uvmode_tree, c_uvmode_probs) << 8;
+                if (b.eof) {
+                    A.status[f] = WEBPB200_ERR_BITSTREAM;
+                    *v_abort = 1;
+                    return;
+                }
+                *reinterpret_cast<uint4*>(mbs + (size_t)mby * mbw + mbx) = make_uint4(w0, 0u, bp0, bp1);
+                __threadfence_block();
+                *v_modes = ++done;
+            }
+        }
+        return;
+    }
+
+    // ---------------- coefficient tokens (read_residual_data, mod.rs:874-963) ----------------
+    const int p = warp - 1;
+    DevBool br;
+    br.init(chunk + H.part_off[p], H.part_len[p]);
+    int16_t* levels = A.levels + (size_t)fd.mb_base * WEBPB200_LEVELS_PER_MB;
+    const int ring = P + 1;
+    int seen_modes = 0;
+    for (int mby = p; mby < mbh; mby += P) {
+        uint16_t* cur = s_top_nz + (size_t)(mby % ring) * A.max_mbw;
+        const uint16_t* prev = s_top_nz + (size_t)((mby + ring - 1) % ring) * A.max_mbw;
+        volatile int* my_prog = &ctl->row_prog[mby % ring];
+        volatile int* up_prog = &ctl->row_prog[(mby + ring - 1) % ring];
+        uint32_t l = 0;  // left context: bit 0 Y2, 1-4 Y rows, 5-6 U rows, 7-8 V rows
+        for (int mbx = 0; mbx < mbw; mbx++) {
+            const int mbi = mby * mbw + mbx;
+            if (seen_modes <= mbi) {
+                if (!wait_shared(v_modes, mbi + 1, v_abort)) return;
+                seen_modes = *v_modes;
+            }
+            if (P > 1 && mby > 0 && !wait_shared(up_prog, ((mby - 1) << 16) | (mbx + 1), v_abort)) return;
+            uint32_t t = mby > 0 ? prev[mbx] : 0;  // top context: bit 0 Y2, 1-4 Y columns, 5-6 U, 7-8 V
+            const uint32_t w0 = *reinterpret_cast<const volatile uint32_t*>(mbs + mbi);
+            const int ymode = w0 & 0xff;
+            const bool skipped = (w0 >> 24) & 1;
+            if (skipped) {  // mod.rs:1263-1272: everything but a B macroblock's Y2 context is cleared
+                t = ymode != 4 ? 0 : (t & 1);
+                l = ymode != 4 ? 0 : (l & 1);
+            } else {
+                int16_t* lv = levels + (size_t)mbi * WEBPB200_LEVELS_PER_MB;
+                uint32_t nflags = 0;
+                int plane = 3, first = 0;
+                if (ymode != 4) {
+                    const int n = read_block(br, s_probs + 1 * 264, (t & 1) + (l & 1), 0, lv + 24 * 16);
+                    t = (t & ~1u) | n;
+                    l = (l & ~1u) | n;
+                    nflags |= (uint32_t)n << 24;
+                    plane = 0;
+                    first = 1;
+                }
+                const uint8_t* yp = s_probs + plane * 264;
+#pragma unroll 1
+                for (int y = 0; y < 4; y++) {
+                    int ll = (l >> (1 + y)) & 1;
+#pragma unroll 1
+                    for (int x = 0; x < 4; x++) {
+                        const int k = y * 4 + x;
+                        const int n = read_block(br, yp, ((t >> (1 + x)) & 1) + ll, first, lv + k * 16);
+                        nflags |= (uint32_t)n << k;
+                        ll = n;
+                        t = (t & ~(2u << x)) | ((uint32_t)n << (1 + x));
+                    }
+                    l = (l & ~(2u << y)) | ((uint32_t)ll << (1 + y));
+                }
+#pragma unroll 1
+                for (int j = 5; j <= 7; j += 2) {
+                    const int blk0 = j == 5 ? 16 : 20;
+#pragma unroll 1
+                    for (int y = 0; y < 2; y++) {
+                        int ll = (l >> (y + j)) & 1;
+#pragma unroll 1
+                        for (int x = 0; x < 2; x++) {
+                            const int k = blk0 + y * 2 + x;
+                            const int n = read_block(br, s_probs + 2 * 264, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
+                            nflags |= (uint32_t)n << k;
+                            ll = n;
+                            t = (t & ~(1u << (x + j))) | ((uint32_t)n << (x + j));
+                        }
+                        l = (l & ~(1u << (y + j))) | ((uint32_t)ll << (y + j));
+                    }
+                }
+                mbs[mbi].nflags = nflags;
+                if (br.eof) {
+                    A.status[f] = WEBPB200_ERR_BITSTREAM;
+                    *v_abort = 1;
+                    return;
+                }
+            }
+            cur[mbx] = (uint16_t)t;
+            if (P > 1) {
+                __threadfence_block();
+                *my_prog = (mby << 16) | (mbx + 1);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+void upload_entropy_tables_once() {
+    cudaMemcpyToSymbol(c_bmode_probs, kBModeProbs, sizeof(kBModeProbs));
+    cudaMemcpyToSymbol(c_zigzag, kZigzag, sizeof(kZigzag));
+    cudaMemcpyToSymbol(c_bands, kCoeffBands, sizeof(kCoeffBands));
+}
+
+size_t entropy_smem_bytes(int max_parts, int max_mbw) {
+    return 1056 + 64 + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw;
+}
+
+cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
+                           int16_t* d_levels, int* d_status, int max_parts, cudaStream_t s) {
+    if (b.n_frames <= 0) return cudaSuccess;
+    EntropyArgs a;
+    a.frames = b.frames; a.hdrs = d_hdrs; a.bits = d_bits; a.mbs = d_mbs; a.levels = d_levels; a.status = d_status;
+    a.frame_first = b.frame_first;
+    a.max_parts = max_parts;
+    a.max_mbw = (int)((b.max_w + 15) / 16);
+    const size_t smem = entropy_smem_bytes(max_parts, a.max_mbw);
+    static_assert(sizeof(EntropyCtl) <= 64, "EntropyCtl outgrew its slot");
+    k_entropy<<<b.n_frames, 32 * (1 + max_parts), smem, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace webpb200

@@ -102,6 +102,72 @@ struct BoolReader {
     }
 };
 
+// The same decoder with a 32-bit window refilled one byte at a time: slow, but its state between
+// two symbols is exactly what the device reader (entropy.cu) continues from.  Header parse only.
+struct ByteBoolReader {
+    const uint8_t* base = nullptr;
+    uint32_t pos = 0, len = 0;
+    uint32_t value = 0, range = 255;
+    int bits = -8;
+    bool phantom = false;
+    bool eof = true;
+
+    void init(const uint8_t* data, size_t n) {
+        base = data;
+        pos = 0;
+        len = (uint32_t)n;
+        value = 0;
+        range = 255;
+        bits = -8;
+        phantom = false;
+        eof = false;
+    }
+    bool refill() {
+        if (pos < len) {
+            value = (value << 8) | base[pos++];
+            bits += 8;
+            return true;
+        }
+        if (!phantom && !eof) {
+            phantom = true;
+            value <<= 8;
+            bits += 8;
+            return true;
+        }
+        eof = true;
+        return false;
+    }
+    int get(int prob) {
+        if (bits < 0 && !refill()) return 0;
+        const uint32_t split = 1 + (((range - 1) * (uint32_t)prob) >> 8);
+        const uint32_t big = split << bits;
+        int bit;
+        if (value >= big) {
+            range -= split;
+            value -= big;
+            bit = 1;
+        } else {
+            range = split;
+            bit = 0;
+        }
+        const int shift = __builtin_clz(range) - 24;
+        range <<= shift;
+        bits -= shift;
+        return bit;
+    }
+    int flag() { return get(128); }
+    int literal(int n) {
+        int v = 0;
+        while (n-- > 0) v = (v << 1) | flag();
+        return v;
+    }
+    int opt_signed(int n) {
+        if (!flag()) return 0;
+        int m = literal(n);
+        return flag() ? -m : m;
+    }
+};
+
 const int8_t kSegmentTree[6] = {2, 4, -0, -1, -2, -3};
 const int8_t kYModeTree[8] = {-4, 2, 4, 6, -0, -1, -2, -3};
 const int8_t kBModeTree[18] = {-0, 2, -1, 4, -2, 6, 8, 12, -3, 10, -5, -6, -4, 14, -7, 16, -8, -9};
@@ -183,9 +249,21 @@ int vp8_probe(const uint8_t* d, size_t len, Vp8Dims* dims) {
     return WEBPB200_OK;
 }
 
-int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
-                       int16_t* levels) {
-    Vp8Dims dims;
+namespace {
+
+struct HeaderFields {  // what the macroblock loop needs from the frame header
+    bool segments_enabled = false, update_map = false;
+    uint8_t seg_probs[3] = {255, 255, 255};
+    int num_parts = 1;
+    size_t first_off = 0, first_len = 0;
+    size_t part_off[8] = {}, part_len[8] = {};
+    uint8_t probs[1056];
+    int prob_skip = -1;
+};
+
+// Frame tag to mb_no_coeff_skip (mod.rs:510-613), with reader `b` left at the first macroblock.
+template <class Reader>
+int parse_frame_header(const uint8_t* d, size_t len, Reader& b, webpb200_frame_desc* fd, Vp8Dims& dims, HeaderFields& h) {
     int st = vp8_probe(d, len, &dims);
     if (st) return st;
     const uint32_t tag = d[0] | (d[1] << 8) | ((uint32_t)d[2] << 16);
@@ -193,8 +271,9 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
     size_t pos = 10;
     if (len - pos < first_size) return WEBPB200_ERR_IO;
 
-    BoolReader b;
     b.init(d + pos, first_size);
+    h.first_off = pos;
+    h.first_len = first_size;
     pos += first_size;
 
     fd->width = (uint16_t)dims.width;
@@ -211,21 +290,20 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
         bool delta = false;
         int quant = 0, lf = 0;
     } seg[4];
-    uint8_t seg_probs[3] = {255, 255, 255};
-    bool update_map = false;
     const bool segments_enabled = b.flag();
     if (segments_enabled) {  // read_segment_updates, 469-508
-        update_map = b.flag();
+        h.update_map = b.flag();
         if (b.flag()) {
             const bool absolute = b.flag();
             for (auto& s : seg) s.delta = !absolute;
             for (auto& s : seg) s.quant = (int8_t)b.opt_signed(7);
             for (auto& s : seg) s.lf = (int8_t)b.opt_signed(6);
         }
-        if (update_map)
-            for (int i = 0; i < 3; i++) seg_probs[i] = b.flag() ? (uint8_t)b.literal(8) : 255;
+        if (h.update_map)
+            for (int i = 0; i < 3; i++) h.seg_probs[i] = b.flag() ? (uint8_t)b.literal(8) : 255;
         if (b.eof) return WEBPB200_ERR_BITSTREAM;
     }
+    h.segments_enabled = segments_enabled;
     fd->segments_enabled = segments_enabled;
     fd->filter_type = (uint8_t)b.flag();
     fd->filter_level = (uint8_t)b.literal(6);
@@ -244,9 +322,9 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
     fd->mode_delta0 = (int8_t)mode_delta[0];
     const int num_parts = 1 << b.literal(2);
     if (b.eof) return WEBPB200_ERR_BITSTREAM;
+    h.num_parts = num_parts;
 
     // ---- token partitions (init_partitions, 369-395) ----
-    BoolReader parts[8];
     if (num_parts > 1) {
         const size_t table = 3 * (size_t)(num_parts - 1);
         if (len - pos < table) return WEBPB200_ERR_IO;
@@ -255,11 +333,13 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
         for (int i = 0; i < num_parts - 1; i++) {
             size_t s = sz[3 * i] | (sz[3 * i + 1] << 8) | ((size_t)sz[3 * i + 2] << 16);
             if (len - pos < s) return WEBPB200_ERR_IO;
-            parts[i].init(d + pos, s);
+            h.part_off[i] = pos;
+            h.part_len[i] = s;
             pos += s;
         }
     }
-    parts[num_parts - 1].init(d + pos, len - pos);
+    h.part_off[num_parts - 1] = pos;
+    h.part_len[num_parts - 1] = len - pos;
 
     // ---- quantiser indices (read_quantization_indices, 397-451) ----
     {
@@ -290,16 +370,59 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
     (void)b.literal(1);  // refresh-entropy bit, ignored (599-600)
 
     // ---- token probabilities (update_token_probabilities, 352-367) ----
-    uint8_t probs_flat[1056];
-    std::memcpy(probs_flat, kCoeffProbsDefault, sizeof(probs_flat));
+    std::memcpy(h.probs, kCoeffProbsDefault, sizeof(h.probs));
     for (int i = 0; i < 1056; i++)
-        if (b.get(kCoeffUpdateProbs[i])) probs_flat[i] = (uint8_t)b.literal(8);
+        if (b.get(kCoeffUpdateProbs[i])) h.probs[i] = (uint8_t)b.literal(8);
     if (b.eof) return WEBPB200_ERR_BITSTREAM;
-    const TokenProbs* probs = reinterpret_cast<const TokenProbs*>(probs_flat);  // [plane]
 
-    int prob_skip = -1;
-    if (b.literal(1) == 1) prob_skip = b.literal(8);
+    if (b.literal(1) == 1) h.prob_skip = b.literal(8);
     if (b.eof) return WEBPB200_ERR_BITSTREAM;
+    return WEBPB200_OK;
+}
+
+}  // namespace
+
+int vp8_parse_header(const uint8_t* d, size_t len, webpb200_frame_desc* fd, Vp8EntropyHdr* eh) {
+    Vp8Dims dims;
+    HeaderFields h;
+    ByteBoolReader b;
+    std::memset(eh, 0, sizeof(*eh));
+    const int st = parse_frame_header(d, len, b, fd, dims, h);
+    if (st) return st;
+    eh->first_off = (uint32_t)h.first_off;
+    eh->first_len = (uint32_t)h.first_len;
+    for (int i = 0; i < 8; i++) {
+        eh->part_off[i] = (uint32_t)h.part_off[i];
+        eh->part_len[i] = (uint32_t)h.part_len[i];
+    }
+    eh->first.pos = b.pos;
+    eh->first.value = b.value;
+    eh->first.range = b.range;
+    eh->first.bits = b.bits;
+    eh->first.phantom = b.phantom;
+    eh->first.eof = b.eof;
+    eh->num_parts = (uint8_t)h.num_parts;
+    eh->update_map = h.segments_enabled && h.update_map;
+    eh->has_prob_skip = h.prob_skip >= 0;
+    eh->prob_skip = (uint8_t)(h.prob_skip >= 0 ? h.prob_skip : 0);
+    std::memcpy(eh->seg_probs, h.seg_probs, 3);
+    std::memcpy(eh->probs, h.probs, sizeof(eh->probs));
+    return WEBPB200_OK;
+}
+
+int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
+                       int16_t* levels) {
+    Vp8Dims dims;
+    HeaderFields h;
+    BoolReader b;
+    const int st = parse_frame_header(d, len, b, fd, dims, h);
+    if (st) return st;
+    const bool segments_enabled = h.segments_enabled, update_map = h.update_map;
+    const uint8_t* seg_probs = h.seg_probs;
+    const int num_parts = h.num_parts, prob_skip = h.prob_skip;
+    BoolReader parts[8];
+    for (int i = 0; i < num_parts; i++) parts[i].init(d + h.part_off[i], h.part_len[i]);
+    const TokenProbs* probs = reinterpret_cast<const TokenProbs*>(h.probs);  // [plane]
 
     // ---- macroblocks (decode_frame_, 1255-1281) ----
     const int mbw = dims.mbw, mbh = dims.mbh;

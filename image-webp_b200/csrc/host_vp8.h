@@ -6,6 +6,7 @@
 #include <cstdint>
 
 #include "../../include/webpb200.h"
+#include "entropy.h"
 
 namespace webpb200 {
 
@@ -25,5 +26,10 @@ int vp8_probe(const uint8_t* data, size_t len, Vp8Dims* dims);
 //   levels <- mbw*mbh*400 raw token values (this function zero-fills them)
 int vp8_entropy_decode(const uint8_t* data, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
                        int16_t* levels);
+
+// The header half of vp8_entropy_decode alone, for the device entropy stage: frame-level fields
+// into fd as above, and into eh the partition layout, token probabilities and the state of the
+// first partition's boolean decoder at the first macroblock (eh->data_off is the caller's).
+int vp8_parse_header(const uint8_t* data, size_t len, webpb200_frame_desc* fd, Vp8EntropyHdr* eh);
 
 }  // namespace webpb200

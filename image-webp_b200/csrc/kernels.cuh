@@ -5,6 +5,7 @@
 #include <cstdint>
 
 #include "../../include/webpb200.h"
+#include "entropy.h"
 
 namespace webpb200 {
 
@@ -59,6 +60,13 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s);
 cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s);
 // ALPH un-filter + merge into byte 3 of the RGBA output; adds its launch count to *launches
 cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches);
+
+// device entropy stage (entropy.cu): macroblock headers + coefficient tokens of frames
+// [b.frame_first, +b.n_frames) from the staged bitstreams into d_mbs / d_levels (both cleared by
+// the caller); d_status[frame] is set to WEBPB200_ERR_BITSTREAM for a frame that ran out of bits
+void upload_entropy_tables_once();
+cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
+                           int16_t* d_levels, int* d_status, int max_parts, cudaStream_t s);
 
 struct CompositeArgs {  // one composite_frame call, reference extended.rs:30-129
     uint8_t* canvas;       // canvas_w * canvas_h * 4, device

@@ -150,6 +150,20 @@ const char* webpb200_last_cuda_error(const webpb200_ctx* c);
 void* webpb200_host_alloc(size_t bytes);
 void webpb200_host_free(void* p);
 
+/* Where webpb200_decode_batch runs the boolean-entropy decode of macroblock headers and
+ * coefficient tokens (lossy/mod.rs:615-671, 785-963; arithmetic_decoder.rs):
+ *   HOST   one frame per host thread, packed levels copied to the device (the default);
+ *   DEVICE one warp per bitstream partition on the GPU, all frames of the batch side by side;
+ *          only the compressed chunks cross PCIe.  Same results, bit for bit.
+ * The default can also be set with the environment variable WEBPB200_ENTROPY=host|device. */
+#define WEBPB200_ENTROPY_HOST 0
+#define WEBPB200_ENTROPY_DEVICE 1
+int webpb200_ctx_set_entropy(webpb200_ctx* c, int where);
+/* After a decode_batch / batch_upload: copies one image's macroblock descriptors and levels as
+ * the device holds them (mbw*mbh descriptors, mbw*mbh*400 levels) -- for parity tests of the
+ * device entropy stage against webpb200_host_entropy_decode. */
+int webpb200_batch_download_packed(webpb200_ctx* c, int image, webpb200_mb_desc* mbs, int16_t* levels);
+
 /* N x (WebPDecoder::new + read_image) for still lossy files: host parse and entropy decode
  * on `host_threads` threads, upload, reconstruct, download into outs[i] (out_lens[i] must be
  * width*height*(3|4)).  status[i] gets each file's own code; a bad file does not poison the

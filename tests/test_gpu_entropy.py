@@ -1,0 +1,114 @@
+"""Device entropy stage (k_entropy) against the host entropy decoder and the CPU oracle.
+
+The stage replaces, on the GPU, the boolean decode of macroblock headers and coefficient tokens
+(reference lossy/mod.rs:615-671, 785-963, 1255-1281).  Its outputs are integers: every comparison
+is bit-exact -- macroblock descriptors and levels against webpb200_host_entropy_decode, pixels
+against the oracle, statuses of damaged streams against the host path.
+"""
+import numpy as np
+import pytest
+
+from util import LOSSY_STILL, SYNTH_CASES, product
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def W():
+    w = product()
+    w.lib()
+    assert w.device_count() > 0, "no CUDA device"
+    return w
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from harness import synth as S
+    S.build()
+    return S
+
+
+@pytest.fixture()
+def dev(W):
+    b = W.BatchDecoder(0)
+    b.set_entropy(b.ENTROPY_DEVICE)
+    yield b
+    b.close()
+
+
+@pytest.fixture()
+def host(W):
+    b = W.BatchDecoder(0)
+    b.set_entropy(b.ENTROPY_HOST)
+    yield b
+    b.close()
+
+
+def _check_packed(W, dev, files, status):
+    for i, f in enumerate(files):
+        if status[i]:
+            continue
+        fd, mbs, levels, _ = W.host_entropy_decode(f)
+        dm, dl = dev.device_packed(i, fd)
+        assert np.array_equal(dm, mbs), "macroblock descriptors of image %d" % i
+        assert np.array_equal(dl, levels), "levels of image %d" % i
+
+
+def test_golden_files(W, dev, fixtures, oracle):
+    files = [bytes(fixtures["webp/" + k]) for k in LOSSY_STILL]
+    outs, status = dev.decode(files)
+    assert status == [0] * len(files)
+    _check_packed(W, dev, files, status)
+    for f, o in zip(files, outs):
+        assert np.array_equal(o, oracle.WebPDecoder(f).read_image())
+
+
+def test_synthetic_features(W, dev, synth, oracle):
+    """Every feature no fixture covers: partitions 1/2/4/8, segment maps, skip flags, probability
+    updates, CAT6 extremes, all-skipped frames, 1x1, one-row and one-column frames."""
+    files = [synth.webp_simple(synth.vp8_frame(**kw)) for kw in SYNTH_CASES.values()]
+    outs, status = dev.decode(files)
+    assert status == [0] * len(files)
+    _check_packed(W, dev, files, status)
+    for name, f, o in zip(SYNTH_CASES, files, outs):
+        assert np.array_equal(o, oracle.WebPDecoder(f).read_image()), name
+
+
+def test_alpha_and_mixed_partitions(W, dev, synth, oracle):
+    w, h = 96, 80
+    files = [synth.webp_extended(synth.vp8_frame(w, h, seed=20 + k, filter_type=0, filter_level=9, log2_parts=k % 4), w, h,
+                                 synth.alph_raw(synth.smooth_alpha(w, h, k), filtering=k % 4)) for k in range(8)]
+    files += [synth.webp_simple(synth.vp8_frame(200, 120, seed=40 + k, log2_parts=3 - k % 4)) for k in range(4)]
+    outs, status = dev.decode(files)
+    assert status == [0] * len(files)
+    _check_packed(W, dev, files, status)
+    for f, o in zip(files, outs):
+        assert np.array_equal(o, oracle.WebPDecoder(f).read_image())
+
+
+def test_damaged_streams_match_host(W, dev, host, synth):
+    """Truncations at every kind of place (header, first partition, partition table, tokens): the
+    per-image status must equal the host path's, and intact neighbours must be unaffected."""
+    good = synth.webp_simple(synth.vp8_frame(160, 160, seed=4, filter_type=0, filter_level=12, log2_parts=3, prob_skip=180, p_skip=0.2))
+    small = synth.webp_simple(synth.vp8_frame(64, 48, seed=9))
+    cuts = [len(good) - 1, len(good) - 2, len(good) - 40, len(good) * 3 // 4, len(good) // 2, len(good) // 3, 400, 120, 60, 40, 31, 25]
+    files = [good] + [good[:c] for c in cuts] + [small] + [small[:c] for c in (len(small) - 1, len(small) - 3, len(small) // 2, 50)]
+    # RIFF sizes are left stale on purpose: the container walk decides what is readable, as in the reference
+    o_dev, s_dev = dev.decode(files)
+    o_host, s_host = host.decode(files)
+    assert s_dev == s_host
+    assert s_dev[0] == 0 and any(s_dev)
+    for a, b, st in zip(o_dev, o_host, s_dev):
+        if st == 0:
+            assert np.array_equal(a, b)
+
+
+def test_batch_scale_checksum(W, dev, host, synth):
+    """256 cfg2-profile images: device-entropy pixels == host-entropy pixels, image by image."""
+    files = synth.make_batch(synth.cfg2_image, 256)
+    o_dev, s_dev = dev.decode(files)
+    o_host, s_host = host.decode(files)
+    assert s_dev == s_host == [0] * len(files)
+    for i, (a, b) in enumerate(zip(o_dev, o_host)):
+        assert np.array_equal(a, b), i
+    _check_packed(W, dev, files[:4], s_dev[:4])

@@ -19,3 +19,7 @@ for th in (os.cpu_count(),):
     for _ in range(3):
         t = time.perf_counter(); bd.decode(files, outs=outs, host_threads=th); dt = time.perf_counter() - t
         print("threads %d: %.1f ms -> %.0f MPix/s" % (th, dt * 1e3, n * 512 * 512 / dt / 1e6), flush=True)
+bd.set_entropy(bd.ENTROPY_DEVICE)
+for _ in range(4):
+    t = time.perf_counter(); bd.decode(files, outs=outs, host_threads=th); dt = time.perf_counter() - t
+    print("device entropy: %.1f ms -> %.0f MPix/s" % (dt * 1e3, n * 512 * 512 / dt / 1e6), flush=True)
