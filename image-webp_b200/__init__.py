@@ -386,7 +386,7 @@ class BatchDecoder:
         levels = np.ctypeslib.as_array(l, shape=(n, 25, 16)).copy() if n else np.zeros((0, 25, 16), np.int16)
         return fd, mbs, levels
 
-    ENTROPY_HOST, ENTROPY_DEVICE = 0, 1
+    ENTROPY_HOST, ENTROPY_DEVICE, ENTROPY_AUTO = 0, 1, 2
 
     def set_entropy(self, where):
         """Where decode() runs the boolean-entropy decode: ENTROPY_HOST (threads) or ENTROPY_DEVICE (k_entropy)."""

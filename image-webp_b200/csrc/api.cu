@@ -116,7 +116,7 @@ struct webpb200_ctx {
     uint64_t launches = 0;
 
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
-    int entropy_where = 0;  // WEBPB200_ENTROPY_HOST / _DEVICE: where decode_batch runs the boolean decode
+    int entropy_where = WEBPB200_ENTROPY_AUTO;  // WEBPB200_ENTROPY_*: where decode_batch runs the boolean decode
     DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status;
 
     // current batch
@@ -500,7 +500,7 @@ extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
     for (auto& e : c->ev) cudaEventCreate(&e);
     upload_tables_once();
     upload_entropy_tables_once();
-    if (const char* e = std::getenv("WEBPB200_ENTROPY")) c->entropy_where = std::strcmp(e, "device") == 0 ? WEBPB200_ENTROPY_DEVICE : WEBPB200_ENTROPY_HOST;
+    if (const char* e = std::getenv("WEBPB200_ENTROPY")) c->entropy_where = std::strcmp(e, "device") == 0 ? WEBPB200_ENTROPY_DEVICE : std::strcmp(e, "host") == 0 ? WEBPB200_ENTROPY_HOST : WEBPB200_ENTROPY_AUTO;
     if (cudaDeviceSynchronize() != cudaSuccess) {
         delete c;
         return WEBPB200_ERR_CUDA;
@@ -534,7 +534,7 @@ extern "C" void webpb200_host_free(void* p) {
 }
 
 extern "C" int webpb200_ctx_set_entropy(webpb200_ctx* c, int where) {
-    if (!c || (where != WEBPB200_ENTROPY_HOST && where != WEBPB200_ENTROPY_DEVICE)) return -WEBPB200_ERR_INVALID_PARAM;
+    if (!c || where < WEBPB200_ENTROPY_HOST || where > WEBPB200_ENTROPY_AUTO) return -WEBPB200_ERR_INVALID_PARAM;
     c->entropy_where = where;
     return 0;
 }
@@ -658,6 +658,8 @@ extern "C" int webpb200_batch_get_packed(webpb200_ctx* c, int image, const webpb
 }
 
 namespace {
+constexpr int kPreferHostEntropy = 1 << 30;  // internal: the cost model of the AUTO mode chose the host
+
 // decode_batch with the entropy stage on the device: the host reads the frame headers and stages
 // the compressed VP8 chunks; the boolean decode of macroblock headers and tokens runs in k_entropy,
 // one warp per partition, all frames of the batch side by side; then the reconstruction kernels as
@@ -694,27 +696,44 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     }
     CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * (size_t)std::max(n, 1), s), "clear status");
 
+    auto drop = [&](int i, int st) {  // the frame stays in the batch as all-DC, all-zero macroblocks nobody looks at
+        c->items[i].status = st;
+        hdrs[i].num_parts = 0;
+        frames[i].filter_level = 0;
+        frames[i].alpha_mode = 0;
+    };
     parallel_for(n, host_threads, [&](int i) {
         WorkItem& it = c->items[i];
         Vp8EntropyHdr& eh = hdrs[i];
         std::memset(&eh, 0, sizeof(eh));
         if (it.status) return;
-        webpb200_frame_desc& fd = frames[i];
-        int st = vp8_parse_header(it.vp8, it.vp8_len, &fd, &eh);
-        if (!st) {
-            eh.data_off = bit_off[i];
-            std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
-            if (fd.alpha_mode) st = alpha_one(c, i, fd);
-        }
-        if (st) {  // the frame stays in the batch as all-DC, all-zero macroblocks nobody looks at
-            it.status = st;
-            eh.num_parts = 0;
-            fd.filter_level = 0;
-            fd.alpha_mode = 0;
-        }
+        const int st = vp8_parse_header(it.vp8, it.vp8_len, &frames[i], &eh);
+        if (st) drop(i, st);
+        eh.data_off = bit_off[i];
     });
     int max_parts = 1;
     for (int i = 0; i < n; i++) max_parts = std::max<int>(max_parts, hdrs[i].num_parts);
+    if (c->entropy_where == WEBPB200_ENTROPY_AUTO) {
+        // The device decodes every partition of every frame at once but each one slowly (one lane,
+        // about 38 us per macroblock on B200); the host decodes fast (about 3 us per macroblock)
+        // but only one frame per thread.  Many small frames: device.  A few large ones: host.
+        double longest = 0, streams = 0;
+        for (int i = 0; i < n; i++)
+            if (hdrs[i].num_parts) {
+                longest = std::max(longest, (double)frames[i].mbw * frames[i].mbh / hdrs[i].num_parts);
+                streams += hdrs[i].num_parts;
+            }
+        const double est_device_us = longest * 38.0 * std::max(1.0, streams / 1184.0);
+        const double est_host_us = (double)c->total_mbs * 3.0 / std::max(1, std::min(host_threads, n));
+        if (est_device_us > est_host_us) return kPreferHostEntropy;
+    }
+    parallel_for(n, host_threads, [&](int i) {  // stage the compressed chunks; ALPH planes are host work in both modes
+        WorkItem& it = c->items[i];
+        if (it.status) return;
+        std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
+        if (frames[i].alpha_mode)
+            if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
+    });
     fill_row_order(frames, 0, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
     finish_items(c);
     const double t_host = ms_since();
@@ -730,12 +749,14 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
     }
     c->uploaded = true;
+    if (trace) cudaEventRecord(c->ev[5], s);
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
                              reinterpret_cast<int*>(c->d_status.p), max_parts, s), "k_entropy");
         c->launches++;
     }
+    if (trace) cudaEventRecord(c->ev[6], s);
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
@@ -747,9 +768,12 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     if ((rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
     if ((rc = check_abort(c)) != 0) return rc;
-    if (trace)
-        std::fprintf(stderr, "[webpb200] decode_batch(device entropy) n=%d: host %.1f ms, +kernels %.1f ms, +download %.1f ms\n", n, t_host,
-                     t_kernels, ms_since());
+    if (trace) {
+        float ems = 0;
+        cudaEventElapsedTime(&ems, c->ev[5], c->ev[6]);
+        std::fprintf(stderr, "[webpb200] decode_batch(device entropy) n=%d: host %.1f ms, +kernels %.1f ms (k_entropy %.2f ms), +download %.1f ms\n",
+                     n, t_host, t_kernels, ems, ms_since());
+    }
     int bad = 0;
     for (int i = 0; i < n; i++) {
         if (status) status[i] = c->items[i].status;
@@ -769,7 +793,10 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
     if (n < 0) return -WEBPB200_ERR_INVALID_PARAM;
     cudaSetDevice(c->device);
-    if (c->entropy_where == WEBPB200_ENTROPY_DEVICE) return decode_batch_device_entropy(c, files, lens, n, outs, out_lens, status, upsampling, host_threads);
+    if (c->entropy_where != WEBPB200_ENTROPY_HOST) {
+        const int r = decode_batch_device_entropy(c, files, lens, n, outs, out_lens, status, upsampling, host_threads);
+        if (r != kPreferHostEntropy) return r;
+    }
     const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<WorkItem> items;

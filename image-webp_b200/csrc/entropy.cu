@@ -25,12 +25,27 @@
 #include "kernels.cuh"
 #include "vp8_constants.h"
 
+// Build-time variants for A/B timing (tools/ab_build.sh); the defaults are the measured best.
+#ifndef ENT_TWO_FLO
+#define ENT_TWO_FLO 0    // normalisation shifts of both outcomes computed beside the comparison
+#endif
+#ifndef ENT_REG_ROWS
+#define ENT_REG_ROWS 0   // probability row of a coefficient held in registers (one LDS.128) instead of a byte load per symbol
+#endif
+#ifndef ENT_HEAD4
+#define ENT_HEAD4 0      // the four probabilities most tokens need (EOB, zero, one, small) come in one 32-bit load
+#endif
+#ifndef ENT_ONE_SITE
+#define ENT_ONE_SITE 1   // one inlined copy of the block decoder (25-block loop) instead of three: less code to fetch
+#endif
+#ifndef ENT_PREFETCH
+#define ENT_PREFETCH 0   // bitstream bytes requested one refill ahead
+#endif
+
 namespace webpb200 {
 namespace {
 
 __constant__ uint8_t c_bmode_probs[900];  // [top][left][node 9], common.rs KEYFRAME_BPRED_MODE_PROBS
-__constant__ uint8_t c_zigzag[16];
-__constant__ uint8_t c_bands[17];
 
 // trees as in host_vp8.cc (common.rs:20-42, 147-172): index > 0 = node, <= 0 = -leaf
 __constant__ int8_t c_segment_tree[6] = {2, 4, -0, -1, -2, -3};
@@ -45,28 +60,48 @@ __constant__ int c_cat_base[4] = {11, 19, 35, 67};
 
 // Boolean decoder, 32-bit window: `bits` + 8 bits of `value` are valid; refilled with up to three
 // bytes when bits < 0.  Symbol for symbol the host reader of host_vp8.cc.
+//
+// One lane runs this alone, so what counts is the length of the dependent chain per symbol
+// (measured on B200, tools/micro/latbench.cu: ALU op 4-5 cycles, FLO 17, LDS 30, taken branch 15):
+// the normalisation shifts of both outcomes are computed next to the comparison instead of after
+// it, and the next three bytes are requested one refill ahead so that their latency is never waited for.
 struct DevBool {
     const uint8_t* base;
     uint32_t pos, len;
     uint32_t value, range;
     int bits;
-    bool phantom, eof;
+    uint32_t n0, n1, n2;  // bytes pos .. pos+2, requested at the previous refill (valid if pre)
+    bool pre, phantom, eof;
 
+    __device__ __forceinline__ void request() {
+        pre = ENT_PREFETCH && len - pos >= 3;
+        if (pre) {
+            n0 = __ldg(base + pos);
+            n1 = __ldg(base + pos + 1);
+            n2 = __ldg(base + pos + 2);
+        }
+    }
     __device__ __forceinline__ void init(const uint8_t* data, uint32_t n) {
         base = data; pos = 0; len = n; value = 0; range = 255; bits = -8; phantom = false; eof = false;
+        request();
     }
     __device__ __forceinline__ void load(const uint8_t* data, uint32_t n, const BoolState& s) {
         base = data; len = n; pos = s.pos; value = s.value; range = s.range; bits = s.bits;
         phantom = s.phantom != 0; eof = s.eof != 0;
+        request();
     }
     __device__ __forceinline__ void refill() {
-        const uint32_t left = len - pos;
-        if (left >= 3) {
+        if (pre) {
+            value = (value << 24) | (n0 << 16) | (n1 << 8) | n2;
+            pos += 3;
+            bits += 24;
+            request();
+        } else if (!ENT_PREFETCH && len - pos >= 3) {
             const uint32_t b0 = __ldg(base + pos), b1 = __ldg(base + pos + 1), b2 = __ldg(base + pos + 2);
             value = (value << 24) | (b0 << 16) | (b1 << 8) | b2;
             pos += 3;
             bits += 24;
-        } else if (left > 0) {
+        } else if (pos < len) {
             value = (value << 8) | __ldg(base + pos);
             pos += 1;
             bits += 8;
@@ -78,71 +113,146 @@ struct DevBool {
             eof = true;
         }
     }
-    __device__ __forceinline__ int get(int prob) {
+    __device__ __forceinline__ bool get(uint32_t prob) {
         if (bits < 0) {
             refill();
-            if (bits < 0) return 0;
+            if (bits < 0) return false;
         }
-        const uint32_t split = 1 + (((range - 1) * (uint32_t)prob) >> 8);
+        const uint32_t split = (range * prob + (256u - prob)) >> 8;  // = 1 + (((range - 1) * prob) >> 8)
+        const uint32_t rest = range - split;                         // >= 1
         const uint32_t big = split << bits;
         const bool one = value >= big;
-        range = one ? range - split : split;
-        value = one ? value - big : value;
-        const int shift = __clz(range) - 24;
-        range <<= shift;
-        bits -= shift;
+        value -= one ? big : 0u;
+#if ENT_TWO_FLO
+        const int s0 = __clz(split) - 24, s1 = __clz(rest) - 24;
+        range = one ? rest << s1 : split << s0;
+        bits -= one ? s1 : s0;
+#else
+        const uint32_t r = one ? rest : split;
+        const int sh = __clz(r) - 24;
+        range = r << sh;
+        bits -= sh;
+#endif
         return one;
     }
     __device__ __forceinline__ int tree(const int8_t* t, const uint8_t* probs) {
         int i = 0;
         do {
-            i = t[i + get(probs[i >> 1])];
+            i = t[i + (int)get(probs[i >> 1])];
         } while (i > 0);
         return -i;
     }
 };
 
-// Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  probs = the
-// plane's [band][ctx][node] table in shared memory.  Returns "has coefficients".
-__device__ __forceinline__ int read_block(DevBool& br, const uint8_t* probs, int ctx, int first, int16_t* out) {
+// COEFF_BANDS and ZIGZAG (common.rs) as nibble tables in immediates: no table load on the chain
+__device__ __forceinline__ uint32_t band_of(int n) { return ((n < 8 ? 0x65463210u : 0x76666666u) >> ((n & 7) * 4)) & 7u; }
+__device__ __forceinline__ uint32_t zigzag_of(int n) { return ((n < 8 ? 0x63258410u : 0xFEB7ADC9u) >> ((n & 7) * 4)) & 15u; }
+
+// one [band][ctx] row of token probabilities, 11 bytes padded to 16, held in registers
+__device__ __forceinline__ uint32_t prob_at(const uint4& r, int k) {
+    const uint32_t w = k < 4 ? r.x : k < 8 ? r.y : r.z;
+    return (w >> (8 * (k & 3))) & 0xffu;
+}
+
+// Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  rows = the plane's
+// [band][ctx] probability rows in shared memory.  The row of the next coefficient is requested as
+// soon as its context is known (before the sign and the extra bits are decoded), and the row a
+// zero token would lead to is requested ahead, so no shared-memory latency sits between symbols.
+// Returns "has coefficients".
+__device__ __forceinline__ int read_block(DevBool& br, const uint4* rows, int ctx, int first, int16_t* out) {
+#if ENT_REG_ROWS
     int n = first;
-    const uint8_t* p = probs + (c_bands[n] * 3 + ctx) * 11;
-    if (!br.get(p[0])) return 0;
+    uint4 row = rows[band_of(n) * 3 + ctx];
+    if (!br.get(prob_at(row, 0))) return 0;  // DCT_EOB straight away
     for (;;) {
-        while (!br.get(p[1])) {
+        uint4 zrow = rows[band_of(n + 1) * 3];
+        while (!br.get(prob_at(row, 1))) {  // DCT_0: no EOB test before the next token
             if (++n == 16) return 1;
-            p = probs + c_bands[n] * 33;
+            row = zrow;
+            zrow = rows[band_of(n + 1) * 3];
         }
         int v;
-        if (!br.get(p[2])) {
+        uint4 nrow;
+        if (!br.get(prob_at(row, 2))) {
+            nrow = rows[band_of(n + 1) * 3 + 1];
+            v = 1;
+        } else {
+            nrow = rows[band_of(n + 1) * 3 + 2];
+            if (!br.get(prob_at(row, 3))) {
+                v = !br.get(prob_at(row, 4)) ? 2 : 3 + (int)br.get(prob_at(row, 5));
+            } else if (!br.get(prob_at(row, 6))) {
+                if (!br.get(prob_at(row, 7))) {
+                    v = 5 + (int)br.get(159);
+                } else {
+                    v = 7 + 2 * (int)br.get(165);
+                    v += (int)br.get(145);
+                }
+            } else {
+                const int b1 = br.get(prob_at(row, 8));
+                const int b0 = br.get(b1 ? prob_at(row, 10) : prob_at(row, 9));
+                const int cat = 2 * b1 + b0;
+                v = 0;
+                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get(*t);
+                v += c_cat_base[cat];
+            }
+        }
+        if (br.get(128)) v = -v;
+        out[zigzag_of(n)] = (int16_t)v;
+        if (++n == 16) return 1;
+        row = nrow;
+        if (!br.get(prob_at(row, 0))) return 1;  // DCT_EOB
+    }
+#else
+    const uint8_t* probs = reinterpret_cast<const uint8_t*>(rows);
+    int n = first;
+    const uint8_t* p = probs + (band_of(n) * 3 + ctx) * 16;
+#if ENT_HEAD4
+    uint32_t h4 = *reinterpret_cast<const uint32_t*>(p);
+#define HEAD(k) ((h4 >> (8 * (k))) & 0xffu)
+#define NEXT_ROW(q) (p = (q), h4 = *reinterpret_cast<const uint32_t*>(p))
+#else
+#define HEAD(k) p[k]
+#define NEXT_ROW(q) (p = (q))
+#endif
+    if (!br.get(HEAD(0))) return 0;
+    for (;;) {
+        while (!br.get(HEAD(1))) {
+            if (++n == 16) return 1;
+            NEXT_ROW(probs + band_of(n) * 48);
+        }
+        int v;
+        if (!br.get(HEAD(2))) {
             v = 1;
             ctx = 1;
         } else {
-            if (!br.get(p[3])) {
-                v = !br.get(p[4]) ? 2 : 3 + br.get(p[5]);
+            if (!br.get(HEAD(3))) {
+                v = !br.get(p[4]) ? 2 : 3 + (int)br.get(p[5]);
             } else if (!br.get(p[6])) {
                 if (!br.get(p[7])) {
-                    v = 5 + br.get(159);
+                    v = 5 + (int)br.get(159);
                 } else {
-                    v = 7 + 2 * br.get(165);
-                    v += br.get(145);
+                    v = 7 + 2 * (int)br.get(165);
+                    v += (int)br.get(145);
                 }
             } else {
                 const int b1 = br.get(p[8]);
                 const int b0 = br.get(p[9 + b1]);
                 const int cat = 2 * b1 + b0;
                 v = 0;
-                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + br.get(*t);
+                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get(*t);
                 v += c_cat_base[cat];
             }
             ctx = 2;
         }
         if (br.get(128)) v = -v;
-        out[c_zigzag[n]] = (int16_t)v;
+        out[zigzag_of(n)] = (int16_t)v;
         if (++n == 16) return 1;
-        p = probs + (c_bands[n] * 3 + ctx) * 11;
-        if (!br.get(p[0])) return 1;
+        NEXT_ROW(probs + (band_of(n) * 3 + ctx) * 16);
+        if (!br.get(HEAD(0))) return 1;
     }
+#undef HEAD
+#undef NEXT_ROW
+#endif
 }
 
 struct EntropyArgs {
@@ -156,6 +266,8 @@ struct EntropyArgs {
     int max_parts;
     int max_mbw;
 };
+
+constexpr int kProbBytes = 4 * 8 * 3 * 16;
 
 struct EntropyCtl {
     int modes_done;   // macroblocks whose descriptor is in global memory
@@ -177,11 +289,12 @@ __device__ __forceinline__ bool wait_shared(volatile int* word, int need, volati
 
 __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     extern __shared__ __align__(16) uint8_t smem[];
-    // layout: probs[1056] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
+    // layout: prob rows uint4[4 planes][8 bands][3 ctx] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
     uint8_t* s_probs = smem;
-    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + 1056);
-    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + 1056 + 64);
-    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + 1056 + 64 + 4 * (size_t)A.max_mbw);
+    const uint4* s_rows = reinterpret_cast<const uint4*>(smem);
+    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + kProbBytes);
+    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + kProbBytes + 64);
+    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + kProbBytes + 64 + 4 * (size_t)A.max_mbw);
 
     const int f = A.frame_first + blockIdx.x;
     const Vp8EntropyHdr& H = A.hdrs[f];
@@ -190,7 +303,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     const webpb200_frame_desc& fd = A.frames[f];
     const int mbw = fd.mbw, mbh = fd.mbh;
 
-    for (int i = threadIdx.x; i < 1056; i += blockDim.x) s_probs[i] = H.probs[i];
+    for (int i = threadIdx.x; i < kProbBytes; i += blockDim.x) s_probs[i] = (i & 15) < 11 ? H.probs[(i >> 4) * 11 + (i & 15)] : 0;
     for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(ctl)[i] = 0;
     for (int i = threadIdx.x; i < mbw; i += blockDim.x) s_top_bpred[i] = 0;
     __syncthreads();
@@ -217,11 +330,11 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                 if (update_map) {
                     int i = 0;
                     do {
-                        i = c_segment_tree[i + b.get(seg_probs[i >> 1])];
+                        i = c_segment_tree[i + (int)b.get(seg_probs[i >> 1])];
                     } while (i > 0);
                     w0 |= (uint32_t)(-i) << 16;
                 }
-                const int skipped = has_skip ? b.get(prob_skip) : 0;
+                const int skipped = has_skip ? (int)b.get(prob_skip) : 0;
                 w0 |= (uint32_t)skipped << 24;
                 const int ymode = b.tree(c_ymode_tree, c_ymode_probs);
                 w0 |= (uint32_t)ymode;
@@ -297,16 +410,32 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
             } else {
                 int16_t* lv = levels + (size_t)mbi * WEBPB200_LEVELS_PER_MB;
                 uint32_t nflags = 0;
+#if ENT_ONE_SITE
+                // 25 blocks in bitstream order: Y2 (if any), 16 Y, 4 U, 4 V.  Context bit of block k:
+                // top  = 1 + column (Y), 5 + column (U), 7 + column (V), 0 (Y2); left likewise with rows.
+                const bool has_y2 = ymode != 4;
+#pragma unroll 1
+                for (int k = has_y2 ? -1 : 0; k < 24; k++) {
+                    int tb, lb, plane, first = 0, blk = k;
+                    if (k < 0) { tb = 0; lb = 0; plane = 1; blk = 24; }
+                    else if (k < 16) { tb = 1 + (k & 3); lb = 1 + (k >> 2); plane = has_y2 ? 0 : 3; first = has_y2; }
+                    else { const int c = k - 16; tb = 5 + 2 * (c >> 2) + (c & 1); lb = 5 + 2 * (c >> 2) + ((c >> 1) & 1); plane = 2; }
+                    const int n = read_block(br, s_rows + plane * 24, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
+                    nflags |= (uint32_t)n << blk;
+                    t = (t & ~(1u << tb)) | ((uint32_t)n << tb);
+                    l = (l & ~(1u << lb)) | ((uint32_t)n << lb);
+                }
+#else
                 int plane = 3, first = 0;
                 if (ymode != 4) {
-                    const int n = read_block(br, s_probs + 1 * 264, (t & 1) + (l & 1), 0, lv + 24 * 16);
+                    const int n = read_block(br, s_rows + 1 * 24, (t & 1) + (l & 1), 0, lv + 24 * 16);
                     t = (t & ~1u) | n;
                     l = (l & ~1u) | n;
                     nflags |= (uint32_t)n << 24;
                     plane = 0;
                     first = 1;
                 }
-                const uint8_t* yp = s_probs + plane * 264;
+                const uint4* yp = s_rows + plane * 24;
 #pragma unroll 1
                 for (int y = 0; y < 4; y++) {
                     int ll = (l >> (1 + y)) & 1;
@@ -329,7 +458,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #pragma unroll 1
                         for (int x = 0; x < 2; x++) {
                             const int k = blk0 + y * 2 + x;
-                            const int n = read_block(br, s_probs + 2 * 264, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
+                            const int n = read_block(br, s_rows + 2 * 24, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
                             nflags |= (uint32_t)n << k;
                             ll = n;
                             t = (t & ~(1u << (x + j))) | ((uint32_t)n << (x + j));
@@ -337,6 +466,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                         l = (l & ~(1u << (y + j))) | ((uint32_t)ll << (y + j));
                     }
                 }
+#endif
                 mbs[mbi].nflags = nflags;
                 if (br.eof) {
                     A.status[f] = WEBPB200_ERR_BITSTREAM;
@@ -357,12 +487,10 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 
 void upload_entropy_tables_once() {
     cudaMemcpyToSymbol(c_bmode_probs, kBModeProbs, sizeof(kBModeProbs));
-    cudaMemcpyToSymbol(c_zigzag, kZigzag, sizeof(kZigzag));
-    cudaMemcpyToSymbol(c_bands, kCoeffBands, sizeof(kCoeffBands));
 }
 
 size_t entropy_smem_bytes(int max_parts, int max_mbw) {
-    return 1056 + 64 + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw;
+    return kProbBytes + 64 + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw;
 }
 
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,

@@ -152,12 +152,15 @@ void webpb200_host_free(void* p);
 
 /* Where webpb200_decode_batch runs the boolean-entropy decode of macroblock headers and
  * coefficient tokens (lossy/mod.rs:615-671, 785-963; arithmetic_decoder.rs):
- *   HOST   one frame per host thread, packed levels copied to the device (the default);
+ *   HOST   one frame per host thread, packed levels copied to the device;
  *   DEVICE one warp per bitstream partition on the GPU, all frames of the batch side by side;
- *          only the compressed chunks cross PCIe.  Same results, bit for bit.
- * The default can also be set with the environment variable WEBPB200_ENTROPY=host|device. */
+ *          only the compressed chunks cross PCIe.  Same results, bit for bit;
+ *   AUTO   (the default) per batch, whichever a cost model expects to finish first: the device
+ *          for many small frames or many partitions, the host for a few large frames.
+ * The default can also be set with the environment variable WEBPB200_ENTROPY=host|device|auto. */
 #define WEBPB200_ENTROPY_HOST 0
 #define WEBPB200_ENTROPY_DEVICE 1
+#define WEBPB200_ENTROPY_AUTO 2
 int webpb200_ctx_set_entropy(webpb200_ctx* c, int where);
 /* After a decode_batch / batch_upload: copies one image's macroblock descriptors and levels as
  * the device holds them (mbw*mbh descriptors, mbw*mbh*400 levels) -- for parity tests of the

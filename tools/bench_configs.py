@@ -27,11 +27,15 @@ def run_still(name, files, bpp, check=2):
     for f in files:
         d = W.WebPDecoder(f); n = d.output_buffer_size()
         outs.append(pin.array[off:off + n]); off += n
-    bd.decode(files, outs=outs, host_threads=CORES)
-    t = time.perf_counter()
-    for _ in range(3):
+    e2e_by_mode = {}
+    for mode, label in ((bd.ENTROPY_HOST, "host"), (bd.ENTROPY_DEVICE, "device"), (bd.ENTROPY_AUTO, "auto")):
+        bd.set_entropy(mode)
         bd.decode(files, outs=outs, host_threads=CORES)
-    e2e = (time.perf_counter() - t) / 3
+        t = time.perf_counter()
+        for _ in range(3):
+            bd.decode(files, outs=outs, host_threads=CORES)
+        e2e_by_mode[label] = (time.perf_counter() - t) / 3
+    e2e = e2e_by_mode["auto"]
     t = time.perf_counter()
     want, wst, bad = O.decode_batch(files, threads=CORES)
     cpu = time.perf_counter() - t
@@ -39,6 +43,7 @@ def run_still(name, files, bpp, check=2):
     px = size["pixels"]
     print(json.dumps({"config": name, "images": len(files), "MPix": px / 1e6, "device_MPix_s": px / ms / 1e3, "ms_per_pass": ms,
                       "kernel_ms": dict(zip(["predict", "loopfilter", "yuv2rgb", "alpha"], k)), "e2e_MPix_s": px / e2e / 1e6,
+                      "e2e_ms_by_entropy_mode": {k: round(v * 1e3, 1) for k, v in e2e_by_mode.items()},
                       "cpu_oracle_MPix_s": px / cpu / 1e6, "cpu_cores": CORES, "bit_exact_vs_oracle": bool(ok)}), flush=True)
     pin.free(); bd.close()
 
