@@ -199,6 +199,7 @@ def main():
         _, st = bd.decode(files, outs=outs, host_threads=host_threads)
     e2e_ms = 1e3 * (time.perf_counter() - t0) / e2e_steps
     assert all(s == 0 for s in st)
+    h2d_bytes, d2h_bytes, entropy_where = bd.last_transfer()
     sh.barrier(dist)
     e2e_px, e2e_max_ms = sh.aggregate(dist, px, e2e_ms)
     e2e_value = e2e_px / (e2e_max_ms / 1e3) / 1e6
@@ -223,7 +224,8 @@ def main():
                          "frac": achieved / peak, "traffic": traffic_per_launch(names[dominant]), "peak_kind": peak_kind,
                          "pipeline_achieved": pipeline_gbs, "pipeline_frac": pipeline_gbs / peak,
                          "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass"},
-            "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": size["in_bytes"], "d2h_bytes_per_step": out_bytes,
+            "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
                     "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum},
             "gpu_launches": int(launches),
             "clocks": clocks,

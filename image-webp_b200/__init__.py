@@ -88,6 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
+    "webpb200_last_transfer",
 ]
 
 
@@ -139,6 +140,7 @@ def lib():
     L.webpb200_batch_time.argtypes = [vp, C.c_uint, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.webpb200_batch_size.argtypes = [vp, pi] + [C.POINTER(C.c_uint64)] * 4
     L.webpb200_batch_get_planes.argtypes = [vp, i32, vp, vp, vp]
+    L.webpb200_last_transfer.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(i32)]
     L.webpb200_ctx_set_entropy.argtypes = [vp, i32]
     L.webpb200_batch_download_packed.argtypes = [vp, i32, vp, vp]
     L.webpb200_batch_get_packed.argtypes = [vp, i32, C.POINTER(C.POINTER(FrameDesc)), C.POINTER(C.POINTER(MbDesc)),
@@ -391,6 +393,12 @@ class BatchDecoder:
     def set_entropy(self, where):
         """Where decode() runs the boolean-entropy decode: ENTROPY_HOST (threads) or ENTROPY_DEVICE (k_entropy)."""
         self._check(lib().webpb200_ctx_set_entropy(self._h, where))
+
+    def last_transfer(self):
+        """(h2d bytes, d2h bytes, 'host'|'device') of the last decode()."""
+        a, b, w = C.c_uint64(), C.c_uint64(), C.c_int()
+        self._check(lib().webpb200_last_transfer(self._h, C.byref(a), C.byref(b), C.byref(w)))
+        return a.value, b.value, "device" if w.value == 1 else "host"
 
     def device_packed(self, image, frame_desc):
         """Macroblock descriptors and levels of one image as the device holds them (after decode/upload)."""

@@ -116,6 +116,8 @@ struct webpb200_ctx {
     uint64_t launches = 0;
 
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
+    uint64_t last_h2d = 0, last_d2h = 0;  // bytes the last decode_batch copied each way
+    int last_entropy = WEBPB200_ENTROPY_HOST;  // where its entropy stage ran
     int entropy_where = WEBPB200_ENTROPY_AUTO;  // WEBPB200_ENTROPY_*: where decode_batch runs the boolean decode
     DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status;
 
@@ -417,6 +419,7 @@ int download_range(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens
             j++;
         }
         CU(c, cudaMemcpyAsync(dst, c->d_out.p + src, run, cudaMemcpyDeviceToHost, c->stream), "D2H out");
+        c->last_d2h += run;
         i = j;
     }
     return 0;
@@ -536,6 +539,14 @@ extern "C" void webpb200_host_free(void* p) {
 extern "C" int webpb200_ctx_set_entropy(webpb200_ctx* c, int where) {
     if (!c || where < WEBPB200_ENTROPY_HOST || where > WEBPB200_ENTROPY_AUTO) return -WEBPB200_ERR_INVALID_PARAM;
     c->entropy_where = where;
+    return 0;
+}
+
+extern "C" int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int* entropy_where) {
+    if (!c) return -WEBPB200_ERR_INVALID_PARAM;
+    if (h2d_bytes) *h2d_bytes = c->last_h2d;
+    if (d2h_bytes) *d2h_bytes = c->last_d2h;
+    if (entropy_where) *entropy_where = c->last_entropy;
     return 0;
 }
 
@@ -749,6 +760,8 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
     }
     c->uploaded = true;
+    c->last_entropy = WEBPB200_ENTROPY_DEVICE;
+    c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + sizeof(Vp8EntropyHdr) * (uint64_t)n + bits_bytes + c->alpha_bytes + c->aux_bytes;
     if (trace) cudaEventRecord(c->ev[5], s);
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
@@ -793,6 +806,7 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
     if (n < 0) return -WEBPB200_ERR_INVALID_PARAM;
     cudaSetDevice(c->device);
+    c->last_d2h = 0;
     if (c->entropy_where != WEBPB200_ENTROPY_HOST) {
         const int r = decode_batch_device_entropy(c, files, lens, n, outs, out_lens, status, upsampling, host_threads);
         if (r != kPreferHostEntropy) return r;
@@ -806,6 +820,9 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     if ((rc = reserve_device(c)) != 0) return rc;
     webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     cudaStream_t s = c->stream;
+    c->last_entropy = WEBPB200_ENTROPY_HOST;
+    c->last_d2h = 0;
+    c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + c->total_mbs * (sizeof(webpb200_mb_desc) + 2 * WEBPB200_LEVELS_PER_MB) + c->alpha_bytes + c->aux_bytes;
 
     // chunks by macroblock count; ticket order row-major inside each chunk
     const uint64_t kChunkMbs = 96 * 1024;

@@ -162,6 +162,9 @@ void webpb200_host_free(void* p);
 #define WEBPB200_ENTROPY_DEVICE 1
 #define WEBPB200_ENTROPY_AUTO 2
 int webpb200_ctx_set_entropy(webpb200_ctx* c, int where);
+/* What the last webpb200_decode_batch on this context moved over PCIe (bytes each way) and
+ * where its entropy stage ran (WEBPB200_ENTROPY_HOST or _DEVICE); for bench accounting. */
+int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int* entropy_where);
 /* After a decode_batch / batch_upload: copies one image's macroblock descriptors and levels as
  * the device holds them (mbw*mbh descriptors, mbw*mbh*400 levels) -- for parity tests of the
  * device entropy stage against webpb200_host_entropy_decode. */
