@@ -111,6 +111,9 @@ struct webpb200_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;      // reconstruction of finished bands while k_entropy still runs
+    unsigned int* h_band = nullptr;      // mapped pinned: macroblock rows finished per band (written by k_entropy)
+    unsigned int* d_band = nullptr;
     cudaEvent_t ev[8] = {};
     std::string err;
     uint64_t launches = 0;
@@ -521,6 +524,8 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->h_band) cudaFreeHost(c->h_band);
     delete c;
 }
 
@@ -762,17 +767,119 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     c->uploaded = true;
     c->last_entropy = WEBPB200_ENTROPY_DEVICE;
     c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + sizeof(Vp8EntropyHdr) * (uint64_t)n + bits_bytes + c->alpha_bytes + c->aux_bytes;
+    // Band pipelining: when every frame has the same size and the caller's buffers are evenly spaced,
+    // the frames are cut into horizontal bands of macroblock rows; k_entropy counts finished rows per
+    // band in host-visible memory, and as soon as a band is complete in every frame this thread
+    // launches its prediction, the loop filter of the band before (one band late: prediction reads
+    // unfiltered neighbours, mod.rs:1289-1294), the colour conversion of the rows that are final
+    // (the last 3 pixel rows above a band edge still wait for the next band's top-edge filter) and
+    // their copy to the host -- all on a second stream, under the still running k_entropy.
+    constexpr int kMaxBands = 16;
+    int nbands = 0, band_rows = 0;
+    size_t dpitch = 0, spitch = 0;
+    {
+        static const int want = [] { const char* e = std::getenv("WEBPB200_BANDS"); return e ? std::atoi(e) : 8; }();
+        bool ok = want > 1 && n >= 2 && c->alpha_bytes == 0 && c->total_mbs >= 16384 && frames[0].mbh >= 8;
+        for (int i = 0; ok && i < n; i++) {
+            const webpb200_frame_desc& f = frames[i];
+            ok = !c->items[i].status && f.width == frames[0].width && f.height == frames[0].height && f.out_bpp == 3 &&
+                 out_lens[i] == (size_t)f.width * f.height * 3;
+        }
+        if (ok) {
+            dpitch = (size_t)(outs[1] - outs[0]);
+            spitch = (size_t)(frames[1].out_off - frames[0].out_off);
+            ok = outs[1] > outs[0] && dpitch >= out_lens[0];
+            for (int i = 0; ok && i < n; i++) ok = outs[i] == outs[0] + (size_t)i * dpitch && frames[i].out_off == frames[0].out_off + (uint64_t)i * spitch;
+        }
+        if (ok) {
+            band_rows = (frames[0].mbh + std::min(want, kMaxBands) - 1) / std::min(want, kMaxBands);
+            if (band_rows < 2) band_rows = 2;
+            nbands = (frames[0].mbh + band_rows - 1) / band_rows;
+            if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
+            if (!c->h_band) {
+                CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_band), sizeof(unsigned int) * kMaxBands, cudaHostAllocMapped), "band counters");
+                CU(c, cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->d_band), c->h_band, 0), "band counters");
+            }
+            for (int k = 0; k < kMaxBands; k++) c->h_band[k] = 0;
+        }
+    }
+    CU(c, cudaEventRecord(c->ev[7], s), "event");  // every input of the reconstruction kernels is on the device
     if (trace) cudaEventRecord(c->ev[5], s);
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
-                             reinterpret_cast<int*>(c->d_status.p), max_parts, s), "k_entropy");
+                             reinterpret_cast<int*>(c->d_status.p), max_parts, nbands ? c->d_band : nullptr, band_rows, s), "k_entropy");
         c->launches++;
     }
     if (trace) cudaEventRecord(c->ev[6], s);
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
+    if (nbands) {
+        cudaStream_t r = c->stream2;
+        CU(c, cudaEventRecord(c->ev[4], s), "event");  // k_entropy (and the status copy) finished
+        CU(c, cudaStreamWaitEvent(r, c->ev[7], 0), "wait inputs");
+        const BatchDev& B = c->bd;
+        CU(c, cudaMemsetAsync(B.scratch + B.lay.progress_pred_off, 0, (size_t)(B.lay.zero_bytes - B.lay.progress_pred_off), r), "clear progress");
+        const int mbh = frames[0].mbh, w = frames[0].width, h = frames[0].height;
+        const int q_all = h / 2 + 1;
+        int q_done = 0;
+        auto emit = [&](int q_end) -> int {  // convert row pairs [q_done, q_end) and send their pixel rows home
+            if (q_end <= q_done) return 0;
+            BatchDev bd = B;
+            bd.q_first = q_done;
+            bd.q_end = q_end;
+            CU(c, launch_yuv2rgb(bd, r), "k_yuv2rgb");
+            c->launches++;
+            const int y0 = q_done == 0 ? 0 : 2 * q_done - 1, y1 = std::min(h, 2 * q_end - 1);
+            const size_t off = (size_t)y0 * w * 3, bytes = (size_t)(y1 - y0) * w * 3;
+            CU(c, cudaMemcpy2DAsync(outs[0] + off, dpitch, c->d_out.p + frames[0].out_off + off, spitch, bytes, (size_t)n, cudaMemcpyDeviceToHost, r), "D2H band");
+            c->last_d2h += bytes * (uint64_t)n;
+            q_done = q_end;
+            return 0;
+        };
+        auto band_dev = [&](int k) {
+            BatchDev bd = B;
+            const int r0 = k * band_rows, r1 = std::min(mbh, r0 + band_rows);
+            bd.order_first = (uint32_t)r0 * (uint32_t)n;
+            bd.total_rows = (uint32_t)(r1 - r0) * (uint32_t)n;
+            return bd;
+        };
+        for (int k = 0; k < nbands; k++) {
+            const unsigned int need = (unsigned int)(std::min(mbh, (k + 1) * band_rows) - k * band_rows) * (unsigned int)n;
+            volatile unsigned int* cnt = c->h_band + k;
+            while (*cnt < need && cudaEventQuery(c->ev[4]) == cudaErrorNotReady) std::this_thread::sleep_for(std::chrono::microseconds(20));
+            CU(c, cudaMemsetAsync(B.scratch, 0, 8, r), "clear tickets");
+            CU(c, launch_predict(band_dev(k), r), "k_predict");
+            c->launches++;
+            if (k > 0) {
+                CU(c, launch_loopfilter(band_dev(k - 1), r), "k_loopfilter");
+                c->launches++;
+                if ((rc = emit(8 * k * band_rows - 3)) != 0) return rc;
+            }
+        }
+        CU(c, cudaMemsetAsync(B.scratch, 0, 8, r), "clear tickets");
+        CU(c, launch_loopfilter(band_dev(nbands - 1), r), "k_loopfilter");
+        c->launches++;
+        if ((rc = emit(q_all)) != 0) return rc;
+        CU(c, cudaStreamSynchronize(s), "sync");
+        CU(c, cudaStreamSynchronize(r), "sync");
+        for (int i = 0; i < n; i++)
+            if (dev_status[i]) c->items[i].status = dev_status[i];  // those pixels are not valid
+        if ((rc = check_abort(c)) != 0) return rc;
+        if (trace) {
+            float ems = 0;
+            cudaEventElapsedTime(&ems, c->ev[5], c->ev[6]);
+            std::fprintf(stderr, "[webpb200] decode_batch(device entropy, %d bands of %d rows) n=%d: host %.1f ms, k_entropy %.2f ms, total %.1f ms\n",
+                         nbands, band_rows, n, t_host, ems, ms_since());
+        }
+        int bad = 0;
+        for (int i = 0; i < n; i++) {
+            if (status) status[i] = c->items[i].status;
+            bad += c->items[i].status != 0;
+        }
+        return bad;
+    }
     if ((rc = reconstruct(c, c->bd, c->alpha_bytes ? 0xF : 0x7, s, nullptr)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
     const double t_kernels = ms_since();

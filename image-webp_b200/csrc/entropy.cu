@@ -265,6 +265,8 @@ struct EntropyArgs {
     int frame_first;
     int max_parts;
     int max_mbw;
+    unsigned int* band_done;  // host-visible row counters per band of band_rows macroblock rows, or null
+    int band_rows;
 };
 
 constexpr int kProbBytes = 4 * 8 * 3 * 16;
@@ -480,6 +482,10 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                 *my_prog = (mby << 16) | (mbx + 1);
             }
         }
+        if (A.band_done) {  // this row's levels and descriptors are complete: let the host see it
+            __threadfence_system();
+            atomicAdd_system(A.band_done + mby / A.band_rows, 1u);
+        }
     }
 }
 
@@ -494,13 +500,15 @@ size_t entropy_smem_bytes(int max_parts, int max_mbw) {
 }
 
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, cudaStream_t s) {
+                           int16_t* d_levels, int* d_status, int max_parts, unsigned int* band_done, int band_rows, cudaStream_t s) {
     if (b.n_frames <= 0) return cudaSuccess;
     EntropyArgs a;
     a.frames = b.frames; a.hdrs = d_hdrs; a.bits = d_bits; a.mbs = d_mbs; a.levels = d_levels; a.status = d_status;
     a.frame_first = b.frame_first;
     a.max_parts = max_parts;
     a.max_mbw = (int)((b.max_w + 15) / 16);
+    a.band_done = band_done;
+    a.band_rows = band_rows > 0 ? band_rows : 1;
     const size_t smem = entropy_smem_bytes(max_parts, a.max_mbw);
     static_assert(sizeof(EntropyCtl) <= 64, "EntropyCtl outgrew its slot");
     k_entropy<<<b.n_frames, 32 * (1 + max_parts), smem, s>>>(a);

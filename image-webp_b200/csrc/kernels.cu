@@ -879,6 +879,7 @@ struct RgbArgs {
     const webpb200_frame_desc* frames;
     const uint8_t* planes;
     uint8_t* out;
+    int q_first, q_end;  // row pairs [q_first, q_end) only (pair q = rows 2q-1, 2q)
 };
 
 // Horizontal half of the fancy upsampler for 8 pixels of one chroma row.  c[0..5] are the chroma
@@ -941,10 +942,10 @@ __device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int
 __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
     const webpb200_frame_desc* fd = A.frames + blockIdx.z;
     const int w = fd->width, h = fd->height;
-    const int q = blockIdx.y * 2 + threadIdx.y;
+    const int q = A.q_first + blockIdx.y * 2 + threadIdx.y;
     const int x0 = (blockIdx.x * 64 + threadIdx.x) * 8;
     const int ya = q == 0 ? 0 : 2 * q - 1, yb = 2 * q;
-    if (x0 >= w || ya >= h) return;
+    if (x0 >= w || ya >= h || q >= A.q_end) return;
     const bool has_b = q > 0 && yb < h;
     const int ystride = fd->mbw * 16, cstride = fd->mbw * 8;
     const int bpp = fd->out_bpp;
@@ -1341,7 +1342,11 @@ cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
     RgbArgs a;
     a.frames = b.frames + b.frame_first; a.planes = b.planes; a.out = b.out;
     // thread = 8 pixels x 2 rows; block = 64 x 2 threads = 512 pixels x 4 rows; row pairs: h/2 + 1
-    dim3 grid((b.max_w + 511) / 512, (b.max_h / 2 + 1 + 1) / 2, b.n_frames);
+    const int q_all = (int)b.max_h / 2 + 1;
+    a.q_first = b.q_end > b.q_first ? b.q_first : 0;
+    a.q_end = b.q_end > b.q_first ? (b.q_end < q_all ? b.q_end : q_all) : q_all;
+    if (a.q_end <= a.q_first) return cudaSuccess;
+    dim3 grid((b.max_w + 511) / 512, (a.q_end - a.q_first + 1) / 2, b.n_frames);
     k_yuv2rgb<<<grid, dim3(64, 2), 0, s>>>(a);
     return cudaGetLastError();
 }

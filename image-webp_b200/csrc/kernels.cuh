@@ -38,6 +38,7 @@ struct BatchDev {
     uint32_t order_first;   // ... whose tickets start at this index of the order array
     uint32_t max_w, max_h;  // largest frame of the batch (grid sizing)
     int sm_count;
+    int q_first, q_end;     // k_yuv2rgb: row pairs [q_first, q_end) only; 0, 0 = every row
     // frames with an ALPH plane, grouped by filter method m: alpha_lists[m * n_frames + k]
     const int* alpha_lists;  // device
     int alpha_counts[4];
@@ -65,8 +66,11 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches);
 // [b.frame_first, +b.n_frames) from the staged bitstreams into d_mbs / d_levels (both cleared by
 // the caller); d_status[frame] is set to WEBPB200_ERR_BITSTREAM for a frame that ran out of bits
 void upload_entropy_tables_once();
+// band_done (may be null): host-visible counters; after each finished macroblock row y the kernel
+// adds 1 to band_done[y / band_rows] (system-scope, after a system fence), so that the host can
+// start reconstructing the top of the frames while the bottom is still being decoded
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, cudaStream_t s);
+                           int16_t* d_levels, int* d_status, int max_parts, unsigned int* band_done, int band_rows, cudaStream_t s);
 
 struct CompositeArgs {  // one composite_frame call, reference extended.rs:30-129
     uint8_t* canvas;       // canvas_w * canvas_h * 4, device

@@ -112,3 +112,55 @@ def test_batch_scale_checksum(W, dev, host, synth):
     for i, (a, b) in enumerate(zip(o_dev, o_host)):
         assert np.array_equal(a, b), i
     _check_packed(W, dev, files[:4], s_dev[:4])
+
+
+def _contiguous_outs(n, per):
+    buf = np.zeros(n * per, dtype=np.uint8)
+    return buf, [buf[i * per:(i + 1) * per] for i in range(n)]
+
+
+@pytest.mark.parametrize("w,h,n,kw", [
+    (512, 512, 128, dict(filter_type=1, filter_level=25, prob_skip=200, p_skip=0.05)),       # cfg2 shape, simple filter
+    (200, 120, 320, dict(filter_type=0, filter_level=40, sharpness=2)),                      # ragged size, normal filter
+    (333, 257, 96, dict(filter_type=0, filter_level=63, sharpness=7, log2_parts=2)),         # odd size, strongest filter, 4 partitions
+    (256, 256, 96, dict(filter_type=0, filter_level=0)),                                     # no loop filter at all
+])
+def test_band_pipeline_matches_host_path(W, dev, host, synth, w, h, n, kw):
+    """Same-size batches with evenly spaced output buffers take the band-pipelined route (bands of
+    macroblock rows reconstructed and copied out while k_entropy still decodes the rows below).
+    The band edges are where it could go wrong (loop filter one band late, colour conversion held
+    back 3 rows): compare every pixel with the host-entropy path, which runs whole frames."""
+    files = [synth.webp_simple(synth.vp8_frame(w, h, seed=1000 + i, **kw)) for i in range(n)]
+    per = w * h * 3
+    _, o_dev = _contiguous_outs(n, per)
+    _, o_host = _contiguous_outs(n, per)
+    _, s_dev = dev.decode(files, outs=o_dev)
+    _, s_host = host.decode(files, outs=o_host)
+    assert s_dev == s_host == [0] * n
+    for i in range(n):
+        assert np.array_equal(o_dev[i], o_host[i]), i
+    # fancy and simple upsampling both
+    _, s2 = dev.decode(files[:64] if n >= 128 else files, outs=o_dev[:64] if n >= 128 else o_dev, lossy_upsampling=W.SIMPLE)
+    _, s3 = host.decode(files[:64] if n >= 128 else files, outs=o_host[:64] if n >= 128 else o_host, lossy_upsampling=W.SIMPLE)
+    assert s2 == s3
+    m = 64 if n >= 128 else n
+    for i in range(m):
+        assert np.array_equal(o_dev[i], o_host[i]), i
+
+
+def test_band_pipeline_with_a_damaged_frame(W, dev, host, synth):
+    """A frame that runs out of bits inside a token partition, in a batch that takes the banded route:
+    its status must say so (as on the host path) and its neighbours must be intact."""
+    n, w, h = 96, 256, 256
+    files = [synth.webp_simple(synth.vp8_frame(w, h, seed=2000 + i, filter_type=0, filter_level=20)) for i in range(n)]
+    files[17] = files[17][:len(files[17]) * 2 // 3]
+    files[40] = files[40][:len(files[40]) - 5]
+    per = w * h * 3
+    _, o_dev = _contiguous_outs(n, per)
+    _, o_host = _contiguous_outs(n, per)
+    _, s_dev = dev.decode(files, outs=o_dev)
+    _, s_host = host.decode(files, outs=o_host)
+    assert s_dev == s_host and s_dev[17] != 0
+    for i in range(n):
+        if s_dev[i] == 0:
+            assert np.array_equal(o_dev[i], o_host[i]), i
