@@ -112,9 +112,10 @@ struct webpb200_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;      // reconstruction of finished bands while k_entropy still runs
-    unsigned int* h_band = nullptr;      // mapped pinned: macroblock rows finished per band (written by k_entropy)
-    unsigned int* d_band = nullptr;
-    cudaEvent_t ev[8] = {};
+    unsigned int* h_rows = nullptr;      // mapped pinned: [frame * 8 + partition] rows finished (written by k_entropy)
+    unsigned int* d_rows = nullptr;
+    size_t rows_cap = 0;
+    cudaEvent_t ev[12] = {};
     std::string err;
     uint64_t launches = 0;
 
@@ -525,7 +526,7 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     if (c->stream2) cudaStreamDestroy(c->stream2);
-    if (c->h_band) cudaFreeHost(c->h_band);
+    if (c->h_rows) cudaFreeHost(c->h_rows);
     delete c;
 }
 
@@ -687,8 +688,10 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     std::vector<WorkItem> items;
     items_from_files(files, lens, n, host_threads, &items);
+    const double t_items = ms_since();
     int rc = layout_items(c, std::move(items), upsampling, host_threads, false);
     if (rc) return rc;
+    const double t_layout = ms_since();
     webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     cudaStream_t s = c->stream;
 
@@ -706,11 +709,13 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     Vp8EntropyHdr* hdrs = reinterpret_cast<Vp8EntropyHdr*>(c->h_ehdr.p);
 
     // clear the outputs of the entropy stage while the host parses headers
+    if (trace) cudaEventRecord(c->ev[8], s);
     if (c->total_mbs) {
         CU(c, cudaMemsetAsync(c->d_mbs.p, 0, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, s), "clear mbs");
         CU(c, cudaMemsetAsync(c->d_levels.p, 0, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, s), "clear levels");
     }
     CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * (size_t)std::max(n, 1), s), "clear status");
+    if (trace) cudaEventRecord(c->ev[9], s);
 
     auto drop = [&](int i, int st) {  // the frame stays in the batch as all-DC, all-zero macroblocks nobody looks at
         c->items[i].status = st;
@@ -718,15 +723,47 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         frames[i].filter_level = 0;
         frames[i].alpha_mode = 0;
     };
-    parallel_for(n, host_threads, [&](int i) {
-        WorkItem& it = c->items[i];
-        Vp8EntropyHdr& eh = hdrs[i];
-        std::memset(&eh, 0, sizeof(eh));
-        if (it.status) return;
-        const int st = vp8_parse_header(it.vp8, it.vp8_len, &frames[i], &eh);
-        if (st) drop(i, st);
-        eh.data_off = bit_off[i];
-    });
+    // Host threads take the frames in order: header parse, then the compressed chunk into the pinned
+    // arena.  This thread follows them and sends each finished slice of the arena on its way, so the
+    // upload hides behind the staging.  (In AUTO mode the slices may turn out to be sent for nothing.)
+    {
+        const int nslices = std::max(1, std::min(16, n / 32));
+        std::vector<int> slice_end((size_t)nslices);
+        for (int k = 0; k < nslices; k++) slice_end[k] = (int)((int64_t)n * (k + 1) / nslices);
+        std::unique_ptr<std::atomic<int>[]> left(new std::atomic<int>[(size_t)nslices]);
+        for (int k = 0; k < nslices; k++) left[k].store(slice_end[k] - (k ? slice_end[k - 1] : 0));
+        std::vector<int> slice_of((size_t)n);
+        for (int k = 0, i = 0; k < nslices; k++)
+            for (; i < slice_end[k]; i++) slice_of[i] = k;
+        std::atomic<int> next{0};
+        auto worker = [&]() {
+            for (;;) {
+                const int i = next.fetch_add(1);
+                if (i >= n) return;
+                WorkItem& it = c->items[i];
+                Vp8EntropyHdr& eh = hdrs[i];
+                std::memset(&eh, 0, sizeof(eh));
+                if (!it.status) {
+                    const int st = vp8_parse_header(it.vp8, it.vp8_len, &frames[i], &eh);
+                    if (st) drop(i, st);
+                    else std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
+                    eh.data_off = bit_off[i];
+                }
+                left[slice_of[i]].fetch_sub(1, std::memory_order_release);
+            }
+        };
+        std::vector<std::thread> pool;
+        for (int t = 0; t < std::max(1, std::min(host_threads, n)); t++) pool.emplace_back(worker);
+        cudaError_t e = cudaSuccess;
+        for (int k = 0; k < nslices; k++) {
+            while (left[k].load(std::memory_order_acquire) > 0) std::this_thread::yield();
+            const uint64_t b0 = bit_off[k ? slice_end[k - 1] : 0], b1 = bit_off[slice_end[k]];
+            if (b1 > b0 && e == cudaSuccess) e = cudaMemcpyAsync(c->d_bits.p + b0, c->h_bits.p + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, s);
+        }
+        for (auto& t : pool) t.join();
+        CU(c, e, "H2D bitstreams");
+    }
+    const double t_headers = ms_since();
     int max_parts = 1;
     for (int i = 0; i < n; i++) max_parts = std::max<int>(max_parts, hdrs[i].num_parts);
     if (c->entropy_where == WEBPB200_ENTROPY_AUTO) {
@@ -743,26 +780,25 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         const double est_host_us = (double)c->total_mbs * 3.0 / std::max(1, std::min(host_threads, n));
         if (est_device_us > est_host_us) return kPreferHostEntropy;
     }
-    parallel_for(n, host_threads, [&](int i) {  // stage the compressed chunks; ALPH planes are host work in both modes
-        WorkItem& it = c->items[i];
-        if (it.status) return;
-        std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
-        if (frames[i].alpha_mode)
-            if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
-    });
+    if (c->alpha_bytes)
+        parallel_for(n, host_threads, [&](int i) {  // ALPH planes are host work in both modes
+            if (!c->items[i].status && frames[i].alpha_mode)
+                if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
+        });
     fill_row_order(frames, 0, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
     finish_items(c);
     const double t_host = ms_since();
+    if (trace) std::fprintf(stderr, "  host: containers %.2f, layout %.2f, headers %.2f, staging %.2f ms\n", t_items, t_layout, t_headers, t_host);
 
+    if (trace) cudaEventRecord(c->ev[10], s);
     CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
     CU(c, cudaMemcpyAsync(c->d_ehdr.p, hdrs, sizeof(Vp8EntropyHdr) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D entropy headers");
-    CU(c, cudaMemcpyAsync(c->d_bits.p, c->h_bits.p, (size_t)bits_bytes, cudaMemcpyHostToDevice, s), "H2D bitstreams");
     if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
     CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
     CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
     if (c->total_rows) {
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->h_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "rowmap");
+        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->h_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "row order");
     }
     c->uploaded = true;
     c->last_entropy = WEBPB200_ENTROPY_DEVICE;
@@ -775,7 +811,8 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     // (the last 3 pixel rows above a band edge still wait for the next band's top-edge filter) and
     // their copy to the host -- all on a second stream, under the still running k_entropy.
     constexpr int kMaxBands = 16;
-    int nbands = 0, band_rows = 0;
+    int nbands = 0;
+    int band_start[kMaxBands + 1] = {0};
     size_t dpitch = 0, spitch = 0;
     {
         static const int want = [] { const char* e = std::getenv("WEBPB200_BANDS"); return e ? std::atoi(e) : 8; }();
@@ -792,15 +829,27 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
             for (int i = 0; ok && i < n; i++) ok = outs[i] == outs[0] + (size_t)i * dpitch && frames[i].out_off == frames[0].out_off + (uint64_t)i * spitch;
         }
         if (ok) {
-            band_rows = (frames[0].mbh + std::min(want, kMaxBands) - 1) / std::min(want, kMaxBands);
-            if (band_rows < 2) band_rows = 2;
-            nbands = (frames[0].mbh + band_rows - 1) / band_rows;
-            if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
-            if (!c->h_band) {
-                CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_band), sizeof(unsigned int) * kMaxBands, cudaHostAllocMapped), "band counters");
-                CU(c, cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->d_band), c->h_band, 0), "band counters");
+            // bands shrink towards the bottom: what is left to do after k_entropy ends is the last band
+            const int mbh = frames[0].mbh, target = std::min(want, kMaxBands);
+            int row = 0;
+            while (row < mbh) {
+                const int left_bands = target - nbands;
+                int size = left_bands <= 1 ? mbh - row : std::max(2, (mbh - row + 3) / 4);
+                if (mbh - row - size == 1) size++;  // no one-row band at the end
+                band_start[nbands++] = row;
+                row += std::min(size, mbh - row);
             }
-            for (int k = 0; k < kMaxBands; k++) c->h_band[k] = 0;
+            band_start[nbands] = mbh;
+            if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
+            if (c->rows_cap < (size_t)n * 8) {
+                if (c->h_rows) cudaFreeHost(c->h_rows);
+                c->h_rows = nullptr;
+                c->rows_cap = 0;
+                CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_rows), sizeof(unsigned int) * 8 * (size_t)n, cudaHostAllocMapped), "row counters");
+                CU(c, cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->d_rows), c->h_rows, 0), "row counters");
+                c->rows_cap = (size_t)n * 8;
+            }
+            std::memset(c->h_rows, 0, sizeof(unsigned int) * 8 * (size_t)n);
         }
     }
     CU(c, cudaEventRecord(c->ev[7], s), "event");  // every input of the reconstruction kernels is on the device
@@ -808,10 +857,14 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
-                             reinterpret_cast<int*>(c->d_status.p), max_parts, nbands ? c->d_band : nullptr, band_rows, s), "k_entropy");
+                             reinterpret_cast<int*>(c->d_status.p), max_parts, nbands ? c->d_rows : nullptr, s), "k_entropy");
         c->launches++;
     }
     if (trace) cudaEventRecord(c->ev[6], s);
+    if (trace) {
+        cudaEventSynchronize(c->ev[5]);
+        std::fprintf(stderr, "  k_entropy started at %.2f ms (enqueued at %.2f)\n", ms_since(), t_host);
+    }
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
@@ -824,6 +877,12 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         const int mbh = frames[0].mbh, w = frames[0].width, h = frames[0].height;
         const int q_all = h / 2 + 1;
         int q_done = 0;
+        cudaEvent_t bev[kMaxBands][4];
+        int band_now = 0;
+        double t_seen[kMaxBands];
+        if (trace)
+            for (int k = 0; k < nbands; k++)
+                for (auto& e : bev[k]) cudaEventCreate(&e);
         auto emit = [&](int q_end) -> int {  // convert row pairs [q_done, q_end) and send their pixel rows home
             if (q_end <= q_done) return 0;
             BatchDev bd = B;
@@ -831,37 +890,73 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
             bd.q_end = q_end;
             CU(c, launch_yuv2rgb(bd, r), "k_yuv2rgb");
             c->launches++;
+            if (trace) cudaEventRecord(bev[band_now][3], r);
             const int y0 = q_done == 0 ? 0 : 2 * q_done - 1, y1 = std::min(h, 2 * q_end - 1);
             const size_t off = (size_t)y0 * w * 3, bytes = (size_t)(y1 - y0) * w * 3;
+            static const bool linear = std::getenv("WEBPB200_BAND_LINEAR") != nullptr;
+            if (linear) {
+                for (int i = 0; i < n; i++)
+                    CU(c, cudaMemcpyAsync(outs[i] + off, c->d_out.p + frames[i].out_off + off, bytes, cudaMemcpyDeviceToHost, r), "D2H band");
+            } else
             CU(c, cudaMemcpy2DAsync(outs[0] + off, dpitch, c->d_out.p + frames[0].out_off + off, spitch, bytes, (size_t)n, cudaMemcpyDeviceToHost, r), "D2H band");
             c->last_d2h += bytes * (uint64_t)n;
             q_done = q_end;
             return 0;
         };
-        auto band_dev = [&](int k) {
+        auto rows_dev = [&](int r0, int r1) {  // macroblock rows [r0, r1) of every frame, in ticket order
             BatchDev bd = B;
-            const int r0 = k * band_rows, r1 = std::min(mbh, r0 + band_rows);
             bd.order_first = (uint32_t)r0 * (uint32_t)n;
             bd.total_rows = (uint32_t)(r1 - r0) * (uint32_t)n;
             return bd;
         };
-        for (int k = 0; k < nbands; k++) {
-            const unsigned int need = (unsigned int)(std::min(mbh, (k + 1) * band_rows) - k * band_rows) * (unsigned int)n;
-            volatile unsigned int* cnt = c->h_band + k;
-            while (*cnt < need && cudaEventQuery(c->ev[4]) == cudaErrorNotReady) std::this_thread::sleep_for(std::chrono::microseconds(20));
-            CU(c, cudaMemsetAsync(B.scratch, 0, 8, r), "clear tickets");
-            CU(c, launch_predict(band_dev(k), r), "k_predict");
-            c->launches++;
-            if (k > 0) {
-                CU(c, launch_loopfilter(band_dev(k - 1), r), "k_loopfilter");
-                c->launches++;
-                if ((rc = emit(8 * k * band_rows - 3)) != 0) return rc;
-            }
+        const double t_launch = ms_since();
+        cudaEvent_t probe[3];
+        const bool copy_probe = trace && std::getenv("WEBPB200_COPY_PROBE") != nullptr;
+        if (copy_probe) {  // how fast is a D2H copy while k_entropy runs? (linear, then 2-D)
+            for (auto& e : probe) cudaEventCreate(&e);
+            cudaEventRecord(probe[0], r);
+            cudaMemcpyAsync(outs[0], c->d_out.p + frames[0].out_off, (size_t)200 << 20, cudaMemcpyDeviceToHost, r);
+            cudaEventRecord(probe[1], r);
+            cudaMemcpy2DAsync(outs[0], dpitch, c->d_out.p + frames[0].out_off, spitch, 196608, (size_t)n, cudaMemcpyDeviceToHost, r);
+            cudaEventRecord(probe[2], r);
         }
-        CU(c, cudaMemsetAsync(B.scratch, 0, 8, r), "clear tickets");
-        CU(c, launch_loopfilter(band_dev(nbands - 1), r), "k_loopfilter");
-        c->launches++;
-        if ((rc = emit(q_all)) != 0) return rc;
+        int lf_done = 0;  // macroblock rows already loop-filtered
+        int scan_from = 0;
+        for (int k = 0; k < nbands; k++) {
+            const int r0 = band_start[k], r1 = band_start[k + 1];
+            // wait until every frame's decode frontier (the first row some partition has not finished) is past the band
+            for (;;) {
+                while (scan_from < n) {
+                    const int P = hdrs[scan_from].num_parts;
+                    const volatile unsigned int* slot = c->h_rows + (size_t)scan_from * 8;
+                    int frontier = mbh;
+                    for (int p = 0; p < P; p++) {
+                        const int rows_p = p < mbh ? (mbh - p + P - 1) / P : 0, done = (int)slot[p];
+                        if (done < rows_p) frontier = std::min(frontier, p + done * P);
+                    }
+                    if (frontier < r1) break;
+                    scan_from++;
+                }
+                if (scan_from >= n || cudaEventQuery(c->ev[4]) != cudaErrorNotReady) break;
+                std::this_thread::sleep_for(std::chrono::microseconds(20));
+            }
+            scan_from = 0;
+            if (trace) { t_seen[k] = ms_since(); band_now = k; cudaEventRecord(bev[k][0], r); }
+            CU(c, cudaMemsetAsync(B.scratch, 0, 8, r), "clear tickets");
+            CU(c, launch_predict(rows_dev(r0, r1), r), "k_predict");
+            c->launches++;
+            // the filter stays one macroblock row behind the prediction (which reads unfiltered pixels
+            // of the row above), except at the very end
+            const int lf_end = k + 1 < nbands ? r1 - 1 : r1;
+            CU(c, launch_loopfilter(rows_dev(lf_done, lf_end), r), "k_loopfilter");
+            c->launches++;
+            lf_done = lf_end;
+            // rows whose pixels are final: all but the 3 above the next unfiltered macroblock edge
+            if (trace) cudaEventRecord(bev[k][1], r);
+            if ((rc = emit(lf_end < mbh ? 8 * lf_end - 3 : q_all)) != 0) return rc;
+            if (trace) cudaEventRecord(bev[k][2], r);
+        }
+        const double t_lastband = ms_since();
         CU(c, cudaStreamSynchronize(s), "sync");
         CU(c, cudaStreamSynchronize(r), "sync");
         for (int i = 0; i < n; i++)
@@ -870,8 +965,33 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         if (trace) {
             float ems = 0;
             cudaEventElapsedTime(&ems, c->ev[5], c->ev[6]);
-            std::fprintf(stderr, "[webpb200] decode_batch(device entropy, %d bands of %d rows) n=%d: host %.1f ms, k_entropy %.2f ms, total %.1f ms\n",
-                         nbands, band_rows, n, t_host, ems, ms_since());
+            if (copy_probe) {
+                float a = 0, b = 0;
+                cudaEventElapsedTime(&a, probe[0], probe[1]);
+                cudaEventElapsedTime(&b, probe[1], probe[2]);
+                std::fprintf(stderr, "  copy probe under k_entropy: linear 210 MB %.2f ms (%.1f GB/s), 2-D %d x 196608 %.2f ms (%.1f GB/s)\n", a, 209.7 / a, n, b,
+                             n * 196608e-6 / b);
+                for (auto& e : probe) cudaEventDestroy(e);
+            }
+            for (int k = 0; k < nbands; k++) {
+                float a = 0, b = 0, d = 0, y = 0;
+                cudaEventElapsedTime(&y, c->ev[5], bev[k][3]);
+                cudaEventElapsedTime(&a, c->ev[5], bev[k][0]);
+                cudaEventElapsedTime(&b, c->ev[5], bev[k][1]);
+                cudaEventElapsedTime(&d, c->ev[5], bev[k][2]);
+                std::fprintf(stderr, "  band %d rows %d-%d: seen by host at %.1f ms; on the device (from k_entropy start) kernels %.1f-%.1f, yuv done %.1f, copy done %.1f\n", k,
+                             band_start[k], band_start[k + 1], t_seen[k], a, b, y, d);
+                for (auto& e : bev[k]) cudaEventDestroy(e);
+            }
+            {
+                float a = 0, b = 0, d = 0;
+                cudaEventElapsedTime(&a, c->ev[8], c->ev[9]);
+                cudaEventElapsedTime(&b, c->ev[9], c->ev[10]);
+                cudaEventElapsedTime(&d, c->ev[10], c->ev[5]);
+                std::fprintf(stderr, "  device before k_entropy: clears %.2f ms, idle %.2f ms, uploads %.2f ms\n", a, b, d);
+            }
+            std::fprintf(stderr, "[webpb200] decode_batch(device entropy, %d bands) n=%d: host %.1f ms, launched at %.1f, k_entropy %.2f ms, last band seen at %.1f, total %.1f ms\n",
+                         nbands, n, t_host, t_launch, ems, t_lastband, ms_since());
         }
         int bad = 0;
         for (int i = 0; i < n; i++) {
