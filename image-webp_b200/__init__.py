@@ -292,6 +292,21 @@ class PinnedBuffer:
         self.free()
 
 
+class BufferList:
+    """A list of byte buffers with its C pointer / length tables built once (what a `Vec<&[u8]>` is to
+    the Rust API): pass it to BatchDecoder.decode instead of a plain list when the same buffers are
+    used for many calls, so that the per-call Python work is O(1)."""
+
+    def __init__(self, bufs):
+        self.bufs = [_as_u8(b) for b in bufs]
+        n = len(self.bufs)
+        self.ptrs = (C.c_void_p * n)(*[b.ctypes.data for b in self.bufs])
+        self.lens = (C.c_size_t * n)(*[b.size for b in self.bufs])
+
+    def __len__(self):
+        return len(self.bufs)
+
+
 class BatchDecoder:
     """Batched still-image decode on one GPU (webpb200_ctx): N x (WebPDecoder::new + read_image)."""
 
@@ -324,6 +339,12 @@ class BatchDecoder:
 
     def decode(self, files, outs=None, lossy_upsampling=BILINEAR, host_threads=0):
         """files: list of bytes/arrays.  Returns (outs, status list).  outs[i]: uint8 array (made if None)."""
+        if isinstance(files, BufferList) and isinstance(outs, BufferList):
+            n = len(files)
+            status = (C.c_int * n)()
+            self._check(lib().webpb200_decode_batch(self._h, files.ptrs, files.lens, n, outs.ptrs, outs.lens, status, lossy_upsampling,
+                                                    host_threads or (os.cpu_count() or 1)))
+            return outs.bufs, list(status)
         bufs = [_as_u8(f) for f in files]
         n = len(bufs)
         if outs is None:

@@ -861,10 +861,6 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         c->launches++;
     }
     if (trace) cudaEventRecord(c->ev[6], s);
-    if (trace) {
-        cudaEventSynchronize(c->ev[5]);
-        std::fprintf(stderr, "  k_entropy started at %.2f ms (enqueued at %.2f)\n", ms_since(), t_host);
-    }
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");

@@ -26,20 +26,15 @@
 #include "vp8_constants.h"
 
 // Build-time variants for A/B timing (tools/ab_build.sh); the defaults are the measured best.
-#ifndef ENT_TWO_FLO
-#define ENT_TWO_FLO 0    // normalisation shifts of both outcomes computed beside the comparison
-#endif
-#ifndef ENT_REG_ROWS
-#define ENT_REG_ROWS 0   // probability row of a coefficient held in registers (one LDS.128) instead of a byte load per symbol
-#endif
-#ifndef ENT_HEAD4
-#define ENT_HEAD4 0      // the four probabilities most tokens need (EOB, zero, one, small) come in one 32-bit load
-#endif
+// Tried and dropped because they were slower on B200 (every added instruction lengthens the one
+// lane's dependency chain): speculative normalisation of both outcomes beside the comparison
+// (+7 %), probability rows held in registers via LDS.128 (+8 %), the first four probabilities of
+// a row in one 32-bit load (+4 %), requesting bitstream bytes one refill ahead (+3 %).
 #ifndef ENT_ONE_SITE
-#define ENT_ONE_SITE 1   // one inlined copy of the block decoder (25-block loop) instead of three: less code to fetch
+#define ENT_ONE_SITE 1   // one inlined copy of the block decoder (25-block loop) instead of three: less code to fetch (-2 %)
 #endif
-#ifndef ENT_PREFETCH
-#define ENT_PREFETCH 0   // bitstream bytes requested one refill ahead
+#ifndef ENT_WIDE
+#define ENT_WIDE 1       // token probabilities stored as {p << 24, (256 - p) << 24}: split = hi32(range * a + b), one IMAD.WIDE
 #endif
 
 namespace webpb200 {
@@ -61,47 +56,31 @@ __constant__ int c_cat_base[4] = {11, 19, 35, 67};
 // Boolean decoder, 32-bit window: `bits` + 8 bits of `value` are valid; refilled with up to three
 // bytes when bits < 0.  Symbol for symbol the host reader of host_vp8.cc.
 //
-// One lane runs this alone, so what counts is the length of the dependent chain per symbol
-// (measured on B200, tools/micro/latbench.cu: ALU op 4-5 cycles, FLO 17, LDS 30, taken branch 15):
-// the normalisation shifts of both outcomes are computed next to the comparison instead of after
-// it, and the next three bytes are requested one refill ahead so that their latency is never waited for.
+// One lane runs this alone, so what counts is the number of instructions per symbol: measured on
+// B200 (tools/micro/latbench.cu) a dependent ALU op costs 4-5 cycles, FLO 17, LDS 30, a taken
+// branch about 15, and ncu shows the warp issuing one instruction every 5.5 cycles.
 struct DevBool {
     const uint8_t* base;
     uint32_t pos, len;
     uint32_t value, range;
     int bits;
-    uint32_t n0, n1, n2;  // bytes pos .. pos+2, requested at the previous refill (valid if pre)
-    bool pre, phantom, eof;
+    bool phantom, eof;
 
-    __device__ __forceinline__ void request() {
-        pre = ENT_PREFETCH && len - pos >= 3;
-        if (pre) {
-            n0 = __ldg(base + pos);
-            n1 = __ldg(base + pos + 1);
-            n2 = __ldg(base + pos + 2);
-        }
-    }
     __device__ __forceinline__ void init(const uint8_t* data, uint32_t n) {
         base = data; pos = 0; len = n; value = 0; range = 255; bits = -8; phantom = false; eof = false;
-        request();
     }
     __device__ __forceinline__ void load(const uint8_t* data, uint32_t n, const BoolState& s) {
         base = data; len = n; pos = s.pos; value = s.value; range = s.range; bits = s.bits;
         phantom = s.phantom != 0; eof = s.eof != 0;
-        request();
     }
     __device__ __forceinline__ void refill() {
-        if (pre) {
-            value = (value << 24) | (n0 << 16) | (n1 << 8) | n2;
-            pos += 3;
-            bits += 24;
-            request();
-        } else if (!ENT_PREFETCH && len - pos >= 3) {
+        const uint32_t left = len - pos;
+        if (left >= 3) {
             const uint32_t b0 = __ldg(base + pos), b1 = __ldg(base + pos + 1), b2 = __ldg(base + pos + 2);
             value = (value << 24) | (b0 << 16) | (b1 << 8) | b2;
             pos += 3;
             bits += 24;
-        } else if (pos < len) {
+        } else if (left > 0) {
             value = (value << 8) | __ldg(base + pos);
             pos += 1;
             bits += 8;
@@ -113,32 +92,37 @@ struct DevBool {
             eof = true;
         }
     }
+    // the decision and the renormalisation, given split = 1 + (((range - 1) * prob) >> 8)
+    __device__ __forceinline__ bool decide(uint32_t split) {
+        const uint32_t big = split << bits;
+        const bool one = value >= big;
+        value -= one ? big : 0u;
+        const uint32_t r = one ? range - split : split;
+        const int sh = __clz(r) - 24;
+        range = r << sh;
+        bits -= sh;
+        return one;
+    }
     __device__ __forceinline__ bool get(uint32_t prob) {
         if (bits < 0) {
             refill();
             if (bits < 0) return false;
         }
-        const uint32_t split = (range * prob + (256u - prob)) >> 8;  // = 1 + (((range - 1) * prob) >> 8)
-        const uint32_t rest = range - split;                         // >= 1
-        const uint32_t big = split << bits;
-        const bool one = value >= big;
-        value -= one ? big : 0u;
-#if ENT_TWO_FLO
-        const int s0 = __clz(split) - 24, s1 = __clz(rest) - 24;
-        range = one ? rest << s1 : split << s0;
-        bits -= one ? s1 : s0;
-#else
-        const uint32_t r = one ? rest : split;
-        const int sh = __clz(r) - 24;
-        range = r << sh;
-        bits -= sh;
-#endif
-        return one;
+        return decide((range * prob + (256u - prob)) >> 8);  // = 1 + (((range - 1) * prob) >> 8)
+    }
+    // prob given as e = {p << 24, (256 - p) << 24} (p = 0 stored as 1: both give split = 1 for any
+    // range <= 255): hi32(range * e.x + e.y) = (range * p + 256 - p) >> 8 in one wide multiply-add
+    __device__ __forceinline__ bool get(uint2 e) {
+        if (bits < 0) {
+            refill();
+            if (bits < 0) return false;
+        }
+        return decide((uint32_t)(((unsigned long long)range * e.x + e.y) >> 32));
     }
     __device__ __forceinline__ int tree(const int8_t* t, const uint8_t* probs) {
         int i = 0;
         do {
-            i = t[i + (int)get(probs[i >> 1])];
+            i = t[i + (int)get((uint32_t)probs[i >> 1])];
         } while (i > 0);
         return -i;
     }
@@ -148,115 +132,60 @@ struct DevBool {
 __device__ __forceinline__ uint32_t band_of(int n) { return ((n < 8 ? 0x65463210u : 0x76666666u) >> ((n & 7) * 4)) & 7u; }
 __device__ __forceinline__ uint32_t zigzag_of(int n) { return ((n < 8 ? 0x63258410u : 0xFEB7ADC9u) >> ((n & 7) * 4)) & 15u; }
 
-// one [band][ctx] row of token probabilities, 11 bytes padded to 16, held in registers
-__device__ __forceinline__ uint32_t prob_at(const uint4& r, int k) {
-    const uint32_t w = k < 4 ? r.x : k < 8 ? r.y : r.z;
-    return (w >> (8 * (k & 3))) & 0xffu;
+#if ENT_WIDE
+typedef uint2 TokenProb;   // {p << 24, (256 - p) << 24}
+__device__ __forceinline__ TokenProb make_token_prob(uint32_t p) {
+    if (p == 0) p = 1;
+    return make_uint2(p << 24, (256u - p) << 24);
 }
-
-// Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  rows = the plane's
-// [band][ctx] probability rows in shared memory.  The row of the next coefficient is requested as
-// soon as its context is known (before the sign and the extra bits are decoded), and the row a
-// zero token would lead to is requested ahead, so no shared-memory latency sits between symbols.
-// Returns "has coefficients".
-__device__ __forceinline__ int read_block(DevBool& br, const uint4* rows, int ctx, int first, int16_t* out) {
-#if ENT_REG_ROWS
-    int n = first;
-    uint4 row = rows[band_of(n) * 3 + ctx];
-    if (!br.get(prob_at(row, 0))) return 0;  // DCT_EOB straight away
-    for (;;) {
-        uint4 zrow = rows[band_of(n + 1) * 3];
-        while (!br.get(prob_at(row, 1))) {  // DCT_0: no EOB test before the next token
-            if (++n == 16) return 1;
-            row = zrow;
-            zrow = rows[band_of(n + 1) * 3];
-        }
-        int v;
-        uint4 nrow;
-        if (!br.get(prob_at(row, 2))) {
-            nrow = rows[band_of(n + 1) * 3 + 1];
-            v = 1;
-        } else {
-            nrow = rows[band_of(n + 1) * 3 + 2];
-            if (!br.get(prob_at(row, 3))) {
-                v = !br.get(prob_at(row, 4)) ? 2 : 3 + (int)br.get(prob_at(row, 5));
-            } else if (!br.get(prob_at(row, 6))) {
-                if (!br.get(prob_at(row, 7))) {
-                    v = 5 + (int)br.get(159);
-                } else {
-                    v = 7 + 2 * (int)br.get(165);
-                    v += (int)br.get(145);
-                }
-            } else {
-                const int b1 = br.get(prob_at(row, 8));
-                const int b0 = br.get(b1 ? prob_at(row, 10) : prob_at(row, 9));
-                const int cat = 2 * b1 + b0;
-                v = 0;
-                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get(*t);
-                v += c_cat_base[cat];
-            }
-        }
-        if (br.get(128)) v = -v;
-        out[zigzag_of(n)] = (int16_t)v;
-        if (++n == 16) return 1;
-        row = nrow;
-        if (!br.get(prob_at(row, 0))) return 1;  // DCT_EOB
-    }
 #else
-    const uint8_t* probs = reinterpret_cast<const uint8_t*>(rows);
-    int n = first;
-    const uint8_t* p = probs + (band_of(n) * 3 + ctx) * 16;
-#if ENT_HEAD4
-    uint32_t h4 = *reinterpret_cast<const uint32_t*>(p);
-#define HEAD(k) ((h4 >> (8 * (k))) & 0xffu)
-#define NEXT_ROW(q) (p = (q), h4 = *reinterpret_cast<const uint32_t*>(p))
-#else
-#define HEAD(k) p[k]
-#define NEXT_ROW(q) (p = (q))
+typedef uint8_t TokenProb;
+__device__ __forceinline__ TokenProb make_token_prob(uint32_t p) { return (uint8_t)p; }
 #endif
-    if (!br.get(HEAD(0))) return 0;
+constexpr int kTokenProbs = 4 * 8 * 3 * 11;  // [plane][band][ctx][node], common.rs COEFF_PROBS layout
+constexpr int kProbBytes = ((int)sizeof(TokenProb) * kTokenProbs + 15) & ~15;
+
+// Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  probs = the plane's
+// [band][ctx][node] table in shared memory.  Returns "has coefficients".
+__device__ __forceinline__ int read_block(DevBool& br, const TokenProb* probs, int ctx, int first, int16_t* out) {
+    int n = first;
+    const TokenProb* p = probs + (band_of(n) * 3 + ctx) * 11;
+    if (!br.get(p[0])) return 0;  // DCT_EOB straight away
     for (;;) {
-        while (!br.get(HEAD(1))) {
+        while (!br.get(p[1])) {  // DCT_0: no EOB test before the next token
             if (++n == 16) return 1;
-            NEXT_ROW(probs + band_of(n) * 48);
+            p = probs + band_of(n) * 33;
         }
         int v;
-        if (!br.get(HEAD(2))) {
+        if (!br.get(p[2])) {
             v = 1;
             ctx = 1;
         } else {
-            if (!br.get(HEAD(3))) {
+            if (!br.get(p[3])) {
                 v = !br.get(p[4]) ? 2 : 3 + (int)br.get(p[5]);
             } else if (!br.get(p[6])) {
                 if (!br.get(p[7])) {
-                    v = 5 + (int)br.get(159);
+                    v = 5 + (int)br.get(159u);
                 } else {
-                    v = 7 + 2 * (int)br.get(165);
-                    v += (int)br.get(145);
+                    v = 7 + 2 * (int)br.get(165u);
+                    v += (int)br.get(145u);
                 }
             } else {
                 const int b1 = br.get(p[8]);
                 const int b0 = br.get(p[9 + b1]);
                 const int cat = 2 * b1 + b0;
                 v = 0;
-                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get(*t);
+                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get((uint32_t)*t);
                 v += c_cat_base[cat];
             }
             ctx = 2;
         }
-        if (br.get(128)) v = -v;
-#ifndef ENT_EXP_NO_STORE
+        if (br.get(128u)) v = -v;
         out[zigzag_of(n)] = (int16_t)v;
-#else
-        if (v == 0x7fffffff) out[0] = 1;
-#endif
         if (++n == 16) return 1;
-        NEXT_ROW(probs + (band_of(n) * 3 + ctx) * 16);
-        if (!br.get(HEAD(0))) return 1;
+        p = probs + (band_of(n) * 3 + ctx) * 11;
+        if (!br.get(p[0])) return 1;  // DCT_EOB
     }
-#undef HEAD
-#undef NEXT_ROW
-#endif
 }
 
 struct EntropyArgs {
@@ -271,8 +200,6 @@ struct EntropyArgs {
     int max_mbw;
     unsigned int* rows_done;  // host-mapped, [frame * 8 + partition] = macroblock rows that partition has finished; or null
 };
-
-constexpr int kProbBytes = 4 * 8 * 3 * 16;
 
 struct EntropyCtl {
     int modes_done;   // macroblocks whose descriptor is in global memory
@@ -294,9 +221,8 @@ __device__ __forceinline__ bool wait_shared(volatile int* word, int need, volati
 
 __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     extern __shared__ __align__(16) uint8_t smem[];
-    // layout: prob rows uint4[4 planes][8 bands][3 ctx] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
-    uint8_t* s_probs = smem;
-    const uint4* s_rows = reinterpret_cast<const uint4*>(smem);
+    // layout: TokenProb[1056] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
+    TokenProb* s_probs = reinterpret_cast<TokenProb*>(smem);
     EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + kProbBytes);
     uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + kProbBytes + 64);
     uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + kProbBytes + 64 + 4 * (size_t)A.max_mbw);
@@ -308,7 +234,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     const webpb200_frame_desc& fd = A.frames[f];
     const int mbw = fd.mbw, mbh = fd.mbh;
 
-    for (int i = threadIdx.x; i < kProbBytes; i += blockDim.x) s_probs[i] = (i & 15) < 11 ? H.probs[(i >> 4) * 11 + (i & 15)] : 0;
+    for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) s_probs[i] = make_token_prob(H.probs[i]);
     for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(ctl)[i] = 0;
     for (int i = threadIdx.x; i < mbw; i += blockDim.x) s_top_bpred[i] = 0;
     __syncthreads();
@@ -425,7 +351,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                     if (k < 0) { tb = 0; lb = 0; plane = 1; blk = 24; }
                     else if (k < 16) { tb = 1 + (k & 3); lb = 1 + (k >> 2); plane = has_y2 ? 0 : 3; first = has_y2; }
                     else { const int c = k - 16; tb = 5 + 2 * (c >> 2) + (c & 1); lb = 5 + 2 * (c >> 2) + ((c >> 1) & 1); plane = 2; }
-                    const int n = read_block(br, s_rows + plane * 24, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
+                    const int n = read_block(br, s_probs + plane * 264, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
                     nflags |= (uint32_t)n << blk;
                     t = (t & ~(1u << tb)) | ((uint32_t)n << tb);
                     l = (l & ~(1u << lb)) | ((uint32_t)n << lb);
@@ -433,14 +359,14 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #else
                 int plane = 3, first = 0;
                 if (ymode != 4) {
-                    const int n = read_block(br, s_rows + 1 * 24, (t & 1) + (l & 1), 0, lv + 24 * 16);
+                    const int n = read_block(br, s_probs + 1 * 264, (t & 1) + (l & 1), 0, lv + 24 * 16);
                     t = (t & ~1u) | n;
                     l = (l & ~1u) | n;
                     nflags |= (uint32_t)n << 24;
                     plane = 0;
                     first = 1;
                 }
-                const uint4* yp = s_rows + plane * 24;
+                const TokenProb* yp = s_probs + plane * 264;
 #pragma unroll 1
                 for (int y = 0; y < 4; y++) {
                     int ll = (l >> (1 + y)) & 1;
@@ -463,7 +389,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #pragma unroll 1
                         for (int x = 0; x < 2; x++) {
                             const int k = blk0 + y * 2 + x;
-                            const int n = read_block(br, s_rows + 2 * 24, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
+                            const int n = read_block(br, s_probs + 2 * 264, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
                             nflags |= (uint32_t)n << k;
                             ll = n;
                             t = (t & ~(1u << (x + j))) | ((uint32_t)n << (x + j));
