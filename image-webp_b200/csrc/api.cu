@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <map>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -469,6 +470,20 @@ int items_from_files(const uint8_t* const* files, const size_t* lens, int n, int
 std::mutex g_default_mu;
 webpb200_ctx* g_default_ctx = nullptr;
 
+// pinned allocations handed out by webpb200_host_alloc: input files that live in one of them can
+// be sent to the device where they lie, without a staging copy
+std::mutex g_pinned_mu;
+std::map<uintptr_t, size_t> g_pinned;
+
+// [lo, hi) inside one pinned allocation?
+bool in_one_pinned_block(const uint8_t* lo, const uint8_t* hi) {
+    std::lock_guard<std::mutex> lock(g_pinned_mu);
+    auto it = g_pinned.upper_bound(reinterpret_cast<uintptr_t>(lo));
+    if (it == g_pinned.begin()) return false;
+    --it;
+    return reinterpret_cast<uintptr_t>(hi) <= it->first + it->second;
+}
+
 webpb200_ctx* default_ctx(int* status) {
     std::lock_guard<std::mutex> lock(g_default_mu);
     if (!g_default_ctx) {
@@ -536,10 +551,17 @@ extern "C" void* webpb200_host_alloc(size_t bytes) {
         cudaGetLastError();
         return nullptr;
     }
+    std::lock_guard<std::mutex> lock(g_pinned_mu);
+    g_pinned[reinterpret_cast<uintptr_t>(p)] = bytes ? bytes : 1;
     return p;
 }
 extern "C" void webpb200_host_free(void* p) {
-    if (p) cudaFreeHost(p);
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mu);
+        g_pinned.erase(reinterpret_cast<uintptr_t>(p));
+    }
+    cudaFreeHost(p);
 }
 
 extern "C" int webpb200_ctx_set_entropy(webpb200_ctx* c, int where) {
@@ -695,15 +717,33 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     cudaStream_t s = c->stream;
 
-    // bitstream arena: the VP8 chunks back to back (16-byte aligned starts)
+    // bitstream arena: the VP8 chunks back to back (16-byte aligned starts), staged through pinned
+    // memory -- unless the caller's files already lie in one pinned block (webpb200_host_alloc) and
+    // are reasonably dense there: then that stretch of the block goes to the device as it is
     std::vector<uint64_t> bit_off((size_t)n + 1, 0);
     for (int i = 0; i < n; i++) bit_off[i + 1] = bit_off[i] + (c->items[i].status ? 0 : ((uint64_t)c->items[i].vp8_len + 15) & ~uint64_t(15));
-    const uint64_t bits_bytes = std::max<uint64_t>(bit_off[n], 16);
-    CU(c, c->h_bits.reserve((size_t)bits_bytes), "pinned bitstreams");
+    uint64_t bits_bytes = std::max<uint64_t>(bit_off[n], 16);
+    const uint8_t* direct_base = nullptr;
+    {
+        const uint8_t *lo = nullptr, *hi = nullptr;
+        for (int i = 0; i < n; i++) {
+            const WorkItem& it = c->items[i];
+            if (it.status) continue;
+            if (!lo || it.vp8 < lo) lo = it.vp8;
+            if (!hi || it.vp8 + it.vp8_len > hi) hi = it.vp8 + it.vp8_len;
+        }
+        if (lo && (uint64_t)(hi - lo) <= 2 * bit_off[n] && in_one_pinned_block(lo, hi)) {
+            direct_base = lo;
+            bits_bytes = (uint64_t)(hi - lo);
+            for (int i = 0; i < n; i++) bit_off[i] = c->items[i].status ? 0 : (uint64_t)(c->items[i].vp8 - lo);
+        }
+    }
+    if (!direct_base) CU(c, c->h_bits.reserve((size_t)bits_bytes), "pinned bitstreams");
     CU(c, c->h_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "pinned entropy headers");
     CU(c, c->h_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "pinned status");
     if ((rc = reserve_device(c)) != 0) return rc;
-    CU(c, c->d_bits.reserve((size_t)bits_bytes), "device bitstreams");
+    CU(c, c->d_bits.reserve((size_t)bits_bytes + 16), "device bitstreams");
+    if (direct_base) CU(c, cudaMemcpyAsync(c->d_bits.p, direct_base, (size_t)bits_bytes, cudaMemcpyHostToDevice, s), "H2D bitstreams");
     CU(c, c->d_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "device entropy headers");
     CU(c, c->d_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "device status");
     Vp8EntropyHdr* hdrs = reinterpret_cast<Vp8EntropyHdr*>(c->h_ehdr.p);
@@ -746,7 +786,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
                 if (!it.status) {
                     const int st = vp8_parse_header(it.vp8, it.vp8_len, &frames[i], &eh);
                     if (st) drop(i, st);
-                    else std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
+                    else if (!direct_base) std::memcpy(c->h_bits.p + bit_off[i], it.vp8, it.vp8_len);
                     eh.data_off = bit_off[i];
                 }
                 left[slice_of[i]].fetch_sub(1, std::memory_order_release);
@@ -757,6 +797,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         cudaError_t e = cudaSuccess;
         for (int k = 0; k < nslices; k++) {
             while (left[k].load(std::memory_order_acquire) > 0) std::this_thread::yield();
+            if (direct_base) continue;
             const uint64_t b0 = bit_off[k ? slice_end[k - 1] : 0], b1 = bit_off[slice_end[k]];
             if (b1 > b0 && e == cudaSuccess) e = cudaMemcpyAsync(c->d_bits.p + b0, c->h_bits.p + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, s);
         }
@@ -852,6 +893,10 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
             std::memset(c->h_rows, 0, sizeof(unsigned int) * 8 * (size_t)n);
         }
     }
+    // Let the clears and uploads drain before the long-lived entropy blocks are placed: launched
+    // right behind them, the 1024 blocks usually ended up unevenly spread over the SMs and the kernel
+    // ran 9.5 % longer (42.9 vs 39.2 ms, bimodal); the wait itself costs nothing that is not needed anyway.
+    CU(c, cudaStreamSynchronize(s), "sync before k_entropy");
     CU(c, cudaEventRecord(c->ev[7], s), "event");  // every input of the reconstruction kernels is on the device
     if (trace) cudaEventRecord(c->ev[5], s);
     if (c->total_mbs) {

@@ -164,3 +164,21 @@ def test_band_pipeline_with_a_damaged_frame(W, dev, host, synth):
     for i in range(n):
         if s_dev[i] == 0:
             assert np.array_equal(o_dev[i], o_host[i]), i
+
+
+def test_inputs_in_pinned_memory_are_uploaded_in_place(W, dev, synth):
+    """Files that lie in one block from webpb200_host_alloc skip the staging copy (the block goes to the
+    device as it is, gaps included): same pixels as from ordinary memory."""
+    files = [synth.webp_simple(synth.vp8_frame(96 + 16 * (i % 3), 64, seed=300 + i, log2_parts=i % 3)) for i in range(40)]
+    want, st0 = dev.decode(files)
+    pin = W.PinnedBuffer(sum(len(f) + 100 for f in files))
+    views, off = [], 7  # odd start, ragged gaps
+    for i, f in enumerate(files):
+        pin.array[off:off + len(f)] = np.frombuffer(f, dtype=np.uint8)
+        views.append(pin.array[off:off + len(f)])
+        off += len(f) + (i * 13) % 90
+    got, st1 = dev.decode(views)
+    assert st0 == st1 == [0] * len(files)
+    for a, b in zip(want, got):
+        assert np.array_equal(a, b)
+    pin.free()
