@@ -34,7 +34,10 @@
 #define ENT_ONE_SITE 1   // one inlined copy of the block decoder (25-block loop) instead of three: less code to fetch (-2 %)
 #endif
 #ifndef ENT_WIDE
-#define ENT_WIDE 1       // token probabilities stored as {p << 24, (256 - p) << 24}: split = hi32(range * a + b), one IMAD.WIDE
+#define ENT_WIDE 2       // token probabilities stored as {p << 24, (256 - p) << 24}: split = hi32(range * a + b), one IMAD.WIDE; 2 = 16-byte entries
+#endif
+#ifndef ENT_LUT
+#define ENT_LUT 1        // band / zigzag of coefficient n from a shared-memory table instead of immediates
 #endif
 
 namespace webpb200 {
@@ -119,6 +122,14 @@ struct DevBool {
         }
         return decide((uint32_t)(((unsigned long long)range * e.x + e.y) >> 32));
     }
+    __device__ __forceinline__ bool get(uint4 e) {
+        if (bits < 0) {
+            refill();
+            if (bits < 0) return false;
+        }
+        const unsigned long long addend = (unsigned long long)e.x | ((unsigned long long)e.y << 32);
+        return decide((uint32_t)(((unsigned long long)range * e.z + addend) >> 32));
+    }
     __device__ __forceinline__ int tree(const int8_t* t, const uint8_t* probs) {
         int i = 0;
         do {
@@ -132,7 +143,15 @@ struct DevBool {
 __device__ __forceinline__ uint32_t band_of(int n) { return ((n < 8 ? 0x65463210u : 0x76666666u) >> ((n & 7) * 4)) & 7u; }
 __device__ __forceinline__ uint32_t zigzag_of(int n) { return ((n < 8 ? 0x63258410u : 0xFEB7ADC9u) >> ((n & 7) * 4)) & 15u; }
 
-#if ENT_WIDE
+#if ENT_WIDE == 2
+// 16-byte entries {(256 - p) << 24, 0, p << 24, -}: one LDS.128 puts the 64-bit addend of the wide
+// multiply-add into an aligned register pair and the multiplier next to it, no moves needed
+typedef uint4 TokenProb;
+__device__ __forceinline__ TokenProb make_token_prob(uint32_t p) {
+    if (p == 0) p = 1;
+    return make_uint4((256u - p) << 24, 0u, p << 24, 0u);
+}
+#elif ENT_WIDE
 typedef uint2 TokenProb;   // {p << 24, (256 - p) << 24}
 __device__ __forceinline__ TokenProb make_token_prob(uint32_t p) {
     if (p == 0) p = 1;
@@ -147,7 +166,55 @@ constexpr int kProbBytes = ((int)sizeof(TokenProb) * kTokenProbs + 15) & ~15;
 
 // Tokens of one 4x4 block (host_vp8.cc read_block; reference mod.rs:785-872).  probs = the plane's
 // [band][ctx][node] table in shared memory.  Returns "has coefficients".
-__device__ __forceinline__ int read_block(DevBool& br, const TokenProb* probs, int ctx, int first, int16_t* out) {
+__device__ __forceinline__ int read_block(DevBool& br, const TokenProb* probs, const uint32_t* lut, int ctx, int first, int16_t* out) {
+#if ENT_LUT
+    // band(n) and zigzag(n) come from one shared-memory word fetched when n advances: the load is
+    // issued a whole symbol before its result is needed, and replaces about eight ALU instructions
+    const char* base = reinterpret_cast<const char*>(probs);
+    int n = first;
+    uint32_t w = lut[n];
+    const TokenProb* p = reinterpret_cast<const TokenProb*>(base + (w & 0xffffu)) + ctx * 11;
+    if (!br.get(p[0])) return 0;  // DCT_EOB straight away
+    for (;;) {
+        while (!br.get(p[1])) {  // DCT_0: no EOB test before the next token
+            if (++n == 16) return 1;
+            w = lut[n];
+            p = reinterpret_cast<const TokenProb*>(base + (w & 0xffffu));
+        }
+        const uint32_t wn = lut[n + 1];
+        int v;
+        if (!br.get(p[2])) {
+            v = 1;
+            ctx = 1;
+        } else {
+            if (!br.get(p[3])) {
+                v = !br.get(p[4]) ? 2 : 3 + (int)br.get(p[5]);
+            } else if (!br.get(p[6])) {
+                if (!br.get(p[7])) {
+                    v = 5 + (int)br.get(159u);
+                } else {
+                    v = 7 + 2 * (int)br.get(165u);
+                    v += (int)br.get(145u);
+                }
+            } else {
+                const int b1 = br.get(p[8]);
+                const int b0 = br.get(p[9 + b1]);
+                const int cat = 2 * b1 + b0;
+                v = 0;
+                for (const uint8_t* t = c_cat_probs[cat]; *t; ++t) v = v + v + (int)br.get((uint32_t)*t);
+                v += c_cat_base[cat];
+            }
+            ctx = 2;
+        }
+        if (br.get(128u)) v = -v;
+        *reinterpret_cast<int16_t*>(reinterpret_cast<char*>(out) + (w >> 16)) = (int16_t)v;
+        if (++n == 16) return 1;
+        w = wn;
+        p = reinterpret_cast<const TokenProb*>(base + (w & 0xffffu)) + ctx * 11;
+        if (!br.get(p[0])) return 1;  // DCT_EOB
+    }
+#else
+    (void)lut;
     int n = first;
     const TokenProb* p = probs + (band_of(n) * 3 + ctx) * 11;
     if (!br.get(p[0])) return 0;  // DCT_EOB straight away
@@ -186,6 +253,7 @@ __device__ __forceinline__ int read_block(DevBool& br, const TokenProb* probs, i
         p = probs + (band_of(n) * 3 + ctx) * 11;
         if (!br.get(p[0])) return 1;  // DCT_EOB
     }
+#endif
 }
 
 struct EntropyArgs {
@@ -205,7 +273,9 @@ struct EntropyCtl {
     int modes_done;   // macroblocks whose descriptor is in global memory
     int abort;        // some warp hit the end of its partition: the frame is a BitStreamError
     int row_prog[9];  // ring slot -> (row << 16) | macroblocks finished, monotone per slot
+    uint32_t lut[17]; // coefficient n -> byte offset of band(n)'s context-0 row | zigzag(n) * 2 << 16  (ENT_LUT)
 };
+constexpr int kCtlBytes = 128;
 
 // spin on a shared-memory word until it reaches `need` or the frame is aborted
 __device__ __forceinline__ bool wait_shared(volatile int* word, int need, volatile int* abort) {
@@ -224,8 +294,8 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     // layout: TokenProb[1056] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
     TokenProb* s_probs = reinterpret_cast<TokenProb*>(smem);
     EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + kProbBytes);
-    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + kProbBytes + 64);
-    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + kProbBytes + 64 + 4 * (size_t)A.max_mbw);
+    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + kProbBytes + kCtlBytes);
+    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + kProbBytes + kCtlBytes + 4 * (size_t)A.max_mbw);
 
     const int f = A.frame_first + blockIdx.x;
     const Vp8EntropyHdr& H = A.hdrs[f];
@@ -237,6 +307,8 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) s_probs[i] = make_token_prob(H.probs[i]);
     for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(ctl)[i] = 0;
     for (int i = threadIdx.x; i < mbw; i += blockDim.x) s_top_bpred[i] = 0;
+    __syncthreads();
+    if (threadIdx.x < 17) ctl->lut[threadIdx.x] = band_of(threadIdx.x) * 33u * (uint32_t)sizeof(TokenProb) | (zigzag_of(threadIdx.x & 15) * 2u) << 16;
     __syncthreads();
 
     const int warp = threadIdx.x >> 5;
@@ -351,7 +423,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                     if (k < 0) { tb = 0; lb = 0; plane = 1; blk = 24; }
                     else if (k < 16) { tb = 1 + (k & 3); lb = 1 + (k >> 2); plane = has_y2 ? 0 : 3; first = has_y2; }
                     else { const int c = k - 16; tb = 5 + 2 * (c >> 2) + (c & 1); lb = 5 + 2 * (c >> 2) + ((c >> 1) & 1); plane = 2; }
-                    const int n = read_block(br, s_probs + plane * 264, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
+                    const int n = read_block(br, s_probs + plane * 264, ctl->lut, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
                     nflags |= (uint32_t)n << blk;
                     t = (t & ~(1u << tb)) | ((uint32_t)n << tb);
                     l = (l & ~(1u << lb)) | ((uint32_t)n << lb);
@@ -359,7 +431,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #else
                 int plane = 3, first = 0;
                 if (ymode != 4) {
-                    const int n = read_block(br, s_probs + 1 * 264, (t & 1) + (l & 1), 0, lv + 24 * 16);
+                    const int n = read_block(br, s_probs + 1 * 264, ctl->lut, (t & 1) + (l & 1), 0, lv + 24 * 16);
                     t = (t & ~1u) | n;
                     l = (l & ~1u) | n;
                     nflags |= (uint32_t)n << 24;
@@ -373,7 +445,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #pragma unroll 1
                     for (int x = 0; x < 4; x++) {
                         const int k = y * 4 + x;
-                        const int n = read_block(br, yp, ((t >> (1 + x)) & 1) + ll, first, lv + k * 16);
+                        const int n = read_block(br, yp, ctl->lut, ((t >> (1 + x)) & 1) + ll, first, lv + k * 16);
                         nflags |= (uint32_t)n << k;
                         ll = n;
                         t = (t & ~(2u << x)) | ((uint32_t)n << (1 + x));
@@ -389,7 +461,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
 #pragma unroll 1
                         for (int x = 0; x < 2; x++) {
                             const int k = blk0 + y * 2 + x;
-                            const int n = read_block(br, s_probs + 2 * 264, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
+                            const int n = read_block(br, s_probs + 2 * 264, ctl->lut, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
                             nflags |= (uint32_t)n << k;
                             ll = n;
                             t = (t & ~(1u << (x + j))) | ((uint32_t)n << (x + j));
@@ -430,7 +502,7 @@ void upload_entropy_tables_once() {
 }
 
 size_t entropy_smem_bytes(int max_parts, int max_mbw) {
-    return kProbBytes + 64 + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw;
+    return kProbBytes + kCtlBytes + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw;
 }
 
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
@@ -443,7 +515,7 @@ cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const
     a.max_mbw = (int)((b.max_w + 15) / 16);
     a.rows_done = rows_done;
     const size_t smem = entropy_smem_bytes(max_parts, a.max_mbw);
-    static_assert(sizeof(EntropyCtl) <= 64, "EntropyCtl outgrew its slot");
+    static_assert(sizeof(EntropyCtl) <= kCtlBytes, "EntropyCtl outgrew its slot");
     k_entropy<<<b.n_frames, 32 * (1 + max_parts), smem, s>>>(a);
     return cudaGetLastError();
 }
