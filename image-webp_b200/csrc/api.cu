@@ -856,7 +856,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     int band_start[kMaxBands + 1] = {0};
     size_t dpitch = 0, spitch = 0;
     {
-        static const int want = [] { const char* e = std::getenv("WEBPB200_BANDS"); return e ? std::atoi(e) : 8; }();
+        static const int want = [] { const char* e = std::getenv("WEBPB200_BANDS"); return e ? std::atoi(e) : 10; }();
         bool ok = want > 1 && n >= 2 && c->alpha_bytes == 0 && c->total_mbs >= 16384 && frames[0].mbh >= 8;
         for (int i = 0; ok && i < n; i++) {
             const webpb200_frame_desc& f = frames[i];
@@ -875,8 +875,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
             int row = 0;
             while (row < mbh) {
                 const int left_bands = target - nbands;
-                int size = left_bands <= 1 ? mbh - row : std::max(2, (mbh - row + 3) / 4);
-                if (mbh - row - size == 1) size++;  // no one-row band at the end
+                const int size = left_bands <= 1 ? mbh - row : std::max(1, (mbh - row + 3) / 4);
                 band_start[nbands++] = row;
                 row += std::min(size, mbh - row);
             }

@@ -278,12 +278,18 @@ struct EntropyCtl {
 constexpr int kCtlBytes = 128;
 
 // spin on a shared-memory word until it reaches `need` or the frame is aborted
-__device__ __forceinline__ bool wait_shared(volatile int* word, int need, volatile int* abort) {
+// (a wait that never ends would be a scheduling bug, not a data property: after a few seconds the
+// frame is failed with WEBPB200_ERR_CUDA instead of hanging the device)
+__device__ __forceinline__ bool wait_shared(volatile int* word, int need, volatile int* abort, int* status) {
     unsigned spins = 0;
     while (*word < need) {
         if (*abort) return false;
         __nanosleep(64);
-        if (++spins > (1u << 26)) return false;  // about a minute: a scheduling bug, not a data property
+        if (++spins > (1u << 26)) {
+            *status = WEBPB200_ERR_CUDA;
+            *abort = 1;
+            return false;
+        }
     }
     __threadfence_block();
     return true;
@@ -399,10 +405,10 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
         for (int mbx = 0; mbx < mbw; mbx++) {
             const int mbi = mby * mbw + mbx;
             if (seen_modes <= mbi) {
-                if (!wait_shared(v_modes, mbi + 1, v_abort)) return;
+                if (!wait_shared(v_modes, mbi + 1, v_abort, A.status + f)) return;
                 seen_modes = *v_modes;
             }
-            if (P > 1 && mby > 0 && !wait_shared(up_prog, ((mby - 1) << 16) | (mbx + 1), v_abort)) return;
+            if (P > 1 && mby > 0 && !wait_shared(up_prog, ((mby - 1) << 16) | (mbx + 1), v_abort, A.status + f)) return;
             uint32_t t = mby > 0 ? prev[mbx] : 0;  // top context: bit 0 Y2, 1-4 Y columns, 5-6 U, 7-8 V
             const uint32_t w0 = *reinterpret_cast<const volatile uint32_t*>(mbs + mbi);
             const int ymode = w0 & 0xff;
