@@ -95,16 +95,24 @@ struct DevBool {
             eof = true;
         }
     }
-    // the decision and the renormalisation, given split = 1 + (((range - 1) * prob) >> 8)
+    // The decision and the renormalisation, given split = 1 + (((range - 1) * prob) >> 8).
+    // Two arms, each with its own renormalisation: every caller branches on the result at once, so
+    // the comparison is made once and nothing has to be selected (-4 % against the select form).
+    // (Folding the bits < 0 test into the one-arm through a saturating shift was slower: +8 %.)
     __device__ __forceinline__ bool decide(uint32_t split) {
         const uint32_t big = split << bits;
-        const bool one = value >= big;
-        value -= one ? big : 0u;
-        const uint32_t r = one ? range - split : split;
-        const int sh = __clz(r) - 24;
-        range = r << sh;
+        if (value >= big) {
+            value -= big;
+            const uint32_t r = range - split;
+            const int sh = __clz(r) - 24;
+            range = r << sh;
+            bits -= sh;
+            return true;
+        }
+        const int sh = __clz(split) - 24;
+        range = split << sh;
         bits -= sh;
-        return one;
+        return false;
     }
     __device__ __forceinline__ bool get(uint32_t prob) {
         if (bits < 0) {
