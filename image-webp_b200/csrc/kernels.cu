@@ -18,6 +18,7 @@
 // reads of neighbour rows.
 #include "kernels.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace webpb200 {
@@ -1307,6 +1308,7 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     // many images: the row above is usually long finished, so publish progress (a release fence each
     // time) only every 4th macroblock; few images: rows really wait on each other, publish every one
     a.publish_every = b.n_frames >= 64 ? 4 : 1;
+    if (const char* e = std::getenv("WEBPB200_PUB_P")) a.publish_every = std::atoi(e);
     static int blocks = 0;
     if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_predict), kThreads, b.sm_count);
     int grid = blocks;
@@ -1328,6 +1330,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
     a.publish_every = b.n_frames >= 64 ? 4 : 1;
+    if (const char* e = std::getenv("WEBPB200_PUB_F")) a.publish_every = std::atoi(e);
     static int blocks = 0;
     if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_loopfilter), kThreads, b.sm_count);
     int grid = blocks;
