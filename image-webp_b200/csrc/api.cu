@@ -711,23 +711,21 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     std::vector<WorkItem> items;
     items_from_files(files, lens, n, host_threads, &items);
     const double t_items = ms_since();
-    int rc = layout_items(c, std::move(items), upsampling, host_threads, false);
-    if (rc) return rc;
-    const double t_layout = ms_since();
-    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     cudaStream_t s = c->stream;
+    int rc = 0;
 
-    // bitstream arena: the VP8 chunks back to back (16-byte aligned starts), staged through pinned
-    // memory -- unless the caller's files already lie in one pinned block (webpb200_host_alloc) and
-    // are reasonably dense there: then that stretch of the block goes to the device as it is
+    // Bitstream arena.  If the caller's files already lie in one pinned block (webpb200_host_alloc)
+    // and are reasonably dense there, that stretch of the block goes to the device as it is, and at
+    // once: the upload then runs under the layout and header work below.  Otherwise the VP8 chunks
+    // are staged back to back (16-byte aligned starts) through pinned memory further down.
     std::vector<uint64_t> bit_off((size_t)n + 1, 0);
-    for (int i = 0; i < n; i++) bit_off[i + 1] = bit_off[i] + (c->items[i].status ? 0 : ((uint64_t)c->items[i].vp8_len + 15) & ~uint64_t(15));
+    for (int i = 0; i < n; i++) bit_off[i + 1] = bit_off[i] + (items[i].status ? 0 : ((uint64_t)items[i].vp8_len + 15) & ~uint64_t(15));
     uint64_t bits_bytes = std::max<uint64_t>(bit_off[n], 16);
     const uint8_t* direct_base = nullptr;
     {
         const uint8_t *lo = nullptr, *hi = nullptr;
         for (int i = 0; i < n; i++) {
-            const WorkItem& it = c->items[i];
+            const WorkItem& it = items[i];
             if (it.status) continue;
             if (!lo || it.vp8 < lo) lo = it.vp8;
             if (!hi || it.vp8 + it.vp8_len > hi) hi = it.vp8 + it.vp8_len;
@@ -735,15 +733,21 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         if (lo && (uint64_t)(hi - lo) <= 2 * bit_off[n] && in_one_pinned_block(lo, hi)) {
             direct_base = lo;
             bits_bytes = (uint64_t)(hi - lo);
-            for (int i = 0; i < n; i++) bit_off[i] = c->items[i].status ? 0 : (uint64_t)(c->items[i].vp8 - lo);
+            for (int i = 0; i < n; i++) bit_off[i] = items[i].status ? 0 : (uint64_t)(items[i].vp8 - lo);
+            cudaSetDevice(c->device);
+            CU(c, c->d_bits.reserve((size_t)bits_bytes + 16), "device bitstreams");
+            CU(c, cudaMemcpyAsync(c->d_bits.p, direct_base, (size_t)bits_bytes, cudaMemcpyHostToDevice, s), "H2D bitstreams");
         }
     }
+    rc = layout_items(c, std::move(items), upsampling, host_threads, false);
+    if (rc) return rc;
+    const double t_layout = ms_since();
+    webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     if (!direct_base) CU(c, c->h_bits.reserve((size_t)bits_bytes), "pinned bitstreams");
     CU(c, c->h_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "pinned entropy headers");
     CU(c, c->h_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "pinned status");
     if ((rc = reserve_device(c)) != 0) return rc;
-    CU(c, c->d_bits.reserve((size_t)bits_bytes + 16), "device bitstreams");
-    if (direct_base) CU(c, cudaMemcpyAsync(c->d_bits.p, direct_base, (size_t)bits_bytes, cudaMemcpyHostToDevice, s), "H2D bitstreams");
+    if (!direct_base) CU(c, c->d_bits.reserve((size_t)bits_bytes + 16), "device bitstreams");
     CU(c, c->d_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "device entropy headers");
     CU(c, c->d_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "device status");
     Vp8EntropyHdr* hdrs = reinterpret_cast<Vp8EntropyHdr*>(c->h_ehdr.p);
