@@ -159,6 +159,7 @@ def main():
     dist = sh.init_distributed()
     cores = os.cpu_count() or 1
     host_threads = max(1, cores // world)
+    near = sh.bind_near_gpu(W.device_pci_bus_id(local_rank)) if world > 1 else None  # before any pinned allocation
     per_gpu = args.images
 
     files = make_files(rank, per_gpu, host_threads)
@@ -238,7 +239,8 @@ def main():
                          "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass"},
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
-                    "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum},
+                    "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum,
+                    "numa_bound_cpus": len(near) if near else None},
             "gpu_launches": int(launches),
             "clocks": clocks,
         }

@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
-    "webpb200_last_transfer",
+    "webpb200_last_transfer", "webpb200_device_pci_bus_id",
 ]
 
 
@@ -140,6 +140,7 @@ def lib():
     L.webpb200_batch_time.argtypes = [vp, C.c_uint, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.webpb200_batch_size.argtypes = [vp, pi] + [C.POINTER(C.c_uint64)] * 4
     L.webpb200_batch_get_planes.argtypes = [vp, i32, vp, vp, vp]
+    L.webpb200_device_pci_bus_id.argtypes = [i32, C.c_char_p, i32]
     L.webpb200_last_transfer.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(i32)]
     L.webpb200_ctx_set_entropy.argtypes = [vp, i32]
     L.webpb200_batch_download_packed.argtypes = [vp, i32, vp, vp]
@@ -290,6 +291,11 @@ class PinnedBuffer:
 
     def __del__(self):
         self.free()
+
+
+def device_pci_bus_id(device):
+    buf = C.create_string_buffer(32)
+    return buf.value.decode().lower() if lib().webpb200_device_pci_bus_id(device, buf, 32) == 0 else None
 
 
 class BufferList:

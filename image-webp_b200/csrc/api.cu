@@ -507,6 +507,15 @@ extern "C" int webpb200_device_count(void) {
     return n;
 }
 
+extern "C" int webpb200_device_pci_bus_id(int device, char* buf, int len) {
+    if (!buf || len < 13) return -WEBPB200_ERR_INVALID_PARAM;
+    if (cudaDeviceGetPCIBusId(buf, len, device) != cudaSuccess) {
+        cudaGetLastError();
+        return -WEBPB200_ERR_NO_DEVICE;
+    }
+    return 0;
+}
+
 extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
     *out = nullptr;
     if (device < 0 || device >= webpb200_device_count()) return WEBPB200_ERR_NO_DEVICE;

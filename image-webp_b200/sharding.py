@@ -54,3 +54,29 @@ def aggregate(dist, units_local, ms_local):
     dist.all_reduce(t_units, op=dist.ReduceOp.SUM)
     dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     return float(t_units.item()), float(t_ms.item())
+
+
+def bind_near_gpu(pci_bus_id):
+    """Pin this process to the CPUs of the NUMA node the GPU hangs off, so that its threads and the
+    pinned buffers it allocates afterwards are local to the GPU's PCIe root (with 8 ranks on two sockets
+    an unbound rank sends half of its D2H traffic across the socket link).  Returns the CPU list used,
+    or None when the topology is not exposed (single node, container without sysfs)."""
+    import os
+    try:
+        with open("/sys/bus/pci/devices/%s/numa_node" % pci_bus_id) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except (OSError, ValueError):
+        return None

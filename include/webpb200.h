@@ -143,6 +143,9 @@ typedef struct webpb200_ctx webpb200_ctx;
 
 int webpb200_device_count(void);                       /* 0 when no CUDA device is usable */
 int webpb200_ctx_create(int device, webpb200_ctx** out);
+/* PCI address of a device ("0000:1b:00.0"), so that a host process can place its threads and its pinned
+ * buffers on the NUMA node the GPU hangs off (see sharding.bind_near_gpu). */
+int webpb200_device_pci_bus_id(int device, char* buf, int len);
 void webpb200_ctx_destroy(webpb200_ctx* c);
 const char* webpb200_last_cuda_error(const webpb200_ctx* c);
 /* Page-locked host memory for input/output buffers (copies to and from it run asynchronously
