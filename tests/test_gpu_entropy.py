@@ -182,3 +182,41 @@ def test_inputs_in_pinned_memory_are_uploaded_in_place(W, dev, synth):
     for a, b in zip(want, got):
         assert np.array_equal(a, b)
     pin.free()
+
+
+def test_randomised_streams_device_vs_host(W, dev, host, synth):
+    """120 frames with randomly drawn stream parameters (size incl. 1-pixel-wide and single-macroblock
+    frames, 1/2/4/8 partitions, segments with and without a map, skip probabilities, probability
+    updates, every coefficient profile, quantiser range), a third of them cut at a random place:
+    descriptors, levels, statuses and pixels of the device entropy stage equal the host's."""
+    rng = np.random.default_rng(20261107)
+    profiles = ["realistic", "uniform", "extreme", "all_tm", "bpred_ld_vl", "zero_tails"]
+    files = []
+    for i in range(120):
+        w = int(rng.choice([1, 15, 16, 17, 33, 64, 100, 160, 250]))
+        h = int(rng.choice([1, 16, 31, 48, 65, 128, 200]))
+        seg = int(rng.integers(0, 5))
+        kw = dict(width=w, height=h, seed=5000 + i, filter_type=int(rng.integers(0, 2)), filter_level=int(rng.integers(0, 64)),
+                  sharpness=int(rng.integers(0, 8)), log2_parts=int(rng.integers(0, 4)), yac_abs=int(rng.integers(0, 128)),
+                  profile=str(rng.choice(profiles)), update_probs=int(rng.integers(0, 2)))
+        if seg:
+            kw.update(segments=seg, seg_quant=tuple(int(v) for v in rng.integers(0, 100, 4)), seg_lf=tuple(int(v) for v in rng.integers(0, 60, 4)),
+                      seg_probs=tuple(int(v) for v in rng.integers(1, 255, 3)))
+        if rng.integers(0, 2):
+            kw.update(prob_skip=int(rng.integers(1, 255)), p_skip=float(rng.choice([0.0, 0.1, 0.5, 1.0])))
+        try:
+            f = synth.webp_simple(synth.vp8_frame(**kw))
+        except ValueError:
+            continue
+        if i % 3 == 2:
+            f = f[:int(rng.integers(21, len(f)))]
+        files.append(f)
+    assert len(files) > 100
+    o_dev, s_dev = dev.decode(files)
+    o_host, s_host = host.decode(files)
+    assert s_dev == s_host
+    assert sum(1 for s in s_dev if s == 0) > 60 and any(s_dev)
+    for i, (a, b, st) in enumerate(zip(o_dev, o_host, s_dev)):
+        if st == 0:
+            assert np.array_equal(a, b), i
+    _check_packed(W, dev, files, s_dev)
