@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
-    "webpb200_last_transfer", "webpb200_device_pci_bus_id",
+    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device",
 ]
 
 
@@ -140,6 +140,7 @@ def lib():
     L.webpb200_batch_time.argtypes = [vp, C.c_uint, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.webpb200_batch_size.argtypes = [vp, pi] + [C.POINTER(C.c_uint64)] * 4
     L.webpb200_batch_get_planes.argtypes = [vp, i32, vp, vp, vp]
+    L.webpb200_batch_output_device.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(u32), C.POINTER(u32), C.POINTER(i32)]
     L.webpb200_device_pci_bus_id.argtypes = [i32, C.c_char_p, i32]
     L.webpb200_last_transfer.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(i32)]
     L.webpb200_ctx_set_entropy.argtypes = [vp, i32]
@@ -298,6 +299,14 @@ def device_pci_bus_id(device):
     return buf.value.decode().lower() if lib().webpb200_device_pci_bus_id(device, buf, 32) == 0 else None
 
 
+class DeviceImage:
+    """A decoded image in device memory (borrowed from a BatchDecoder): uint8, (height, width, channels)."""
+
+    def __init__(self, ptr, shape):
+        self.ptr, self.shape = ptr, shape
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
 class BufferList:
     """A list of byte buffers with its C pointer / length tables built once (what a `Vec<&[u8]>` is to
     the Rust API): pass it to BatchDecoder.decode instead of a plain list when the same buffers are
@@ -328,7 +337,10 @@ class BatchDecoder:
 
     def close(self):
         if getattr(self, "_h", None):
-            lib().webpb200_ctx_destroy(self._h)
+            try:
+                lib().webpb200_ctx_destroy(self._h)
+            except TypeError:  # interpreter shutdown: the module globals are already gone
+                pass
             self._h = None
 
     __del__ = close
@@ -420,6 +432,25 @@ class BatchDecoder:
     def set_entropy(self, where):
         """Where decode() runs the boolean-entropy decode: ENTROPY_HOST (threads) or ENTROPY_DEVICE (k_entropy)."""
         self._check(lib().webpb200_ctx_set_entropy(self._h, where))
+
+    def decode_to_device(self, files, lossy_upsampling=BILINEAR, host_threads=0):
+        """Decode and leave the images in device memory: returns (list of objects exposing
+        __cuda_array_interface__ with shape (h, w, channels), status list).  torch.as_tensor(x, device="cuda")
+        or cupy.asarray(x) wraps one without a copy.  The memory is the context's: valid until its next call."""
+        fl = files if isinstance(files, BufferList) else BufferList(files)
+        n = len(fl)
+        status = (C.c_int * n)()
+        self._keep = fl
+        self._check(lib().webpb200_decode_batch(self._h, fl.ptrs, fl.lens, n, None, None, status, lossy_upsampling,
+                                                host_threads or (os.cpu_count() or 1)))
+        out = []
+        for i in range(n):
+            p, ln, w, h, b = C.c_void_p(), C.c_size_t(), C.c_uint32(), C.c_uint32(), C.c_int()
+            if status[i] or lib().webpb200_batch_output_device(self._h, i, C.byref(p), C.byref(ln), C.byref(w), C.byref(h), C.byref(b)):
+                out.append(None)
+                continue
+            out.append(DeviceImage(p.value, (h.value, w.value, b.value)))
+        return out, list(status)
 
     def last_transfer(self):
         """(h2d bytes, d2h bytes, 'host'|'device') of the last decode()."""

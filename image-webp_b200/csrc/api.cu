@@ -579,6 +579,18 @@ extern "C" int webpb200_ctx_set_entropy(webpb200_ctx* c, int where) {
     return 0;
 }
 
+extern "C" int webpb200_batch_output_device(webpb200_ctx* c, int image, void** d_ptr, size_t* len, uint32_t* width, uint32_t* height, int* bpp) {
+    if (!c || !c->uploaded || image < 0 || image >= c->n) return -WEBPB200_ERR_INVALID_PARAM;
+    if (c->items[image].status) return c->items[image].status;
+    const webpb200_frame_desc& fd = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p)[image];
+    if (d_ptr) *d_ptr = c->d_out.p + fd.out_off;
+    if (len) *len = (size_t)fd.width * fd.height * fd.out_bpp;
+    if (width) *width = fd.width;
+    if (height) *height = fd.height;
+    if (bpp) *bpp = fd.out_bpp;
+    return 0;
+}
+
 extern "C" int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int* entropy_where) {
     if (!c) return -WEBPB200_ERR_INVALID_PARAM;
     if (h2d_bytes) *h2d_bytes = c->last_h2d;
@@ -874,9 +886,9 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         for (int i = 0; ok && i < n; i++) {
             const webpb200_frame_desc& f = frames[i];
             ok = !c->items[i].status && f.width == frames[0].width && f.height == frames[0].height && f.out_bpp == 3 &&
-                 out_lens[i] == (size_t)f.width * f.height * 3;
+                 (!outs || out_lens[i] == (size_t)f.width * f.height * 3);
         }
-        if (ok) {
+        if (ok && outs) {
             dpitch = (size_t)(outs[1] - outs[0]);
             spitch = (size_t)(frames[1].out_off - frames[0].out_off);
             ok = outs[1] > outs[0] && dpitch >= out_lens[0];
@@ -946,6 +958,10 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
             if (trace) cudaEventRecord(bev[band_now][3], r);
             const int y0 = q_done == 0 ? 0 : 2 * q_done - 1, y1 = std::min(h, 2 * q_end - 1);
             const size_t off = (size_t)y0 * w * 3, bytes = (size_t)(y1 - y0) * w * 3;
+            if (!outs) {  // the images stay on the device (webpb200_batch_output_device)
+                q_done = q_end;
+                return 0;
+            }
             static const bool linear = std::getenv("WEBPB200_BAND_LINEAR") != nullptr;
             if (linear) {
                 for (int i = 0; i < n; i++)
@@ -964,7 +980,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
         };
         const double t_launch = ms_since();
         cudaEvent_t probe[3];
-        const bool copy_probe = trace && std::getenv("WEBPB200_COPY_PROBE") != nullptr;
+        const bool copy_probe = trace && outs && std::getenv("WEBPB200_COPY_PROBE") != nullptr;
         if (copy_probe) {  // how fast is a D2H copy while k_entropy runs? (linear, then 2-D)
             for (auto& e : probe) cudaEventCreate(&e);
             cudaEventRecord(probe[0], r);
@@ -1058,7 +1074,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
     const double t_kernels = ms_since();
     for (int i = 0; i < n; i++)
         if (!c->items[i].status && dev_status[i]) c->items[i].status = dev_status[i];
-    if ((rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
+    if (outs && (rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
     if ((rc = check_abort(c)) != 0) return rc;
     if (trace) {
@@ -1169,7 +1185,7 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
             bd.total_rows = row1 - row0;
             if (int r = reconstruct(c, bd, 0x7, s, nullptr)) err = r;
         }
-        if (!any_alpha && !err)
+        if (!any_alpha && !err && outs)
             if (int r = download_range(c, outs, out_lens, i0, i1)) err = r;
     }
     for (auto& t : pool) t.join();
@@ -1185,7 +1201,7 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
         int l = 0;
         CU(c, launch_alpha(c->bd, s, &l), "k_alpha");
         c->launches += (uint64_t)l;
-        if ((rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
+        if (outs && (rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
     }
     CU(c, cudaStreamSynchronize(s), "sync");
     if ((rc = check_abort(c)) != 0) return rc;

@@ -165,6 +165,13 @@ void webpb200_host_free(void* p);
 #define WEBPB200_ENTROPY_DEVICE 1
 #define WEBPB200_ENTROPY_AUTO 2
 int webpb200_ctx_set_entropy(webpb200_ctx* c, int where);
+/* No counterpart in the reference (which fills host slices).  webpb200_decode_batch with outs = NULL
+ * (out_lens is then ignored) leaves the decoded images in device memory; this gives the device
+ * address, byte length (tightly packed RGB8 / RGBA8, as read_image would write it) and geometry of
+ * image i.  The memory belongs to the context and is reused by its next batch call.  Returns the
+ * image's status if it failed to decode. */
+int webpb200_batch_output_device(webpb200_ctx* c, int image, void** d_ptr, size_t* len, uint32_t* width,
+                                 uint32_t* height, int* bpp);
 /* What the last webpb200_decode_batch on this context moved over PCIe (bytes each way) and
  * where its entropy stage ran (WEBPB200_ENTROPY_HOST or _DEVICE); for bench accounting. */
 int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int* entropy_where);

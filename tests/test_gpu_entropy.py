@@ -220,3 +220,28 @@ def test_randomised_streams_device_vs_host(W, dev, host, synth):
         if st == 0:
             assert np.array_equal(a, b), i
     _check_packed(W, dev, files, s_dev)
+
+
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_images_left_in_device_memory(W, dev, host, synth, where):
+    """outs = NULL: no download; webpb200_batch_output_device hands out the device copy of each image
+    (wrapped here as torch tensors through __cuda_array_interface__, no copy)."""
+    import torch
+    bd = dev if where == "device" else host
+    uniform = [synth.webp_simple(synth.vp8_frame(256, 256, seed=700 + i, filter_type=0, filter_level=15)) for i in range(80)]  # banded route
+    w, h = 96, 80
+    mixed = [synth.webp_extended(synth.vp8_frame(w, h, seed=20 + k, filter_type=0, filter_level=9), w, h,
+                                 synth.alph_raw(synth.smooth_alpha(w, h, k), filtering=k % 4)) for k in range(4)]
+    mixed += [synth.webp_simple(synth.vp8_frame(200, 120, seed=40)), b"junk"]
+    for files in (uniform, mixed):
+        want, st_want = host.decode(files)
+        got, st = bd.decode_to_device(files)
+        assert st == st_want
+        assert bd.last_transfer()[1] == 0  # nothing was downloaded
+        for g, wnt, s in zip(got, want, st):
+            if s:
+                assert g is None
+                continue
+            t = torch.as_tensor(g, device="cuda")
+            assert tuple(t.shape) == g.shape and t.dtype == torch.uint8
+            assert np.array_equal(t.cpu().numpy().reshape(-1), np.asarray(wnt).reshape(-1))
