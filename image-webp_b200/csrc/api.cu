@@ -962,11 +962,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
                 q_done = q_end;
                 return 0;
             }
-            static const bool linear = std::getenv("WEBPB200_BAND_LINEAR") != nullptr;
-            if (linear) {
-                for (int i = 0; i < n; i++)
-                    CU(c, cudaMemcpyAsync(outs[i] + off, c->d_out.p + frames[i].out_off + off, bytes, cudaMemcpyDeviceToHost, r), "D2H band");
-            } else
+            // one 2-D copy for the band of every frame (a copy per frame is API-bound: 5 us x 1024 per band)
             CU(c, cudaMemcpy2DAsync(outs[0] + off, dpitch, c->d_out.p + frames[0].out_off + off, spitch, bytes, (size_t)n, cudaMemcpyDeviceToHost, r), "D2H band");
             c->last_d2h += bytes * (uint64_t)n;
             q_done = q_end;
