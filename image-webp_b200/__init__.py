@@ -469,12 +469,14 @@ class BatchDecoder:
     def launch_count(self):
         return lib().webpb200_launch_count(self._h)
 
-    def decode_animation(self, data, lossy_upsampling=BILINEAR, host_threads=0):
-        """All composited frames of an animated lossy file: (list of canvases, durations)."""
+    def decode_animation(self, data, lossy_upsampling=BILINEAR, host_threads=0, outs=None):
+        """All composited frames of an animated lossy file: (list of canvases, durations).
+        outs: optional list of num_frames uint8 arrays of output_buffer_size() bytes (e.g. pinned)."""
         buf = _as_u8(data)
         d = WebPDecoder(buf)
         nf = d.num_frames()
-        outs = [d._new_buf() for _ in range(nf)]
+        if outs is None:
+            outs = [d._new_buf() for _ in range(nf)]
         op, _ = self._ptr_arrays(outs)
         dur = (C.c_uint32 * max(nf, 1))()
         rc = lib().webpb200_decode_animation(self._h, buf.ctypes.data, buf.size, op, outs[0].size if outs else 0, dur, nf,

@@ -724,13 +724,13 @@ constexpr int kPreferHostEntropy = 1 << 30;  // internal: the cost model of the 
 // the compressed VP8 chunks; the boolean decode of macroblock headers and tokens runs in k_entropy,
 // one warp per partition, all frames of the batch side by side; then the reconstruction kernels as
 // before.  The 800 bytes per macroblock of levels are produced in HBM and never cross PCIe.
-int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
-                                const size_t* out_lens, int* status, int upsampling, int host_threads) {
+int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& items_in, uint8_t* const* outs, const size_t* out_lens,
+                                int* status, int upsampling, int host_threads) {
     const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
-    std::vector<WorkItem> items;
-    items_from_files(files, lens, n, host_threads, &items);
+    std::vector<WorkItem> items = items_in;  // the caller keeps its list: the cost model may hand the batch to the host path
+    const int n = (int)items.size();
     const double t_items = ms_since();
     cudaStream_t s = c->stream;
     int rc = 0;
@@ -1093,20 +1093,40 @@ int decode_batch_device_entropy(webpb200_ctx* c, const uint8_t* const* files, co
 // decode images in order, and as soon as a chunk is complete its packed arrays go to the device,
 // its kernels run and its pixels come back, all on the context's stream, while the host threads
 // are already decoding the following chunks.  The copies and kernels hide behind the entropy decode.
+namespace {
+int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, uint8_t* const* outs, const size_t* out_lens, int* status,
+                              int upsampling, int host_threads);
+
+// One batch of reconstruction work items (still images, or the frames of an animation) through
+// whichever placement of the entropy stage the context asks for.  outs may be null (images stay on
+// the device).  Returns the number of failed items, or a negative status.
+int decode_items(webpb200_ctx* c, std::vector<WorkItem>&& items, uint8_t* const* outs, const size_t* out_lens, int* status, int upsampling,
+                 int host_threads) {
+    cudaSetDevice(c->device);
+    c->last_d2h = 0;
+    if (c->entropy_where != WEBPB200_ENTROPY_HOST) {
+        const int r = decode_batch_device_entropy(c, items, outs, out_lens, status, upsampling, host_threads);
+        if (r != kPreferHostEntropy) return r;
+    }
+    return decode_items_host_entropy(c, std::move(items), outs, out_lens, status, upsampling, host_threads);
+}
+}  // namespace
+
 extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
                                      const size_t* out_lens, int* status, int upsampling, int host_threads) {
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
     if (n < 0) return -WEBPB200_ERR_INVALID_PARAM;
-    cudaSetDevice(c->device);
-    c->last_d2h = 0;
-    if (c->entropy_where != WEBPB200_ENTROPY_HOST) {
-        const int r = decode_batch_device_entropy(c, files, lens, n, outs, out_lens, status, upsampling, host_threads);
-        if (r != kPreferHostEntropy) return r;
-    }
-    const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
-    const auto t0 = std::chrono::steady_clock::now();
     std::vector<WorkItem> items;
     items_from_files(files, lens, n, host_threads, &items);
+    return decode_items(c, std::move(items), outs, out_lens, status, upsampling, host_threads);
+}
+
+namespace {
+int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, uint8_t* const* outs, const size_t* out_lens, int* status,
+                              int upsampling, int host_threads) {
+    const bool trace = std::getenv("WEBPB200_TRACE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    const int n = (int)items.size();
     int rc = layout_items(c, std::move(items), upsampling, host_threads);
     if (rc) return rc;
     if ((rc = reserve_device(c)) != 0) return rc;
@@ -1210,6 +1230,8 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     }
     return bad;
 }
+
+}  // namespace
 
 // ------------------------------------------------------------------------------------------------
 // host half alone (no CUDA calls): container walk + entropy decode into caller arrays
@@ -1567,13 +1589,13 @@ extern "C" int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, s
         }
         pos = frs[f].next;
     }
-    // all frames reconstruct as one batch (every VP8 frame is a keyframe, lossy/mod.rs:513-518) ...
-    int rc = prepare_items(c, std::move(items), upsampling, host_threads);
-    if (rc) return rc;
+    // all frames reconstruct as one batch (every VP8 frame is a keyframe, lossy/mod.rs:513-518), through
+    // the same pipelined path as still images with the pictures left on the device ...
+    std::vector<int> fstatus((size_t)std::max(nf, 1), 0);
+    int rc = decode_items(c, std::move(items), nullptr, nullptr, fstatus.data(), upsampling, host_threads);
+    if (rc < 0) return rc;
     for (int f = 0; f < nf; f++)
-        if (c->items[f].status) return -c->items[f].status;
-    if ((rc = upload(c)) != 0) return rc;
-    if ((rc = reconstruct(c, c->bd, 0xF, c->stream, nullptr)) != 0) return rc;
+        if (fstatus[f]) return -fstatus[f];
     // ... compositing is sequential over frames (decoder.rs:861-919)
     const size_t cbytes = (size_t)ct.width * ct.height * 4;
     CU(c, c->d_canvas.reserve(cbytes), "canvas");

@@ -59,6 +59,23 @@ def main():
     if "cfg4" in which:
         run_still("cfg4: 64 x 1920x1080 VP8X + raw ALPH (filter 0..3 cycling), normal filter, RGBA",
                   S.make_batch(S.cfg4_image, 64, threads=CORES), 4)
+    if "cfg4c" in which:
+        # cfg4 as SURVEY 8(d) words it: the ALPH chunk VP8L-compressed by libwebp (PIL), spliced next to a synthetic VP8 chunk
+        import io
+        from PIL import Image
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+        from util import chunk_payload
+        files = []
+        for i in range(64):
+            a = S.smooth_alpha(1920, 1080, i)
+            rgba = np.zeros((1080, 1920, 4), np.uint8)
+            rgba[..., 3] = a
+            buf = io.BytesIO()
+            Image.fromarray(rgba, "RGBA").save(buf, "WEBP", quality=50, method=0)
+            alph = chunk_payload(buf.getvalue(), b"ALPH")
+            vp8 = S.vp8_frame(1920, 1080, seed=0xB200 + i, filter_type=0, filter_level=20, yac_abs=36, prob_skip=200, p_skip=0.05)
+            files.append(S.webp_extended(vp8, 1920, 1080, S.chunk(b"ALPH", alph)))
+        run_still("cfg4c: 64 x 1920x1080 VP8X + VP8L-compressed ALPH (libwebp), normal filter, RGBA", files, 4)
     if "cfg5" in which:
         frames = []
         for k in range(120):
@@ -67,10 +84,13 @@ def main():
                                alph=S.alph_raw(S.smooth_alpha(1920, 1080, k), filtering=k % 4)))
         data = S.webp_animation(1920, 1080, frames, alpha=True)
         bd = W.BatchDecoder(0)
-        bd.decode_animation(data, host_threads=CORES)
+        pin = W.PinnedBuffer(120 * 1920 * 1080 * 4)
+        pouts = [pin.array[k * 1920 * 1080 * 4:(k + 1) * 1920 * 1080 * 4] for k in range(120)]
+        bd.decode_animation(data, host_threads=CORES, outs=pouts)
         t = time.perf_counter()
-        outs, durs = bd.decode_animation(data, host_threads=CORES)
+        outs, durs = bd.decode_animation(data, host_threads=CORES, outs=pouts)
         e2e = time.perf_counter() - t
+        outs = [o.reshape(1080, 1920, 4) for o in outs]
         t = time.perf_counter()
         o = O.WebPDecoder(data)
         ok = True
