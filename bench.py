@@ -213,6 +213,7 @@ def main():
     e2e_ms = 1e3 * (time.perf_counter() - t0) / e2e_steps
     assert all(s == 0 for s in st)
     h2d_bytes, d2h_bytes, entropy_where = bd.last_transfer()
+    entropy_ms = bd.last_entropy_ms()
     # for information: the same call with the images left in device memory (no download), as a GPU consumer would use it
     bd.decode_to_device(file_list, host_threads=host_threads)
     t1 = time.perf_counter()
@@ -245,7 +246,7 @@ def main():
                          "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass"},
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
-                    "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum,
+                    "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum,
                     "numa_bound_cpus": len(near) if near else None,
                     "images_left_on_device": {"ms_per_step": dev_out_ms, "value": px / (dev_out_ms / 1e3) / 1e6, "note": "rank 0, outs = NULL: no D2H"}},
             "gpu_launches": int(launches),

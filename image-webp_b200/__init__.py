@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
-    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device",
+    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms",
 ]
 
 
@@ -141,6 +141,7 @@ def lib():
     L.webpb200_batch_size.argtypes = [vp, pi] + [C.POINTER(C.c_uint64)] * 4
     L.webpb200_batch_get_planes.argtypes = [vp, i32, vp, vp, vp]
     L.webpb200_batch_output_device.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(u32), C.POINTER(u32), C.POINTER(i32)]
+    L.webpb200_last_entropy_ms.argtypes = [vp]; L.webpb200_last_entropy_ms.restype = C.c_float
     L.webpb200_device_pci_bus_id.argtypes = [i32, C.c_char_p, i32]
     L.webpb200_last_transfer.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(i32)]
     L.webpb200_ctx_set_entropy.argtypes = [vp, i32]
@@ -457,6 +458,10 @@ class BatchDecoder:
         a, b, w = C.c_uint64(), C.c_uint64(), C.c_int()
         self._check(lib().webpb200_last_transfer(self._h, C.byref(a), C.byref(b), C.byref(w)))
         return a.value, b.value, "device" if w.value == 1 else "host"
+
+    def last_entropy_ms(self):
+        """Device milliseconds of k_entropy in the last decode() (0.0 when the host did the entropy stage)."""
+        return float(lib().webpb200_last_entropy_ms(self._h))
 
     def device_packed(self, image, frame_desc):
         """Macroblock descriptors and levels of one image as the device holds them (after decode/upload)."""

@@ -123,6 +123,7 @@ struct webpb200_ctx {
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
     uint64_t last_h2d = 0, last_d2h = 0;  // bytes the last decode_batch copied each way
     int last_entropy = WEBPB200_ENTROPY_HOST;  // where its entropy stage ran
+    float last_entropy_ms = 0;  // device time of k_entropy in the last decode_batch (0 if it ran on the host)
     int entropy_where = WEBPB200_ENTROPY_AUTO;  // WEBPB200_ENTROPY_*: where decode_batch runs the boolean decode
     DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status;
 
@@ -599,6 +600,8 @@ extern "C" int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes
     return 0;
 }
 
+extern "C" float webpb200_last_entropy_ms(const webpb200_ctx* c) { return c ? c->last_entropy_ms : 0.f; }
+
 extern "C" int webpb200_batch_download_packed(webpb200_ctx* c, int image, webpb200_mb_desc* mbs, int16_t* levels) {
     if (!c || !c->uploaded || image < 0 || image >= c->n) return -WEBPB200_ERR_INVALID_PARAM;
     cudaSetDevice(c->device);
@@ -922,14 +925,14 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     // ran 9.5 % longer (42.9 vs 39.2 ms, bimodal); the wait itself costs nothing that is not needed anyway.
     CU(c, cudaStreamSynchronize(s), "sync before k_entropy");
     CU(c, cudaEventRecord(c->ev[7], s), "event");  // every input of the reconstruction kernels is on the device
-    if (trace) cudaEventRecord(c->ev[5], s);
+    cudaEventRecord(c->ev[5], s);
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
                              reinterpret_cast<int*>(c->d_status.p), max_parts, nbands ? c->d_rows : nullptr, s), "k_entropy");
         c->launches++;
     }
-    if (trace) cudaEventRecord(c->ev[6], s);
+    cudaEventRecord(c->ev[6], s);
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
@@ -1024,6 +1027,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         const double t_lastband = ms_since();
         CU(c, cudaStreamSynchronize(s), "sync");
         CU(c, cudaStreamSynchronize(r), "sync");
+        cudaEventElapsedTime(&c->last_entropy_ms, c->ev[5], c->ev[6]);
         for (int i = 0; i < n; i++)
             if (dev_status[i]) c->items[i].status = dev_status[i];  // those pixels are not valid
         if ((rc = check_abort(c)) != 0) return rc;
@@ -1072,6 +1076,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         if (!c->items[i].status && dev_status[i]) c->items[i].status = dev_status[i];
     if (outs && (rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
+    cudaEventElapsedTime(&c->last_entropy_ms, c->ev[5], c->ev[6]);
     if ((rc = check_abort(c)) != 0) return rc;
     if (trace) {
         float ems = 0;
@@ -1133,6 +1138,7 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
     webpb200_frame_desc* frames = reinterpret_cast<webpb200_frame_desc*>(c->h_frames.p);
     cudaStream_t s = c->stream;
     c->last_entropy = WEBPB200_ENTROPY_HOST;
+    c->last_entropy_ms = 0;
     c->last_d2h = 0;
     c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + c->total_mbs * (sizeof(webpb200_mb_desc) + 2 * WEBPB200_LEVELS_PER_MB) + c->alpha_bytes + c->aux_bytes;
 

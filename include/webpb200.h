@@ -175,6 +175,8 @@ int webpb200_batch_output_device(webpb200_ctx* c, int image, void** d_ptr, size_
 /* What the last webpb200_decode_batch on this context moved over PCIe (bytes each way) and
  * where its entropy stage ran (WEBPB200_ENTROPY_HOST or _DEVICE); for bench accounting. */
 int webpb200_last_transfer(const webpb200_ctx* c, uint64_t* h2d_bytes, uint64_t* d2h_bytes, int* entropy_where);
+/* Device time (CUDA events, ms) of the entropy kernel in the last webpb200_decode_batch; 0 if it ran on the host. */
+float webpb200_last_entropy_ms(const webpb200_ctx* c);
 /* After a decode_batch / batch_upload: copies one image's macroblock descriptors and levels as
  * the device holds them (mbw*mbh descriptors, mbw*mbh*400 levels) -- for parity tests of the
  * device entropy stage against webpb200_host_entropy_decode. */
