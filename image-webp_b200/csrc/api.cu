@@ -545,6 +545,7 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
     for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status}) b->release();
     for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status})
         b->release();
@@ -734,6 +735,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     std::vector<WorkItem> items = items_in;  // the caller keeps its list: the cost model may hand the batch to the host path
     const int n = (int)items.size();
+    if (c->stream2) cudaStreamSynchronize(c->stream2);  // nothing of an earlier call that ended early may still be in flight
     const double t_items = ms_since();
     cudaStream_t s = c->stream;
     int rc = 0;
