@@ -1209,7 +1209,35 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
             bd.total_rows = row1 - row0;
             if (int r = reconstruct(c, bd, 0x7, s, nullptr)) err = r;
         }
-        if (!any_alpha && !err && outs)
+        if (any_alpha && !err) {
+            // ALPH planes of this chunk: their filter methods are known now (entropy_one read the chunk
+            // headers), so the un-filter + merge runs per chunk too and nothing is left for the end.
+            // The chunk's index lists live at [4 * i0, 4 * i1) of the list area, method-major.
+            const int nc = i1 - i0;
+            int* lists = reinterpret_cast<int*>(c->h_aux.p + c->aux_lists_off) + (size_t)4 * i0;
+            BatchDev bd = c->bd;
+            bd.n_frames = nc;
+            for (int m = 0; m < 4; m++) bd.alpha_counts[m] = 0, bd.alpha_maxw[m] = 0, bd.alpha_maxh[m] = 0;
+            for (int i = i0; i < i1; i++) {
+                const webpb200_frame_desc& fd = frames[i];
+                if (!fd.alpha_mode || fd.out_bpp != 4) continue;
+                const int m = fd.alpha_filter & 3;
+                lists[m * nc + bd.alpha_counts[m]++] = i;
+                bd.alpha_maxw[m] = std::max<uint32_t>(bd.alpha_maxw[m], fd.width);
+                bd.alpha_maxh[m] = std::max<uint32_t>(bd.alpha_maxh[m], fd.height);
+            }
+            if (bd.alpha_counts[0] + bd.alpha_counts[1] + bd.alpha_counts[2] + bd.alpha_counts[3]) {
+                const uint64_t a0 = frames[i0].alpha_off, a1 = i1 < n ? frames[i1].alpha_off : c->alpha_bytes;
+                if (a1 > a0) fail(cudaMemcpyAsync(c->d_alpha.p + a0, c->h_alpha.p + a0, (size_t)(a1 - a0), cudaMemcpyHostToDevice, s), "H2D alpha");
+                const size_t lo = c->aux_lists_off + sizeof(int) * 4 * (size_t)i0;
+                fail(cudaMemcpyAsync(c->d_aux.p + lo, c->h_aux.p + lo, sizeof(int) * 4 * (size_t)nc, cudaMemcpyHostToDevice, s), "H2D lists");
+                bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + lo);
+                int l = 0;
+                if (!err) fail(launch_alpha(bd, s, &l), "k_alpha");
+                c->launches += (uint64_t)l;
+            }
+        }
+        if (!err && outs)
             if (int r = download_range(c, outs, out_lens, i0, i1)) err = r;
     }
     for (auto& t : pool) t.join();
@@ -1217,18 +1245,12 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
         cudaStreamSynchronize(s);
         return err;
     }
-    if (any_alpha) {  // the ALPH filter methods are known now: merge alpha for the whole batch, then fetch
-        finish_items(c);
-        CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
-        CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
-        CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
-        int l = 0;
-        CU(c, launch_alpha(c->bd, s, &l), "k_alpha");
-        c->launches += (uint64_t)l;
-        if (outs && (rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
-    }
     CU(c, cudaStreamSynchronize(s), "sync");
     if ((rc = check_abort(c)) != 0) return rc;
+    if (any_alpha) {  // whole-batch lists, for the staged API that may follow (batch_reconstruct)
+        finish_items(c);
+        CU(c, cudaMemcpy(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice), "H2D lists");
+    }
     if (trace) std::fprintf(stderr, "[webpb200] decode_batch n=%d in %d chunks: %.1f ms\n", n, nchunks,
                             std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     int bad = 0;
