@@ -80,18 +80,23 @@ struct DevBool {
         base = data; len = n; pos = s.pos; value = s.value; range = s.range; bits = s.bits;
         phantom = s.phantom != 0; eof = s.eof != 0;
     }
+    // Fast path straight-line: three bytes are always fetched (the bitstream arena is padded, so
+    // reading past the end of a partition is safe) and the rare overshoot at the end of a partition
+    // is undone and replayed byte by byte with the end-of-data rules (arithmetic_decoder.rs:249-276).
     __device__ __forceinline__ void refill() {
-        const uint32_t left = len - pos;
-        if (left >= 3) {
-            const uint32_t b0 = __ldg(base + pos), b1 = __ldg(base + pos + 1), b2 = __ldg(base + pos + 2);
-            value = (value << 24) | (b0 << 16) | (b1 << 8) | b2;
-            pos += 3;
-            bits += 24;
-        } else if (left > 0) {
-            value = (value << 8) | __ldg(base + pos);
-            pos += 1;
-            bits += 8;
-        } else if (!phantom && !eof) {
+        const uint32_t b0 = __ldg(base + pos), b1 = __ldg(base + pos + 1), b2 = __ldg(base + pos + 2);
+        value = (value << 24) | (b0 << 16) | (b1 << 8) | b2;
+        pos += 3;
+        bits += 24;
+        if (pos > len) refill_tail();
+    }
+    __device__ __forceinline__ void refill_tail() {
+        const uint32_t over = pos - len;  // 1..3 bytes that do not exist
+        value >>= 8 * over;
+        bits -= 8 * (int)over;
+        pos = len;
+        if (bits >= 0) return;  // the real bytes were enough
+        if (!phantom && !eof) {
             phantom = true;
             value <<= 8;
             bits += 8;
