@@ -10,6 +10,8 @@
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
 #include <memory>
 #include <map>
 #include <mutex>
@@ -27,6 +29,63 @@ using namespace webpb200;
 
 namespace {
 
+// A small pool of parked worker threads: a decode_batch call runs three or four short parallel
+// loops (container walk, probe, header parse), and creating 15 threads for each costs more than
+// the loops themselves.  One user at a time; a second concurrent caller falls back to plain threads.
+class WorkerPool {
+public:
+    static WorkerPool& get() {
+        static WorkerPool* p = new WorkerPool();  // leaked on purpose: workers may outlive static destruction
+        return *p;
+    }
+    // runs job() on `extra` pool threads and on the caller; returns false if the pool is in use
+    bool run(int extra, const std::function<void()>& job) {
+        if (busy_.exchange(true)) return false;
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            while ((int)threads_.size() < extra) threads_.emplace_back([this, id = (int)threads_.size()] { loop(id); });
+            job_ = &job;
+            want_ = extra;
+            pending_ = extra;
+            ++gen_;
+        }
+        cv_.notify_all();
+        job();
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            done_.wait(lk, [this] { return pending_ == 0; });
+            job_ = nullptr;
+        }
+        busy_.store(false);
+        return true;
+    }
+
+private:
+    void loop(int id) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void()>* job = nullptr;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (id < want_) job = job_;
+            }
+            if (!job) continue;
+            (*job)();
+            std::unique_lock<std::mutex> lk(mu_);
+            if (--pending_ == 0) done_.notify_one();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    std::vector<std::thread> threads_;
+    const std::function<void()>* job_ = nullptr;
+    uint64_t gen_ = 0;
+    int want_ = 0, pending_ = 0;
+    std::atomic<bool> busy_{false};
+};
+
 template <class F>
 void parallel_for(int n, int threads, F fn) {
     if (threads < 1) threads = 1;
@@ -43,6 +102,7 @@ void parallel_for(int n, int threads, F fn) {
             fn(i);
         }
     };
+    if (threads - 1 <= 63 && WorkerPool::get().run(threads - 1, work)) return;
     std::vector<std::thread> pool;
     for (int t = 1; t < threads; t++) pool.emplace_back(work);
     work();
@@ -823,7 +883,11 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
             }
         };
         std::vector<std::thread> pool;
-        for (int t = 0; t < std::max(1, std::min(host_threads, n)); t++) pool.emplace_back(worker);
+        if (direct_base) {  // nothing to upload behind the workers: this thread works too (parked pool threads, no thread creation)
+            parallel_for(std::max(1, std::min(host_threads, n)), host_threads, [&](int) { worker(); });
+        } else {
+            for (int t = 0; t < std::max(1, std::min(host_threads, n)); t++) pool.emplace_back(worker);
+        }
         cudaError_t e = cudaSuccess;
         for (int k = 0; k < nslices; k++) {
             while (left[k].load(std::memory_order_acquire) > 0) std::this_thread::yield();
