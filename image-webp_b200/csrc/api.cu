@@ -903,7 +903,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     for (int i = 0; i < n; i++) max_parts = std::max<int>(max_parts, hdrs[i].num_parts);
     if (c->entropy_where == WEBPB200_ENTROPY_AUTO) {
         // The device decodes every partition of every frame at once but each one slowly (one lane,
-        // about 38 us per macroblock on B200); the host decodes fast (about 3 us per macroblock)
+        // about 33 us per macroblock on B200); the host decodes fast (about 3 us per macroblock)
         // but only one frame per thread.  Many small frames: device.  A few large ones: host.
         double longest = 0, streams = 0;
         for (int i = 0; i < n; i++)
@@ -911,7 +911,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
                 longest = std::max(longest, (double)frames[i].mbw * frames[i].mbh / hdrs[i].num_parts);
                 streams += hdrs[i].num_parts;
             }
-        const double est_device_us = longest * 38.0 * std::max(1.0, streams / 1184.0);
+        const double est_device_us = longest * 33.0 * std::max(1.0, streams / 1184.0);
         const double est_host_us = (double)c->total_mbs * 3.0 / std::max(1, std::min(host_threads, n));
         if (est_device_us > est_host_us) return kPreferHostEntropy;
     }
