@@ -245,3 +245,37 @@ def test_images_left_in_device_memory(W, dev, host, synth, where):
             t = torch.as_tensor(g, device="cuda")
             assert tuple(t.shape) == g.shape and t.dtype == torch.uint8
             assert np.array_equal(t.cpu().numpy().reshape(-1), np.asarray(wnt).reshape(-1))
+
+
+def test_uniform_size_random_parameters_and_ragged_count(W, dev, host, synth):
+    """131 frames of one size (so the band pipeline and, for single-partition batches, the
+    four-frames-per-block entropy layout are taken; 131 is not a multiple of 4) with per-frame random
+    filter type / level / sharpness / segments / skip, two of them damaged and one not a WebP at all;
+    then the same with random partition counts (one frame per block)."""
+    rng = np.random.default_rng(77)
+    w, h, n = 208, 176, 131
+    for parts in (False, True):
+        files = []
+        for i in range(n):
+            kw = dict(filter_type=int(rng.integers(0, 2)), filter_level=int(rng.integers(0, 64)), sharpness=int(rng.integers(0, 8)),
+                      yac_abs=int(rng.integers(4, 100)), log2_parts=int(rng.integers(0, 4)) if parts else 0)
+            if rng.integers(0, 2):
+                kw.update(segments=1, seg_quant=tuple(int(v) for v in rng.integers(5, 90, 4)), seg_lf=tuple(int(v) for v in rng.integers(0, 60, 4)),
+                          seg_probs=tuple(int(v) for v in rng.integers(1, 255, 3)))
+            if rng.integers(0, 2):
+                kw.update(prob_skip=int(rng.integers(1, 255)), p_skip=float(rng.choice([0.1, 0.6])))
+            files.append(synth.webp_simple(synth.vp8_frame(w, h, seed=9000 + i, **kw)))
+        files[5] = files[5][:len(files[5]) // 2]
+        files[129] = files[129][:len(files[129]) - 3]
+        files[64] = b"RIFF\\x10\\x00\\x00\\x00WEBPjunkjunkjunk"
+        per = w * h * 3
+        _, o_dev = _contiguous_outs(n, per)
+        _, o_host = _contiguous_outs(n, per)
+        _, s_dev = dev.decode(files, outs=o_dev)
+        _, s_host = host.decode(files, outs=o_host)
+        assert s_dev == s_host and s_dev[5] != 0 and s_dev[64] != 0
+        for i in range(n):
+            if s_dev[i] == 0:
+                assert np.array_equal(o_dev[i], o_host[i]), (parts, i)
+        good = [i for i in range(n) if s_dev[i] == 0]
+        _check_packed(W, dev, [files[i] for i in good[:3]], [0, 0, 0]) if good[:3] == [0, 1, 2] else None
