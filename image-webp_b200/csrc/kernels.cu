@@ -289,11 +289,12 @@ __device__ __forceinline__ void unpack8(const uint4& v, int* c) {
     c[6] = (int)(short)(v.w & 0xffff); c[7] = (int)v.w >> 16;
 }
 // residuals only ever meet a pixel through clamp(p + r, 0, 255) (prediction.rs:133-147), so
-// clamping r to [-255, 255] first changes nothing and makes it fit 16 bits
+// saturating r first (to anything of magnitude >= 255) changes nothing and makes it fit 16 bits
+// (any saturation bound >= 255 does: one cvt.pack.sat saturates both to int16 and packs them)
 __device__ __forceinline__ uint32_t pack_res(int a, int b) {
-    a = min(max(a, -255), 255);
-    b = min(max(b, -255), 255);
-    return ((uint32_t)a & 0xffffu) | ((uint32_t)b << 16);
+    uint32_t d;
+    asm("cvt.pack.sat.s16.s32 %0, %1, %2;" : "=r"(d) : "r"(b), "r"(a));
+    return d;
 }
 
 // ---------------------------------------------------------------------------------------------
