@@ -47,6 +47,13 @@ constexpr unsigned kFull = 0xffffffffu;
 // small helpers
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ int clamp255(int v) { return min(max(v, 0), 255); }
+// four values clamped to 0..255 and packed, a lowest: two saturating cvt.pack instead of eight min/max and the shifts
+__device__ __forceinline__ uint32_t clamp_pack4(int a, int b, int c, int d) {
+    uint32_t hi, r;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(d), "r"(c), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(b), "r"(a), "r"(hi));
+    return r;
+}
 
 __device__ __forceinline__ uint32_t ld_cg_u32(const void* p) { return __ldcg(reinterpret_cast<const unsigned int*>(p)); }
 __device__ __forceinline__ uint2 ld_cg_u64(const void* p) { return __ldcg(reinterpret_cast<const uint2*>(p)); }
@@ -554,12 +561,8 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 const uint2 r1 = *reinterpret_cast<const uint2*>(S.res + (blk + 1) * 16 + (row & 3) * 4);
                 const int rr[8] = {(int)(short)(r0.x & 0xffff), (int)r0.x >> 16, (int)(short)(r0.y & 0xffff), (int)r0.y >> 16,
                                    (int)(short)(r1.x & 0xffff), (int)r1.x >> 16, (int)(short)(r1.y & 0xffff), (int)r1.y >> 16};
-                uint32_t o0 = 0, o1 = 0;
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    o0 |= (uint32_t)clamp255(pr[i] + rr[i]) << (8 * i);
-                    o1 |= (uint32_t)clamp255(pr[4 + i] + rr[4 + i]) << (8 * i);
-                }
+                const uint32_t o0 = clamp_pack4(pr[0] + rr[0], pr[1] + rr[1], pr[2] + rr[2], pr[3] + rr[3]);
+                const uint32_t o1 = clamp_pack4(pr[4] + rr[4], pr[5] + rr[5], pr[6] + rr[6], pr[7] + rr[7]);
                 yw32[(1 + row) * 8 + 1 + (x0 >> 2)] = o0;
                 yw32[(1 + row) * 8 + 2 + (x0 >> 2)] = o1;
                 __syncwarp();
@@ -602,9 +605,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 const int blk = 16 + plane * 4 + (row >> 2) * 2 + (x0 >> 2);
                 const uint2 r = *reinterpret_cast<const uint2*>(S.res + blk * 16 + (row & 3) * 4);
                 const int rr[4] = {(int)(short)(r.x & 0xffff), (int)r.x >> 16, (int)(short)(r.y & 0xffff), (int)r.y >> 16};
-                uint32_t o = 0;
-#pragma unroll
-                for (int i = 0; i < 4; i++) o |= (uint32_t)clamp255(pr[i] + rr[i]) << (8 * i);
+                const uint32_t o = clamp_pack4(pr[0] + rr[0], pr[1] + rr[1], pr[2] + rr[2], pr[3] + rr[3]);
                 cw32[(1 + row) * 4 + 1 + (x0 >> 2)] = o;
                 *reinterpret_cast<uint32_t*>(cout + (size_t)mbx * 8) = o;
             }
