@@ -872,10 +872,14 @@ __device__ __forceinline__ int mulhi8(int v, int coeff) { return (v * coeff) >> 
 __device__ __forceinline__ int clip6(int v) { return min(max(v >> 6, 0), 255); }
 __device__ __forceinline__ uint32_t yuv_to_rgb(int y, int u, int v) {  // r | g << 8 | b << 16
     const int yy = mulhi8(y, 19077);
-    const int r = clip6(yy + mulhi8(v, 26149) - 14234);
-    const int g = clip6(yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708);
-    const int b = clip6(yy + mulhi8(u, 33050) - 17685);
-    return (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16);
+    const int r = (yy + mulhi8(v, 26149) - 14234) >> 6;
+    const int g = (yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708) >> 6;
+    const int b = (yy + mulhi8(u, 33050) - 17685) >> 6;
+    // clip(x) = clamp(x >> 6, 0, 255) (yuv.rs:66-71): the clamps and the packing are two saturating cvt.pack
+    uint32_t hi, px;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(0), "r"(b), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(px) : "r"(g), "r"(r), "r"(hi));
+    return px;
 }
 
 struct RgbArgs {
