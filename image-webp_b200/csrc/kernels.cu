@@ -622,9 +622,18 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
 // k_loopfilter
 // ---------------------------------------------------------------------------------------------
 // loop_filter.rs:4-23
-__device__ __forceinline__ int lf_c(int v) { return min(max(v, -128), 127); }
+// (the clamps as single saturating conversions: c(v) = sat_s8(v), s2u(v) = c(v) + 128 = sat_u8(v + 128))
+__device__ __forceinline__ int lf_c(int v) {
+    int r;
+    asm("cvt.sat.s8.s32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
 __device__ __forceinline__ int u2s(int v) { return v - 128; }
-__device__ __forceinline__ int s2u(int v) { return lf_c(v) + 128; }
+__device__ __forceinline__ int s2u(int v) {
+    int r;
+    asm("cvt.sat.u8.s32 %0, %1;" : "=r"(r) : "r"(v + 128));
+    return r;
+}
 
 // One 8-pixel line across an edge; q0 is at p[0], neighbours at multiples of `st` bytes.
 // kind 0: simple_segment (loop_filter.rs:144-162), 1: subblock_filter (167-206),
