@@ -938,9 +938,9 @@ __device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int
 #pragma unroll
         for (int j = 0; j < 2; j++) {
             const uint32_t a = px[4 * j], b = px[4 * j + 1], c = px[4 * j + 2], d = px[4 * j + 3];
-            wv[3 * j] = a | (b << 24);
-            wv[3 * j + 1] = (b >> 8) | (c << 16);
-            wv[3 * j + 2] = (c >> 16) | (d << 8);
+            wv[3 * j] = __byte_perm(a, b, 0x4210);      // a0 a1 a2 b0
+            wv[3 * j + 1] = __byte_perm(b, c, 0x5421);  // b1 b2 c0 c1
+            wv[3 * j + 2] = __byte_perm(c, d, 0x6542);  // c2 d0 d1 d2
         }
         if ((reinterpret_cast<uintptr_t>(out) & 7) == 0) {
             uint2* o = reinterpret_cast<uint2*>(out);
