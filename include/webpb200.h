@@ -182,11 +182,15 @@ float webpb200_last_entropy_ms(const webpb200_ctx* c);
  * device entropy stage against webpb200_host_entropy_decode. */
 int webpb200_batch_download_packed(webpb200_ctx* c, int image, webpb200_mb_desc* mbs, int16_t* levels);
 
-/* N x (WebPDecoder::new + read_image) for still lossy files: host parse and entropy decode
- * on `host_threads` threads, upload, reconstruct, download into outs[i] (out_lens[i] must be
- * width*height*(3|4)).  status[i] gets each file's own code; a bad file does not poison the
- * batch.  Returns the number of failed files, or a negative WEBPB200_ERR_* for a batch-level
- * failure (no device, CUDA error). */
+/* N x (WebPDecoder::new + read_image) for still lossy files: container and frame-header parse on
+ * `host_threads` threads, entropy decode on the device or on those threads (see
+ * webpb200_ctx_set_entropy), reconstruction kernels, download into outs[i] (out_lens[i] must be
+ * width*height*(3|4)); outs = NULL leaves the images on the device (webpb200_batch_output_device).
+ * status[i] gets each file's own code; a bad file does not poison the batch, and outs[i] of a
+ * failed file holds no valid image.  Returns the number of failed files, or a negative
+ * WEBPB200_ERR_* for a batch-level failure (no device, CUDA error).  The stages overlap most when
+ * the files lie in one block from webpb200_host_alloc and the outs of same-size images are evenly
+ * spaced; neither is required. */
 int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n,
                           uint8_t* const* outs, const size_t* out_lens, int* status,
                           int upsampling, int host_threads);
