@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
-    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms",
+    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
 ]
 
 
@@ -187,6 +187,24 @@ def host_entropy_decode(data):
     if st:
         raise DecodingError(st)
     return fd, mbs, levels, alpha
+
+
+def entropy_decode_resumed(data):
+    """host_entropy_decode through the device stage's hand-over structure (host only): (FrameDesc, mbs, levels)."""
+    buf = _as_u8(data)
+    fd = FrameDesc()
+    st = lib().webpb200_host_entropy_decode(buf.ctypes.data, buf.size, C.byref(fd), None, 0, None, 0, None, 0)
+    if st:
+        raise DecodingError(st)
+    m = fd.mbw * fd.mbh
+    mbs = np.zeros(m, dtype=MB_DTYPE)
+    levels = np.zeros((m, 25, 16), dtype=np.int16)
+    L = lib()
+    L.webpb200_debug_entropy_resumed.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    st = L.webpb200_debug_entropy_resumed(buf.ctypes.data, buf.size, C.byref(fd), mbs.ctypes.data, m, levels.ctypes.data, levels.size)
+    if st:
+        raise DecodingError(st)
+    return fd, mbs, levels
 
 
 class WebPDecoder:

@@ -1366,6 +1366,24 @@ extern "C" int webpb200_host_entropy_decode(const uint8_t* file, size_t len, web
     return 0;
 }
 
+// The same through the hand-over structure of the device entropy stage (host_vp8.h), no ALPH part.
+extern "C" int webpb200_debug_entropy_resumed(const uint8_t* file, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs, size_t mbs_cap,
+                                              int16_t* levels, size_t levels_cap) {
+    std::vector<WorkItem> items;
+    const uint8_t* files[1] = {file};
+    const size_t lens[1] = {len};
+    items_from_files(files, lens, 1, 1, &items);
+    WorkItem& it = items[0];
+    if (it.status) return it.status;
+    int st = vp8_probe(it.vp8, it.vp8_len, &it.dims);
+    if (st) return st;
+    if (it.dims.width != it.check_w || it.dims.height != it.check_h) return WEBPB200_ERR_INCONSISTENT_SIZE;
+    std::memset(fd, 0, sizeof(*fd));
+    const size_t m = (size_t)it.dims.mbw * it.dims.mbh;
+    if (mbs_cap < m || levels_cap < m * WEBPB200_LEVELS_PER_MB) return WEBPB200_ERR_INVALID_PARAM;
+    return vp8_entropy_decode_resumed(it.vp8, it.vp8_len, fd, mbs, levels);
+}
+
 extern "C" void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8_t* out16) { bpred_table_eval(mode, edge13, out16); }
 
 // ------------------------------------------------------------------------------------------------

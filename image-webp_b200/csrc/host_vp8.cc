@@ -166,6 +166,17 @@ struct ByteBoolReader {
         int m = literal(n);
         return flag() ? -m : m;
     }
+    int tree(const int8_t* t, const uint8_t* probs) {
+        int i = 0;
+        do {
+            i = t[i + get(probs[i >> 1])];
+        } while (i > 0);
+        return -i;
+    }
+    void resume(const uint8_t* data, size_t n, const BoolState& s) {  // what the device reader does with the header's state
+        base = data; len = (uint32_t)n; pos = s.pos; value = s.value; range = s.range; bits = s.bits;
+        phantom = s.phantom != 0; eof = s.eof != 0;
+    }
 };
 
 const int8_t kSegmentTree[6] = {2, 4, -0, -1, -2, -3};
@@ -185,7 +196,8 @@ typedef uint8_t TokenProbs[8][3][11];  // [band][ctx][node] of one plane
 
 // Tokens of one 4x4 block.  Same token tree as the reference (common.rs:659-662) written
 // out as nested branches.  Returns "has coefficients" (mod.rs:809, 823-828, 868).
-inline int read_block(BoolReader& br, const TokenProbs& probs, int ctx, int first, int16_t* out) {
+template <class Reader>
+inline int read_block(Reader& br, const TokenProbs& probs, int ctx, int first, int16_t* out) {
     int n = first;
     const uint8_t* p = probs[kCoeffBands[n]][ctx];
     if (!br.get(p[0])) return 0;  // DCT_EOB straight away
@@ -410,18 +422,14 @@ int vp8_parse_header(const uint8_t* d, size_t len, webpb200_frame_desc* fd, Vp8E
     return WEBPB200_OK;
 }
 
-int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
-                       int16_t* levels) {
-    Vp8Dims dims;
-    HeaderFields h;
-    BoolReader b;
-    const int st = parse_frame_header(d, len, b, fd, dims, h);
-    if (st) return st;
+namespace {
+// The macroblock loop (decode_frame_, mod.rs:1255-1281): `b` is the first-partition reader standing at
+// the first macroblock, `parts` the token-partition readers.
+template <class Reader>
+int decode_macroblocks(Reader& b, Reader* parts, const HeaderFields& h, const Vp8Dims& dims, webpb200_mb_desc* mbs, int16_t* levels) {
     const bool segments_enabled = h.segments_enabled, update_map = h.update_map;
     const uint8_t* seg_probs = h.seg_probs;
     const int num_parts = h.num_parts, prob_skip = h.prob_skip;
-    BoolReader parts[8];
-    for (int i = 0; i < num_parts; i++) parts[i].init(d + h.part_off[i], h.part_len[i]);
     const TokenProbs* probs = reinterpret_cast<const TokenProbs*>(h.probs);  // [plane]
 
     // ---- macroblocks (decode_frame_, 1255-1281) ----
@@ -431,7 +439,7 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
     static const uint8_t kImpliedBMode[4] = {0, 2, 3, 1};  // DC->B_DC V->B_VE H->B_HE TM->B_TM (common.rs:75-83)
 
     for (int mby = 0; mby < mbh; mby++) {
-        BoolReader& tp = parts[mby % num_parts];
+        Reader& tp = parts[mby % num_parts];
         NeighbourCtx left;
         std::memset(&left, 0, sizeof(left));
         for (int mbx = 0; mbx < mbw; mbx++) {
@@ -510,6 +518,38 @@ int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, we
         }
     }
     return WEBPB200_OK;
+}
+}  // namespace
+
+int vp8_entropy_decode(const uint8_t* d, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs,
+                       int16_t* levels) {
+    Vp8Dims dims;
+    HeaderFields h;
+    BoolReader b;
+    const int st = parse_frame_header(d, len, b, fd, dims, h);
+    if (st) return st;
+    BoolReader parts[8];
+    for (int i = 0; i < h.num_parts; i++) parts[i].init(d + h.part_off[i], h.part_len[i]);
+    return decode_macroblocks(b, parts, h, dims, mbs, levels);
+}
+
+int vp8_entropy_decode_resumed(const uint8_t* d, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs, int16_t* levels) {
+    Vp8EntropyHdr eh;
+    int st = vp8_parse_header(d, len, fd, &eh);
+    if (st) return st;
+    // everything the loop needs is rebuilt from the exported header alone, as on the device
+    Vp8Dims dims{fd->width, fd->height, fd->mbw, fd->mbh};
+    HeaderFields h;
+    h.segments_enabled = eh.update_map != 0;  // only ever used together with update_map
+    h.update_map = eh.update_map != 0;
+    std::memcpy(h.seg_probs, eh.seg_probs, 3);
+    h.num_parts = eh.num_parts;
+    h.prob_skip = eh.has_prob_skip ? eh.prob_skip : -1;
+    std::memcpy(h.probs, eh.probs, sizeof(h.probs));
+    ByteBoolReader b, parts[8];
+    b.resume(d + eh.first_off, eh.first_len, eh.first);
+    for (int i = 0; i < eh.num_parts; i++) parts[i].init(d + eh.part_off[i], eh.part_len[i]);
+    return decode_macroblocks(b, parts, h, dims, mbs, levels);
 }
 
 }  // namespace webpb200

@@ -32,4 +32,9 @@ int vp8_entropy_decode(const uint8_t* data, size_t len, webpb200_frame_desc* fd,
 // first partition's boolean decoder at the first macroblock (eh->data_off is the caller's).
 int vp8_parse_header(const uint8_t* data, size_t len, webpb200_frame_desc* fd, Vp8EntropyHdr* eh);
 
+// vp8_entropy_decode done the way the device entropy stage does it, on the host: the frame header is
+// parsed into a Vp8EntropyHdr, and the macroblock loop then runs from that structure alone with the
+// byte-wise reader resumed from the exported state.  For tests of the hand-over (no GPU needed).
+int vp8_entropy_decode_resumed(const uint8_t* data, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs, int16_t* levels);
+
 }  // namespace webpb200

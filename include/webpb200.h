@@ -239,6 +239,12 @@ int webpb200_host_entropy_decode(const uint8_t* file, size_t len, webpb200_frame
 /* Evaluates the kernels' 4x4 sub-block prediction table on the CPU (table self-test):
  * edge13 = {P, A0..A7, L0..L3} (prediction.rs:290-337), mode = IntraMode 1..9. */
 void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8_t* out16);
+/* webpb200_host_entropy_decode (VP8 part only) done the way the device entropy stage is fed: frame
+ * header into the hand-over structure, then the macroblock loop from that structure alone with the
+ * boolean decoder resumed from the exported state.  Same outputs and statuses: a CPU-side check of
+ * the hand-over (csrc/entropy.h).  mbs_cap / levels_cap as in webpb200_host_entropy_decode. */
+int webpb200_debug_entropy_resumed(const uint8_t* file, size_t len, webpb200_frame_desc* fd,
+                                   webpb200_mb_desc* mbs, size_t mbs_cap, int16_t* levels, size_t levels_cap);
 
 /* Device-resident seam: reconstruct a batch whose packed arrays the caller already holds
  * in device memory (all pointers are device pointers; d_planes / d_out / d_scratch sized

@@ -155,3 +155,37 @@ def test_bpred_table_matches_oracle(W, oracle):
             oracle.lib().ora_predict_bmode(ws.ctypes.data + 16, 32, 4, 1, mode)
             want = np.array([ws[o + 32 * y + x] for y in range(4) for x in range(4)])
             assert np.array_equal(got, want), mode
+
+
+def _both_ways(W, data):
+    """(status, mbs, levels) of the ordinary host entropy decode and of the one resumed from the hand-over
+    structure the device entropy stage is fed with (csrc/entropy.h)."""
+    out = []
+    for fn in (lambda d: W.host_entropy_decode(d)[:3], W.entropy_decode_resumed):
+        try:
+            fd, mbs, levels = fn(data)
+            out.append((0, mbs, levels))
+        except W.DecodingError as e:
+            out.append((e.code, None, None))
+    return out
+
+
+@pytest.mark.parametrize("key", LOSSY_STILL)
+def test_header_handover_on_fixtures(W, fixtures, key):
+    (sa, ma, la), (sb, mb, lb) = _both_ways(W, bytes(fixtures["webp/" + key]))
+    assert sa == sb == 0 and np.array_equal(ma, mb) and np.array_equal(la, lb)
+
+
+def test_header_handover_on_synthetic_and_truncated(W, synth):
+    """Every synthetic feature case, and one multi-partition stream cut at many places: the decoder
+    resumed from the exported header state gives the same arrays and the same verdicts."""
+    for name, kw in SYNTH_CASES.items():
+        (sa, ma, la), (sb, mb, lb) = _both_ways(W, synth.webp_simple(synth.vp8_frame(**kw)))
+        assert sa == sb == 0 and np.array_equal(ma, mb) and np.array_equal(la, lb), name
+    vp8 = synth.vp8_frame(width=96, height=64, seed=78, filter_type=0, filter_level=10, log2_parts=2, segments=1,
+                          seg_quant=(20, 35, 50, 70), seg_lf=(10, 20, 30, 45), seg_probs=(128, 100, 200), prob_skip=150, p_skip=0.3)
+    for cut in list(range(len(vp8), 10, -7)) + [10, 9, 4]:
+        (sa, ma, la), (sb, mb, lb) = _both_ways(W, synth.webp_simple(vp8[:cut]))
+        assert sa == sb, cut
+        if sa == 0:
+            assert np.array_equal(ma, mb) and np.array_equal(la, lb), cut
