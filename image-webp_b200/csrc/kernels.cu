@@ -640,15 +640,18 @@ __device__ __forceinline__ int s2u(int v) {
 // 2: macroblock_filter (212-295); thresholds per 79-139; common_adjust 28-76.
 __device__ __forceinline__ void lf_line(uint8_t* p, int st, int kind, int edge_limit, int interior, int hev_thr) {
     const int P1 = p[-2 * st], P0 = p[-st], Q0 = p[0], Q1 = p[st];
-    if (abs(P0 - Q0) * 2 + (abs(P1 - Q1) >> 1) > edge_limit) return;
+    {   // |p0-q0| * 2 + |p1-q1| / 2 (loop_filter.rs:79-83) as sum-of-absolute-difference instructions
+        const unsigned d0 = __usad(P0, Q0, 0u);
+        if (__usad(P0, Q0, d0 + (__usad(P1, Q1, 0u) >> 1)) > (unsigned)edge_limit) return;
+    }
     int P3 = 0, P2 = 0, Q2 = 0, Q3 = 0;
     bool hv = true;  // the simple filter always uses the outer taps
     if (kind != 0) {
         P3 = p[-4 * st]; P2 = p[-3 * st]; Q2 = p[2 * st]; Q3 = p[3 * st];
-        if (abs(P3 - P2) > interior || abs(P2 - P1) > interior || abs(P1 - P0) > interior ||
-            abs(Q3 - Q2) > interior || abs(Q2 - Q1) > interior || abs(Q1 - Q0) > interior)
+        const unsigned dp = __usad(P1, P0, 0u), dq = __usad(Q1, Q0, 0u), lim = (unsigned)interior;
+        if (__usad(P3, P2, 0u) > lim || __usad(P2, P1, 0u) > lim || dp > lim || __usad(Q3, Q2, 0u) > lim || __usad(Q2, Q1, 0u) > lim || dq > lim)
             return;
-        hv = abs(P1 - P0) > hev_thr || abs(Q1 - Q0) > hev_thr;
+        hv = dp > (unsigned)hev_thr || dq > (unsigned)hev_thr;
     }
     const int p1 = u2s(P1), p0 = u2s(P0), q0 = u2s(Q0), q1 = u2s(Q1);
     if (kind == 2 && !hv) {
