@@ -910,7 +910,7 @@ __device__ __forceinline__ void chroma_row8(const uint8_t* row, int k4, int lim,
     const uint32_t wd = __ldg(reinterpret_cast<const uint32_t*>(row + k4));
     int c[6];
     c[0] = __ldg(row + max(k4 - 1, 0));
-    c[1] = wd & 0xff; c[2] = (wd >> 8) & 0xff; c[3] = (wd >> 16) & 0xff; c[4] = wd >> 24;
+    c[1] = __byte_perm(wd, 0, 0x4440); c[2] = __byte_perm(wd, 0, 0x4441); c[3] = __byte_perm(wd, 0, 0x4442); c[4] = __byte_perm(wd, 0, 0x4443);
     c[5] = __ldg(row + k4 + min(4, lim));
     if (lim < 3) {  // the row's last thread: columns past the visible width repeat the last one
         if (lim < 1) c[2] = c[1];
@@ -1007,11 +1007,11 @@ __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
     }
     uint32_t px[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(((i < 4 ? ywa.x : ywa.y) >> (8 * (i & 3))) & 0xff, ua[i], va[i]);
+    for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(__byte_perm(i < 4 ? ywa.x : ywa.y, 0, 0x4440 | (i & 3)), ua[i], va[i]);
     store_row8(A.out + fd->out_off + ((size_t)ya * w + x0) * bpp, px, n, bpp);
     if (has_b) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(((i < 4 ? ywb.x : ywb.y) >> (8 * (i & 3))) & 0xff, ub[i], vb[i]);
+        for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(__byte_perm(i < 4 ? ywb.x : ywb.y, 0, 0x4440 | (i & 3)), ub[i], vb[i]);
         store_row8(A.out + fd->out_off + ((size_t)yb * w + x0) * bpp, px, n, bpp);
     }
 }
