@@ -316,11 +316,12 @@ struct __align__(16) PredictSmem {
     uint8_t yw[17 * 32];
     uint8_t uw[9 * 16];
     uint8_t vw[9 * 16];
-    int16_t res[24 * 16];  // residuals of the 24 blocks, raster inside a block
-    int32_t wht[16];
+    int16_t res[2][24 * 16];  // residuals of the 24 blocks of the even / odd macroblock of a pair, raster inside a block
+    int32_t wht[2][16];
     uint32_t quant[16];                  // this frame's quantisers: [segment * 4 + class] = dc | ac << 16
-    int16_t lv[32 * 16];                 // next macroblock's levels (25 x 16 used), prefetched with cp.async
-    uint4 desc;                          // and its descriptor
+    int16_t lv[2][32 * 16];              // the next pair's levels (25 x 16 used each), prefetched with cp.async
+    uint4 desc[2];                       // and their descriptors
+    uint8_t map[64];                     // transform slot -> (macroblock of the pair) << 5 | block
 };
 
 struct PredictArgs {
@@ -342,15 +343,21 @@ struct PredictArgs {
 #define PREDICT_MIN_BLOCKS 4
 #endif
 
-// levels (800 B) + descriptor (16 B) of macroblock `mbi` -> the warp's staging buffer, asynchronously
-__device__ __forceinline__ void prefetch_mb(PredictSmem& S, const PredictArgs& A, size_t mbi, int lane) {
+// levels (800 B) + descriptor (16 B) of macroblocks `mbi` and (if `two`) `mbi + 1` -> the warp's staging
+// buffers, asynchronously
+__device__ __forceinline__ void prefetch_pair(PredictSmem& S, const PredictArgs& A, size_t mbi, bool two, int lane) {
     if (lane < 25) {
         const char* src = reinterpret_cast<const char*>(A.levels + mbi * WEBPB200_LEVELS_PER_MB) + lane * 32;
-        char* dst = reinterpret_cast<char*>(S.lv) + lane * 32;
+        char* dst = reinterpret_cast<char*>(S.lv[0]) + lane * 32;
         cp_async16(dst, src);
         cp_async16(dst + 16, src + 16);
+        if (two) {
+            cp_async16(dst + sizeof(S.lv[0]), src + 2 * WEBPB200_LEVELS_PER_MB);
+            cp_async16(dst + sizeof(S.lv[0]) + 16, src + 2 * WEBPB200_LEVELS_PER_MB + 16);
+        }
     } else if (lane == 25) {
-        cp_async16(&S.desc, A.mbs + mbi);
+        cp_async16(&S.desc[0], A.mbs + mbi);
+        if (two) cp_async16(&S.desc[1], A.mbs + mbi + 1);
     }
     cp_async_commit();
 }
@@ -400,7 +407,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         uint8_t* const yout = Y + (size_t)(mby * 16 + (lane >> 1)) * ystride + (lane & 1) * 8;
         uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
 
-        prefetch_mb(S, A, mb_row0, lane);
+        prefetch_pair(S, A, mb_row0, mbw > 1, lane);
         // the frame's quantisers, once per row (class 0 = Y, 1 = U/V, 2 = Y2): descriptor loads would
         // miss L1 on every macroblock because the acquire fences keep invalidating it
         if (lane < 16) {
@@ -412,70 +419,95 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         }
         __syncwarp();
         const int qcls = lane < 16 ? 0 : lane < 24 ? 1 : 2;
+        uint4 desc_odd = make_uint4(0, 0, 0, 0);  // descriptor of the pair's second macroblock, kept for its turn
         for (int mbx = 0; mbx < mbw; mbx++) {
             const size_t mbi = mb_row0 + mbx;
-            cp_async_wait_all();
-            __syncwarp();
-            const uint4 mbw4 = S.desc;
-            const uint4* lp = reinterpret_cast<const uint4*>(S.lv + lane * 16);  // lanes 25..31 read padding
-            const uint4 lv_lo = lp[0], lv_hi = lp[1];
-            __syncwarp();
-            if (mbx + 1 < mbw) prefetch_mb(S, A, mbi + 1, lane);
-            const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff, segment = (mbw4.x >> 16) & 3;
-            const bool skipped = (mbw4.x >> 24) & 1;
-            const uint32_t nflags = mbw4.y;
-            const uint32_t bpred_lo = mbw4.z, bpred_hi = mbw4.w;
-
-            // ---- dequantise + inverse transforms: lane b owns block b (24 = Y2) ----
-            // read_coefficients mod.rs:865-866 (the multiply), read_residual_data 888-952
-            bool nzdct = false;
-            if (!skipped) {
-                int c[16];
-                unpack8(lv_lo, c);
-                unpack8(lv_hi, c + 8);
-                const uint32_t qw = S.quant[segment * 4 + qcls];
-                const int dcq = qw & 0xffff, acq = qw >> 16;  // quantisers are positive and below 2^15
-                if (ymode != 4) {
-                    if (lane == 24) {
-                        c[0] *= dcq;
-#pragma unroll
-                        for (int i = 1; i < 16; i++) c[i] *= acq;
-                        iwht4x4(c);
-#pragma unroll
-                        for (int i = 0; i < 16; i++) S.wht[i] = c[i];
-                    }
-                    __syncwarp();
-                }
-                bool nz = false;
-                if (lane < 24) {
+            uint4 mbw4 = desc_odd;
+            if ((mbx & 1) == 0) {
+                // ---- dequantise + inverse transforms for the pair (mbx, mbx + 1) ----
+                // read_coefficients mod.rs:865-866 (the multiply), read_residual_data 888-952.  On average
+                // 13 of a macroblock's 24 blocks carry coefficients, so the blocks that need a transform
+                // of BOTH macroblocks usually fit the warp's 32 lanes: one pass instead of two.
+                const bool two = mbx + 1 < mbw;
+                cp_async_wait_all();
+                __syncwarp();
+                mbw4 = S.desc[0];
+                desc_odd = two ? S.desc[1] : make_uint4(0x01000000u, 0, 0, 0);  // a missing partner counts as skipped
+                const uint32_t d0 = mbw4.x, d1 = desc_odd.x;
+                const bool use0 = !((d0 >> 24) & 1), use1 = !((d1 >> 24) & 1);       // not skipped
+                const bool y2_0 = use0 && (d0 & 0xff) != 4, y2_1 = use1 && (d1 & 0xff) != 4;
+                // Y2 first (iwht, transform.rs:54-86): lane 24 for the even macroblock, lane 25 for the odd one
+                if ((lane == 24 && y2_0) || (lane == 25 && y2_1)) {
+                    const int wh = lane - 24;
+                    const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + 24 * 16);
+                    int c[16];
+                    unpack8(lp[0], c);
+                    unpack8(lp[1], c + 8);
+                    const uint32_t qw = S.quant[(((wh ? d1 : d0) >> 16) & 3) * 4 + 2];
+                    const int dcq = qw & 0xffff, acq = qw >> 16;
                     c[0] *= dcq;
 #pragma unroll
                     for (int i = 1; i < 16; i++) c[i] *= acq;
-                    if (ymode != 4 && lane < 16) c[0] = S.wht[lane];
-                    nz = c[0] != 0 || ((nflags >> lane) & 1);  // mod.rs:920, 949
+                    iwht4x4(c);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) S.wht[wh][i] = c[i];
                 }
-                const unsigned nzmask = __ballot_sync(kFull, nz);
-                nzdct = nzmask != 0;
-                if (nzdct) {  // idct(0) = 0, so running it on blocks without the flag is value-neutral
-                    if (lane < 24) {
+                __syncwarp();
+                // which blocks need the IDCT: DC != 0 or the "has coefficients" flag (mod.rs:920, 949)
+                bool nz0 = false, nz1 = false;
+                if (lane < 24) {
+                    const int dc0 = (y2_0 && lane < 16) ? S.wht[0][lane] : (int)S.lv[0][lane * 16];
+                    const int dc1 = (y2_1 && lane < 16) ? S.wht[1][lane] : (int)S.lv[1][lane * 16];
+                    nz0 = use0 && (dc0 != 0 || ((mbw4.y >> lane) & 1));
+                    nz1 = use1 && (dc1 != 0 || ((desc_odd.y >> lane) & 1));
+                    // blocks that need none have zero residuals
+                    uint4* r0 = reinterpret_cast<uint4*>(S.res[0] + lane * 16);
+                    uint4* r1 = reinterpret_cast<uint4*>(S.res[1] + lane * 16);
+                    if (!nz0) { r0[0] = make_uint4(0, 0, 0, 0); r0[1] = make_uint4(0, 0, 0, 0); }
+                    if (!nz1) { r1[0] = make_uint4(0, 0, 0, 0); r1[1] = make_uint4(0, 0, 0, 0); }
+                }
+                const unsigned m0 = __ballot_sync(kFull, nz0), m1 = __ballot_sync(kFull, nz1);
+                const int n0 = __popc(m0), total = n0 + __popc(m1);
+                const unsigned below = (1u << lane) - 1u;
+                if (nz0) S.map[__popc(m0 & below)] = (uint8_t)lane;
+                if (nz1) S.map[n0 + __popc(m1 & below)] = (uint8_t)(32 + lane);
+                if (lane == 0) {
+                    A.mbinfo[mbi] = m0 ? 1 : 0;
+                    if (two) A.mbinfo[mbi + 1] = m1 ? 1 : 0;
+                }
+                __syncwarp();
+                for (int base = 0; base < total; base += 32) {
+                    const int slot = base + lane;
+                    if (slot < total) {
+                        const int mm = S.map[slot], wh = mm >> 5, blk = mm & 31;
+                        const uint32_t dw = wh ? d1 : d0;
+                        const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + blk * 16);
+                        int c[16];
+                        unpack8(lp[0], c);
+                        unpack8(lp[1], c + 8);
+                        const uint32_t qw = S.quant[((dw >> 16) & 3) * 4 + (blk < 16 ? 0 : 1)];
+                        const int dcq = qw & 0xffff, acq = qw >> 16;  // quantisers are positive and below 2^15
+                        c[0] *= dcq;
+#pragma unroll
+                        for (int i = 1; i < 16; i++) c[i] *= acq;
+                        if (blk < 16 && (wh ? y2_1 : y2_0)) c[0] = S.wht[wh][blk];
                         idct4x4(c);
                         uint4 o0, o1;
                         o0.x = pack_res(c[0], c[1]);  o0.y = pack_res(c[2], c[3]);
                         o0.z = pack_res(c[4], c[5]);  o0.w = pack_res(c[6], c[7]);
                         o1.x = pack_res(c[8], c[9]);  o1.y = pack_res(c[10], c[11]);
                         o1.z = pack_res(c[12], c[13]); o1.w = pack_res(c[14], c[15]);
-                        uint4* rp = reinterpret_cast<uint4*>(S.res + lane * 16);
+                        uint4* rp = reinterpret_cast<uint4*>(S.res[wh] + blk * 16);
                         rp[0] = o0;
                         rp[1] = o1;
                     }
                 }
+                __syncwarp();
+                if (mbx + 2 < mbw) prefetch_pair(S, A, mbi + 2, mbx + 3 < mbw, lane);
             }
-            if (!nzdct && lane < 24) {
-                uint4* rp = reinterpret_cast<uint4*>(S.res + lane * 16);
-                rp[0] = make_uint4(0, 0, 0, 0);
-                rp[1] = make_uint4(0, 0, 0, 0);
-            }
-            if (lane == 0) A.mbinfo[mbi] = nzdct ? 1 : 0;
+            const int16_t* const res = S.res[mbx & 1];
+            const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff;
+            const uint32_t bpred_lo = mbw4.z, bpred_hi = mbw4.w;
 
             // ---- neighbours: wait for the above-right macroblock, then build the borders ----
             // create_border_luma / create_border_chroma, prediction.rs:13-123
@@ -527,7 +559,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                     const int cc = S.yw[org + (int)(int8_t)((w >> 16) & 0xff)];
                     int pred = (w >> 24) ? clamp255(a + b - cc) : (a + 2 * b + cc + 2) >> 2;
                     if (mode == 0) pred = (dc + 4) >> 3;
-                    const int r = S.res[sb * 16 + p];
+                    const int r = res[sb * 16 + p];
                     S.yw[org + pix] = (uint8_t)clamp255(pred + r);  // add_residue
                     __syncwarp();
                 }
@@ -557,8 +589,8 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 }
                 __syncwarp();  // all reads of the borders done before the block is written
                 const int blk = (row >> 2) * 4 + (x0 >> 2);
-                const uint2 r0 = *reinterpret_cast<const uint2*>(S.res + blk * 16 + (row & 3) * 4);
-                const uint2 r1 = *reinterpret_cast<const uint2*>(S.res + (blk + 1) * 16 + (row & 3) * 4);
+                const uint2 r0 = *reinterpret_cast<const uint2*>(res + blk * 16 + (row & 3) * 4);
+                const uint2 r1 = *reinterpret_cast<const uint2*>(res + (blk + 1) * 16 + (row & 3) * 4);
                 const int rr[8] = {(int)(short)(r0.x & 0xffff), (int)r0.x >> 16, (int)(short)(r0.y & 0xffff), (int)r0.y >> 16,
                                    (int)(short)(r1.x & 0xffff), (int)r1.x >> 16, (int)(short)(r1.y & 0xffff), (int)r1.y >> 16};
                 const uint32_t o0 = clamp_pack4(pr[0] + rr[0], pr[1] + rr[1], pr[2] + rr[2], pr[3] + rr[3]);
@@ -603,7 +635,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 }
                 __syncwarp();
                 const int blk = 16 + plane * 4 + (row >> 2) * 2 + (x0 >> 2);
-                const uint2 r = *reinterpret_cast<const uint2*>(S.res + blk * 16 + (row & 3) * 4);
+                const uint2 r = *reinterpret_cast<const uint2*>(res + blk * 16 + (row & 3) * 4);
                 const int rr[4] = {(int)(short)(r.x & 0xffff), (int)r.x >> 16, (int)(short)(r.y & 0xffff), (int)r.y >> 16};
                 const uint32_t o = clamp_pack4(pr[0] + rr[0], pr[1] + rr[1], pr[2] + rr[2], pr[3] + rr[3]);
                 cw32[(1 + row) * 4 + 1 + (x0 >> 2)] = o;
