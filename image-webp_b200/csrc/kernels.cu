@@ -453,27 +453,40 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                     for (int i = 0; i < 16; i++) S.wht[wh][i] = c[i];
                 }
                 __syncwarp();
-                // which blocks need the IDCT: DC != 0 or the "has coefficients" flag (mod.rs:920, 949)
-                bool nz0 = false, nz1 = false;
+                // Which blocks get the IDCT (mod.rs:920, 949: DC != 0 or the "has coefficients" flag).  A block
+                // without the flag has no coefficients of its own; if its DC (from the Y2 block) is not zero the
+                // transform of a lone DC is the constant (dc + 4) >> 3, written here directly -- those blocks
+                // (most luma blocks of a 16x16-predicted macroblock) then do not take a lane of the IDCT pass.
+                bool nz0 = false, nz1 = false, need0 = false, need1 = false;
                 if (lane < 24) {
                     const int dc0 = (y2_0 && lane < 16) ? S.wht[0][lane] : (int)S.lv[0][lane * 16];
                     const int dc1 = (y2_1 && lane < 16) ? S.wht[1][lane] : (int)S.lv[1][lane * 16];
-                    nz0 = use0 && (dc0 != 0 || ((mbw4.y >> lane) & 1));
-                    nz1 = use1 && (dc1 != 0 || ((desc_odd.y >> lane) & 1));
-                    // blocks that need none have zero residuals
+                    need0 = use0 && ((mbw4.y >> lane) & 1);
+                    need1 = use1 && ((desc_odd.y >> lane) & 1);
+                    nz0 = need0 || (use0 && dc0 != 0);
+                    nz1 = need1 || (use1 && dc1 != 0);
                     uint4* r0 = reinterpret_cast<uint4*>(S.res[0] + lane * 16);
                     uint4* r1 = reinterpret_cast<uint4*>(S.res[1] + lane * 16);
-                    if (!nz0) { r0[0] = make_uint4(0, 0, 0, 0); r0[1] = make_uint4(0, 0, 0, 0); }
-                    if (!nz1) { r1[0] = make_uint4(0, 0, 0, 0); r1[1] = make_uint4(0, 0, 0, 0); }
+                    if (!need0) {
+                        const int r = nz0 ? (dc0 + 4) >> 3 : 0;
+                        const uint32_t w = pack_res(r, r);
+                        r0[0] = make_uint4(w, w, w, w); r0[1] = make_uint4(w, w, w, w);
+                    }
+                    if (!need1) {
+                        const int r = nz1 ? (dc1 + 4) >> 3 : 0;
+                        const uint32_t w = pack_res(r, r);
+                        r1[0] = make_uint4(w, w, w, w); r1[1] = make_uint4(w, w, w, w);
+                    }
                 }
-                const unsigned m0 = __ballot_sync(kFull, nz0), m1 = __ballot_sync(kFull, nz1);
+                const unsigned m0 = __ballot_sync(kFull, need0), m1 = __ballot_sync(kFull, need1);
+                const bool any0 = __any_sync(kFull, nz0), any1 = __any_sync(kFull, nz1);
                 const int n0 = __popc(m0), total = n0 + __popc(m1);
                 const unsigned below = (1u << lane) - 1u;
-                if (nz0) S.map[__popc(m0 & below)] = (uint8_t)lane;
-                if (nz1) S.map[n0 + __popc(m1 & below)] = (uint8_t)(32 + lane);
+                if (need0) S.map[__popc(m0 & below)] = (uint8_t)lane;
+                if (need1) S.map[n0 + __popc(m1 & below)] = (uint8_t)(32 + lane);
                 if (lane == 0) {
-                    A.mbinfo[mbi] = m0 ? 1 : 0;
-                    if (two) A.mbinfo[mbi + 1] = m1 ? 1 : 0;
+                    A.mbinfo[mbi] = any0 ? 1 : 0;
+                    if (two) A.mbinfo[mbi + 1] = any1 ? 1 : 0;
                 }
                 __syncwarp();
                 for (int base = 0; base < total; base += 32) {
