@@ -538,11 +538,12 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
         }
         if (A.rows_done) {
             // This row's levels and descriptors are complete: tell the host, which starts reconstructing
-            // finished bands of rows while the rest is still being decoded.  Device-scope fence (the
-            // consumers are kernels launched on this GPU once the host has seen the count), then a
-            // plain posted store into this partition's own slot -- system-scope ATOMICS on host memory
-            // cut concurrent D2H copies from 57 to 6 GB/s (tools/micro/copybench.cu).
-            __threadfence();
+            // finished bands of rows while the rest is still being decoded.  The observer is the host, so
+            // the fence that orders this row's global writes before the flag is system-scope; the flag
+            // itself is a plain posted store into this partition's own slot -- system-scope ATOMICS on
+            // host memory cut concurrent D2H copies from 57 to 6 GB/s (tools/micro/copybench.cu), a
+            // fence once per macroblock row does not.
+            __threadfence_system();
             *reinterpret_cast<volatile unsigned int*>(A.rows_done + (size_t)f * 8 + p) = (unsigned int)(mby / P + 1);
         }
     }

@@ -276,6 +276,9 @@ struct Decoder {
                 size_t length, dcode;
                 if (!copy_value(s - 256, &length)) return WEBPB200_ERR_BITSTREAM;
                 uint32_t ds;
+                // a length code and its extra bits may have used 25 of the 57 bits fill() guarantees; the
+                // distance code and its extra bits can need 33 more
+                if (br.n < 33) br.fill();
                 NEED(g->c[4].get(br, &ds));
                 if (!copy_value(ds, &dcode)) return WEBPB200_ERR_BITSTREAM;
                 size_t dist;
