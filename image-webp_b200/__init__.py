@@ -87,7 +87,7 @@ SYMBOLS = [
     "webpb200_batch_time", "webpb200_batch_size", "webpb200_batch_get_planes", "webpb200_batch_get_packed",
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
-    "webpb200_predict_device_static", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
+    "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
     "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
 ]
 
@@ -155,6 +155,7 @@ def lib():
     L.webpb200_reconstruct_device.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, C.c_uint, vp]
     L.webpb200_decode_animation.argtypes = [vp, vp, sz, pp, sz, C.POINTER(u32), i32, i32, i32]
     L.webpb200_predict_device_static.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
+    L.webpb200_predict_device_static_check.argtypes = [vp]
     _lib = L
     return L
 

@@ -171,6 +171,7 @@ static_assert(sizeof(webpb200_frame_desc) == 136 && sizeof(webpb200_mb_desc) == 
 struct webpb200_ctx {
     int device = 0;
     int sm_count = 0;
+    int predict_blocks = 1, filter_blocks = 1;  // resident blocks per SM of the wavefront kernels on this device
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;      // reconstruction of finished bands while k_entropy still runs
     unsigned int* h_rows = nullptr;      // mapped pinned: [frame * 8 + partition] rows finished (written by k_entropy)
@@ -192,7 +193,7 @@ struct webpb200_ctx {
     std::vector<WorkItem> items;
     uint64_t total_mbs = 0, total_rows = 0, total_px = 0;
     uint64_t plane_bytes = 0, out_bytes = 0, alpha_bytes = 0;
-    size_t aux_rowmap_off = 0, aux_order_off = 0, aux_lists_off = 0, aux_bytes = 0;
+    size_t aux_rowmap_off = 0, aux_order_off = 0, aux_recbase_off = 0, aux_lists_off = 0, aux_bytes = 0;
     BatchDev bd{};
     bool uploaded = false;
 
@@ -223,6 +224,19 @@ void fill_row_order(const webpb200_frame_desc* frames, int i0, int i1, uint32_t*
     for (uint32_t r = 0; r < max_h; r++)
         for (int i = i0; i < i1; i++)
             if (frames[i].mbh > r) order[k++] = frames[i].row_base + r;
+}
+
+// row id -> image, and row id -> first edge-record slot of that row (kernels.cuh: image i owns 2 * mbw_i
+// slots, its row y uses the mbw_i slots of parity y & 1)
+void fill_row_tables(const webpb200_frame_desc* frames, int n, uint32_t* rowmap, uint32_t* recbase) {
+    uint32_t slot = 0;
+    for (int i = 0; i < n; i++) {
+        for (uint32_t r = 0; r < frames[i].mbh; r++) {
+            rowmap[frames[i].row_base + r] = (uint32_t)i;
+            recbase[frames[i].row_base + r] = slot + (r & 1) * frames[i].mbw;
+        }
+        slot += 2u * frames[i].mbw;
+    }
 }
 
 // Host side of a batch, part 1: probe sizes, lay the arenas out, size the pinned staging, build
@@ -295,12 +309,11 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
     CU(c, c->h_alpha.reserve((size_t)std::max<uint64_t>(aoff, 1)), "pinned alpha");
     c->aux_rowmap_off = 0;
     c->aux_order_off = (size_t)align256(4 * rows);
-    c->aux_lists_off = c->aux_order_off + (size_t)align256(4 * rows);
+    c->aux_recbase_off = c->aux_order_off + (size_t)align256(4 * rows);
+    c->aux_lists_off = c->aux_recbase_off + (size_t)align256(4 * rows);
     c->aux_bytes = c->aux_lists_off + (size_t)align256(16 * (uint64_t)std::max(n, 1));
     CU(c, c->h_aux.reserve(c->aux_bytes), "pinned aux");
-    uint32_t* rowmap = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
-    for (int i = 0; i < n; i++)
-        for (uint32_t r = 0; r < frames[i].mbh; r++) rowmap[frames[i].row_base + r] = (uint32_t)i;
+    fill_row_tables(frames, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_rowmap_off), reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_recbase_off));
     BatchDev& bd = c->bd;
     std::memset(&bd, 0, sizeof(bd));
     bd.n_frames = n;
@@ -308,7 +321,9 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
     bd.max_w = max_w;
     bd.max_h = max_h;
     bd.sm_count = c->sm_count;
-    bd.lay = scratch_layout(rows, mbs);
+    bd.predict_blocks = c->predict_blocks;
+    bd.filter_blocks = c->filter_blocks;
+    bd.lay = scratch_layout(rows, mbs, edge_slots_of(frames, n));
     return 0;
 }
 
@@ -408,6 +423,17 @@ int reserve_device(webpb200_ctx* c) {
     return 0;
 }
 
+// rowmap, ticket order and edge-slot table -> scratch arena (they live next to the counters they are used with)
+int upload_row_tables(webpb200_ctx* c, const uint8_t* aux, cudaMemcpyKind kind, cudaStream_t s) {
+    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
+    if (!c->total_rows) return 0;
+    const size_t bytes = 4 * (size_t)c->total_rows;
+    CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, aux + c->aux_rowmap_off, bytes, kind, s), "rowmap");
+    CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, aux + c->aux_order_off, bytes, kind, s), "row order");
+    CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.recbase_off, aux + c->aux_recbase_off, bytes, kind, s), "edge slots");
+    return 0;
+}
+
 int upload(webpb200_ctx* c) {
     int rc = reserve_device(c);
     if (rc) return rc;
@@ -420,12 +446,7 @@ int upload(webpb200_ctx* c) {
     }
     if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
     CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
-    // the row map lives in the scratch arena next to the counters it is used with
-    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
-    if (c->total_rows) {
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->d_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "rowmap");
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->d_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyDeviceToDevice, s), "row order");
-    }
+    if (int r = upload_row_tables(c, c->d_aux.p, cudaMemcpyDeviceToDevice, s)) return r;
     c->uploaded = true;
     return 0;
 }
@@ -433,11 +454,12 @@ int upload(webpb200_ctx* c) {
 // events: optional array of 5 events recorded before/after each stage (timing runs)
 int reconstruct(webpb200_ctx* c, const BatchDev& bd, unsigned stages, cudaStream_t s, cudaEvent_t* events) {
     if (bd.total_rows == 0) return 0;
-    // ticket counters and row progress start at zero; the watchdog word (offset 8) is cleared once
-    // per batch, not per pass, so that a trip in any pass is still there when the host looks
-    CU(c, cudaMemsetAsync(bd.scratch, 0, 8, s), "clear tickets");
-    CU(c, cudaMemsetAsync(bd.scratch + bd.lay.progress_pred_off, 0, (size_t)(bd.lay.zero_bytes - bd.lay.progress_pred_off), s), "clear progress");
+    // ticket counters and edge records start at zero; the watchdog word (offset 8) is cleared once
+    // per batch, not per pass, so that a trip in any pass is still there when the host looks.  The
+    // clears belong to the pass: a timing run records its first event before them.
     if (events) cudaEventRecord(events[0], s);
+    CU(c, cudaMemsetAsync(bd.scratch, 0, 8, s), "clear tickets");
+    CU(c, cudaMemsetAsync(bd.scratch + bd.lay.edge_pred_off, 0, (size_t)(bd.lay.zero_bytes - bd.lay.edge_pred_off), s), "clear edge records");
     if (stages & 1) { CU(c, launch_predict(bd, s), "k_predict"); c->launches++; }
     if (events) cudaEventRecord(events[1], s);
     if (stages & 2) { CU(c, launch_loopfilter(bd, s), "k_loopfilter"); c->launches++; }
@@ -590,8 +612,12 @@ extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
     }
     c->sm_count = prop.multiProcessorCount;
     for (auto& e : c->ev) cudaEventCreate(&e);
-    upload_tables_once();
+    if (upload_tables_once() != cudaSuccess) {
+        delete c;
+        return WEBPB200_ERR_CUDA;
+    }
     upload_entropy_tables_once();
+    wavefront_blocks_per_sm(&c->predict_blocks, &c->filter_blocks);
     if (const char* e = std::getenv("WEBPB200_ENTROPY")) c->entropy_where = std::strcmp(e, "device") == 0 ? WEBPB200_ENTROPY_DEVICE : std::strcmp(e, "host") == 0 ? WEBPB200_ENTROPY_HOST : WEBPB200_ENTROPY_AUTO;
     if (cudaDeviceSynchronize() != cudaSuccess) {
         delete c;
@@ -930,11 +956,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     CU(c, cudaMemcpyAsync(c->d_ehdr.p, hdrs, sizeof(Vp8EntropyHdr) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D entropy headers");
     if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
     CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
-    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
-    if (c->total_rows) {
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, c->h_aux.p + c->aux_rowmap_off, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "rowmap");
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, c->h_aux.p + c->aux_order_off, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "row order");
-    }
+    if (int r2 = upload_row_tables(c, c->h_aux.p, cudaMemcpyHostToDevice, s)) return r2;
     c->uploaded = true;
     c->last_entropy = WEBPB200_ENTROPY_DEVICE;
     c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + sizeof(Vp8EntropyHdr) * (uint64_t)n + bits_bytes + c->alpha_bytes + c->aux_bytes;
@@ -943,7 +965,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     // band in host-visible memory, and as soon as a band is complete in every frame this thread
     // launches its prediction, the loop filter of the band before (one band late: prediction reads
     // unfiltered neighbours, mod.rs:1289-1294), the colour conversion of the rows that are final
-    // (the last 3 pixel rows above a band edge still wait for the next band's top-edge filter) and
+    // (the last rows above a band edge are still in the edge record of the loop filter) and
     // their copy to the host -- all on a second stream, under the still running k_entropy.
     constexpr int kMaxBands = 16;
     int nbands = 0;
@@ -1007,7 +1029,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         CU(c, cudaEventRecord(c->ev[4], s), "event");  // k_entropy (and the status copy) finished
         CU(c, cudaStreamWaitEvent(r, c->ev[7], 0), "wait inputs");
         const BatchDev& B = c->bd;
-        CU(c, cudaMemsetAsync(B.scratch + B.lay.progress_pred_off, 0, (size_t)(B.lay.zero_bytes - B.lay.progress_pred_off), r), "clear progress");
+        CU(c, cudaMemsetAsync(B.scratch + B.lay.edge_pred_off, 0, (size_t)(B.lay.zero_bytes - B.lay.edge_pred_off), r), "clear edge records");
         const int mbh = frames[0].mbh, w = frames[0].width, h = frames[0].height;
         const int q_all = h / 2 + 1;
         int q_done = 0;
@@ -1085,9 +1107,11 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
             CU(c, launch_loopfilter(rows_dev(lf_done, lf_end), r), "k_loopfilter");
             c->launches++;
             lf_done = lf_end;
-            // rows whose pixels are final: all but the 3 above the next unfiltered macroblock edge
+            // rows whose pixels are final and in the planes: the bottom 4 luma and chroma rows of the last filtered
+            // macroblock row are still in its edge record (the row below filters and stores them), so the
+            // last row pair converted is the one whose second chroma row is the row just above those
             if (trace) cudaEventRecord(bev[k][1], r);
-            if ((rc = emit(lf_end < mbh ? 8 * lf_end - 3 : q_all)) != 0) return rc;
+            if ((rc = emit(lf_end < mbh ? 8 * lf_end - 4 : q_all)) != 0) return rc;
             if (trace) cudaEventRecord(bev[k][2], r);
         }
         const double t_lastband = ms_since();
@@ -1226,12 +1250,7 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
     const int nchunks = (int)chunk_end.size();
     uint32_t* order = reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off);
     for (int k = 0; k < nchunks; k++) fill_row_order(frames, k ? chunk_end[k - 1] : 0, chunk_end[k], order);
-    CU(c, cudaMemsetAsync(c->d_scratch.p, 0, 256, s), "clear watchdog");
-    if (c->total_rows) {
-        const uint32_t* rowmap = reinterpret_cast<const uint32_t*>(c->h_aux.p + c->aux_rowmap_off);
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.rowmap_off, rowmap, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "rowmap");
-        CU(c, cudaMemcpyAsync(c->d_scratch.p + c->bd.lay.order_off, order, 4 * (size_t)c->total_rows, cudaMemcpyHostToDevice, s), "row order");
-    }
+    if (int r2 = upload_row_tables(c, c->h_aux.p, cudaMemcpyHostToDevice, s)) return r2;
     c->uploaded = true;
 
     // host threads: images in order, one at a time each
@@ -1403,7 +1422,7 @@ extern "C" int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n
     if (plane_bytes) *plane_bytes = p;
     if (out_bytes) *out_bytes = o;
     if (scratch_bytes)
-        *scratch_bytes = scratch_layout(rows, mbs).total + align256(16 * (uint64_t)std::max(n, 1)) + (alpha_end ? alpha_handoff_size(alpha_end) : 0);
+        *scratch_bytes = scratch_layout(rows, mbs, edge_slots_of(frames, n)).total + align256(16 * (uint64_t)std::max(n, 1)) + (alpha_end ? alpha_handoff_size(alpha_end) : 0);
     return 0;
 }
 
@@ -1425,9 +1444,9 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
         bd.max_w = std::max<uint32_t>(bd.max_w, hf[i].width);
         bd.max_h = std::max<uint32_t>(bd.max_h, hf[i].height);
     }
-    bd.lay = scratch_layout(rows, mbs);
-    // row map and ALPH lists are built on the host and copied into the caller's scratch arena
-    std::vector<uint32_t> rowmap((size_t)rows, 0), order((size_t)rows, 0);
+    bd.lay = scratch_layout(rows, mbs, edge_slots_of(hf, n));
+    // row tables and ALPH lists are built on the host and copied into the caller's scratch arena
+    std::vector<uint32_t> rowmap((size_t)rows, 0), order((size_t)rows, 0), recbase((size_t)rows, 0);
     std::vector<int> lists((size_t)4 * n, 0);
     {
         size_t k = 0;  // rows in use may be fewer than `rows` if the caller left gaps; fill those with valid ids
@@ -1438,8 +1457,8 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
                 if (hf[i].mbh > r) order[k++] = hf[i].row_base + r;
         rows = k;  // tickets handed out = rows that exist
     }
+    fill_row_tables(hf, n, rowmap.data(), recbase.data());
     for (int i = 0; i < n; i++) {
-        for (uint32_t r = 0; r < hf[i].mbh; r++) rowmap[hf[i].row_base + r] = (uint32_t)i;
         if (hf[i].alpha_mode && hf[i].out_bpp == 4) {
             const int m = hf[i].alpha_filter & 3;
             lists[(size_t)m * n + bd.alpha_counts[m]++] = i;
@@ -1451,11 +1470,13 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     CU(c, cudaMemsetAsync(scratch, 0, 256, s), "clear watchdog");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.rowmap_off, rowmap.data(), 4 * rowmap.size(), cudaMemcpyHostToDevice, s), "rowmap");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.order_off, order.data(), 4 * order.size(), cudaMemcpyHostToDevice, s), "row order");
+    CU(c, cudaMemcpyAsync(scratch + bd.lay.recbase_off, recbase.data(), 4 * recbase.size(), cudaMemcpyHostToDevice, s), "edge slots");
     CU(c, cudaMemcpyAsync(scratch + bd.lay.total, lists.data(), sizeof(int) * lists.size(), cudaMemcpyHostToDevice, s), "lists");
     CU(c, cudaStreamSynchronize(s), "sync");  // the host vectors go away
     bd.frames = d_frames; bd.mbs = d_mbs; bd.levels = d_levels; bd.alpha = d_alpha;
     bd.planes = d_planes; bd.out = d_out; bd.scratch = scratch;
     bd.n_frames = n; bd.total_rows = (uint32_t)rows; bd.sm_count = c->sm_count;
+    bd.predict_blocks = c->predict_blocks; bd.filter_blocks = c->filter_blocks;
     bd.alpha_lists = reinterpret_cast<const int*>(scratch + bd.lay.total);
     if (alpha_end) {
         bd.alpha_handoff = reinterpret_cast<uint16_t*>(scratch + bd.lay.total + align256(16 * (uint64_t)n));

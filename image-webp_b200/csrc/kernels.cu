@@ -12,7 +12,15 @@
 // image and rows advance as a wavefront (row y may work on macroblock x once row y-1 has
 // finished macroblock x+1, i.e. the x+2y order the dependencies allow).  Rows are handed out
 // by a global ticket counter in (image, row) order, so every dependency points at a lower
-// ticket and the scheme cannot deadlock whatever the residency.  Integer/byte work bound by
+// ticket and the scheme cannot deadlock whatever the residency.
+//
+// Hand-off between rows: what row y needs from row y-1 is its bottom edge (one pixel row for the
+// prediction, four for the loop filter).  The producer writes that edge, per macroblock, into an
+// EDGE RECORD of 8-byte units {4 pixels, tag}, tag = producer's macroblock row + 1; the consumer
+// polls the unit until the tag is there.  An aligned 8-byte access is single-copy atomic, so the
+// pixels and their valid mark arrive together: no counter, no release/acquire fence on either side
+// (round 1's counters cost a MEMBAR per macroblock in the producer and one per wait in the
+// consumer -- 30 % of all stall samples on large frames).  The records are cleared before a pass.  Integer/byte work bound by
 // instruction issue and HBM, so no tensor cores and no TMA tiles: coalesced 16-byte loads of
 // the level array, shared-memory staging of the macroblock workspace, L2-coherent (ld.cg)
 // reads of neighbour rows.
@@ -23,18 +31,25 @@
 
 namespace webpb200 {
 
-ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs) {
+ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs, uint64_t edge_slots, bool with_filter) {
     ScratchLayout l;
     auto up = [](uint64_t v) { return (v + 255) & ~(uint64_t)255; };
     l.tickets_off = 0;
-    l.progress_pred_off = 256;
-    l.progress_lf_off = up(l.progress_pred_off + 4 * total_rows);
-    l.zero_bytes = up(l.progress_lf_off + 4 * total_rows);
+    l.edge_pred_off = 256;
+    l.edge_lf_off = up(l.edge_pred_off + kEdgePredBytes * edge_slots);
+    l.zero_bytes = up(l.edge_lf_off + (with_filter ? kEdgeFilterBytes * edge_slots : 0));
     l.rowmap_off = l.zero_bytes;
     l.order_off = up(l.rowmap_off + 4 * total_rows);
-    l.mbinfo_off = up(l.order_off + 4 * total_rows);
+    l.recbase_off = up(l.order_off + 4 * total_rows);
+    l.mbinfo_off = up(l.recbase_off + 4 * total_rows);
     l.total = up(l.mbinfo_off + total_mbs);
     return l;
+}
+
+uint64_t edge_slots_of(const webpb200_frame_desc* frames, int n) {
+    uint64_t slots = 0;
+    for (int i = 0; i < n; i++) slots += 2 * (uint64_t)frames[i].mbw;
+    return slots;
 }
 
 namespace {
@@ -59,18 +74,30 @@ __device__ __forceinline__ uint32_t ld_cg_u32(const void* p) { return __ldcg(rei
 __device__ __forceinline__ uint2 ld_cg_u64(const void* p) { return __ldcg(reinterpret_cast<const uint2*>(p)); }
 __device__ __forceinline__ uint4 ld_cg_u128(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 
-__device__ __forceinline__ int ld_acquire(const int* p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+// one unit of an edge record: {4 pixels, tag} read / written as ONE aligned 64-bit access
+__device__ __forceinline__ uint2 ld_edge(const uint2* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return make_uint2((uint32_t)v, (uint32_t)(v >> 32));
 }
-__device__ __forceinline__ int ld_relaxed(const int* p) {
-    int v;
-    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ void st_edge(uint2* p, uint32_t pixels, uint32_t tag) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"((unsigned long long)pixels | ((unsigned long long)tag << 32)) : "memory");
 }
-__device__ __forceinline__ void st_release(int* p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// `v` is what an earlier ld_edge(p) returned; poll until the producer's tag is there and return the pixels.
+// Watchdog: a wait that lasts absurdly long (a scheduling bug, never a data property) raises the abort
+// word; every waiter then stops waiting, the kernel drains with garbage pixels and the host reports an
+// error instead of hanging the device.
+__device__ __forceinline__ uint32_t wait_edge(const uint2* p, uint2 v, uint32_t tag, unsigned int* abort_word) {
+    unsigned spins = 0;
+    while (v.y != tag) {
+        __nanosleep(40);
+        v = ld_edge(p);
+        if ((++spins & 0x3ff) == 0) {
+            if (spins > (1u << 24)) atomicExch(abort_word, 1u);
+            if (*reinterpret_cast<volatile unsigned int*>(abort_word)) break;
+        }
+    }
+    return v.x;
 }
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
@@ -78,39 +105,6 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
-// Wait until the row above has finished `need` macroblocks.  `seen` caches the last value read.
-// Watchdog: a wait that lasts absurdly long (a scheduling bug, never a data property) raises the
-// abort word; every waiter sees it, the kernel drains and the host reports an error instead of
-// hanging the device.  Returns false when aborted.
-__device__ __forceinline__ bool wait_row(const int* prog, int need, int& seen, int lane, unsigned int* abort_word) {
-    if (seen >= need) return true;
-    if (lane == 0) {
-        // poll with relaxed loads (an acquire load would invalidate L1 on every spin), then one
-        // fence: it pairs with the fence inside the producer's release store
-        int v = ld_relaxed(prog);
-        unsigned spins = 0;
-        while (v < need) {
-            __nanosleep(100);
-            v = ld_relaxed(prog);
-            if ((++spins & 0x3ff) == 0) {
-                if (spins > (1u << 24)) atomicExch(abort_word, 1u);
-                if (*reinterpret_cast<volatile unsigned int*>(abort_word)) { v = -1; break; }
-            }
-        }
-        __threadfence();
-        seen = v;
-    }
-    seen = __shfl_sync(kFull, seen, 0);
-    __syncwarp();
-    return seen >= 0;
-}
-
-// Publish "macroblocks 0..done-1 of my row are finished": all lanes' global writes first.
-__device__ __forceinline__ void publish_row(int* prog, int done, int lane) {
-    __syncwarp();
-    if (lane == 0) st_release(prog, done);  // release = fence + store; the warp barrier orders the other lanes' writes before it
-}
 
 // ---------------------------------------------------------------------------------------------
 // B_PRED lookup table.  Every 4x4 sub-block predictor except B_DC is, per pixel, either
@@ -224,9 +218,9 @@ void bpred_table_eval(int mode, const uint8_t edge[13], uint8_t out[16]) {
     }
 }
 
-void upload_tables_once() {
+cudaError_t upload_tables_once() {
     static const BpredTable t = make_bpred_table();
-    cudaMemcpyToSymbol(c_bpred, &t, sizeof(t));
+    return cudaMemcpyToSymbol(c_bpred, &t, sizeof(t));
 }
 
 namespace {
@@ -331,12 +325,12 @@ struct PredictArgs {
     uint8_t* planes;
     unsigned int* ticket;
     unsigned int* abort_word;
-    int* progress;
+    uint2* edges;             // edge records, 8 units per slot (units 0-3 bottom luma row, 4-5 U, 6-7 V)
+    const uint32_t* recbase;  // row id -> first slot of that row
     const uint32_t* rowmap;
     const uint32_t* order;
     uint8_t* mbinfo;
     uint32_t total_rows;
-    int publish_every;  // progress is published every this many macroblocks (a power of two) and at the row end
 };
 
 #ifndef PREDICT_MIN_BLOCKS
@@ -373,12 +367,16 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
     uint32_t* yw32 = reinterpret_cast<uint32_t*>(S.yw);
     uint32_t* uw32 = reinterpret_cast<uint32_t*>(S.uw);
     uint32_t* vw32 = reinterpret_cast<uint32_t*>(S.vw);
-    // border roles, fixed per lane.  Lanes 0..11 each fetch one word of the row above: 0 = the word
-    // ending in the luma corner, 1..4 = the 16 pixels above, 5 = above-right, 6..8 = U (corner word,
-    // 8 pixels), 9..11 = V.  Every lane moves one byte of the right column to the left border.
-    const int trole = lane < 6 ? lane : (lane - 6) % 3;            // position inside its plane's group
-    const bool tcorner = lane < 12 && trole == 0;
-    uint32_t* const top_dst = lane < 6 ? yw32 + lane : lane < 9 ? uw32 + (lane - 6) : vw32 + (lane - 9);
+    // border roles, fixed per lane.  Lanes 0..7 each hold one 4-pixel unit of the edge record of the
+    // macroblock above: 0..3 = its bottom luma row, 4..5 = U, 6..7 = V; `top_dst` is where that unit goes
+    // in the workspace's top row.  Lanes 3, 5 and 7 hold the unit whose last byte is the corner of the
+    // NEXT macroblock (prediction.rs:30-33, 96-99).  Every lane moves one byte of the right column to
+    // the left border.
+    uint32_t* const top_dst = lane < 4 ? yw32 + 1 + lane : lane < 6 ? uw32 + (lane - 3) : vw32 + (lane - 5);
+    uint32_t* const corner_dst = lane == 3 ? yw32 : lane == 5 ? uw32 : vw32;
+    const bool corner_lane = lane == 3 || lane == 5 || lane == 7;
+    // ... and of the macroblock just finished: its bottom row, for the row below
+    const uint32_t* const bottom_src = lane < 4 ? yw32 + 16 * 8 + 1 + lane : lane < 6 ? uw32 + 8 * 4 + (lane - 3) : vw32 + 8 * 4 + (lane - 5);
     uint8_t* const lb_dst = lane < 16 ? S.yw + (1 + lane) * 32 + 3 : lane < 24 ? S.uw + (lane - 15) * 16 + 3 : S.vw + (lane - 23) * 16 + 3;
     const int lb_gap = lane < 16 ? 16 : 8;  // right column = left border + gap
 
@@ -396,14 +394,20 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         uint8_t* Y = A.planes + fd->y_off;
         uint8_t* U = A.planes + fd->u_off;
         uint8_t* V = A.planes + fd->v_off;
-        const int* prog_above = A.progress + rid - 1;
-        int* prog_mine = A.progress + rid;
-        int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
-        // where my border word of macroblock 0 lives in the row above, and what my pixels go to
-        const uint8_t* top_ptr = lane < 6 ? Y + (size_t)(mby * 16 - 1) * ystride + 4 * (lane - 1)
-                                          : (lane < 9 ? U : V) + (size_t)(mby * 8 - 1) * cstride + 4 * (trole - 1);
-        const int top_step = lane < 6 ? 16 : 8;
+        // edge records: mine (written for the row below, if there is one) and the row above's
+        const uint32_t tag_above = (uint32_t)mby, tag_mine = (uint32_t)mby + 1u;
+        const bool hand_down = mby + 1 < (int)fd->mbh;
+        uint2* const edge_mine = A.edges + (size_t)__ldg(A.recbase + rid) * 8 + (lane & 7);
+        const uint2* const edge_above = A.edges + (size_t)__ldg(A.recbase + (mby > 0 ? rid - 1 : rid)) * 8 + (lane & 7);
+        // cur = my unit of the record above macroblock mbx, nxt = of the one above mbx + 1 (as loaded: its tag
+        // is checked when it is needed), prev = of the one above mbx - 1
+        uint2 nxt = make_uint2(0u, 0u);
+        uint32_t cur = 0, prev = 0;
+        if (mby > 0 && lane < 8) {
+            cur = wait_edge(edge_above, ld_edge(edge_above), tag_above, A.abort_word);
+            if (mbw > 1) nxt = ld_edge(edge_above + 8);
+        }
         uint8_t* const yout = Y + (size_t)(mby * 16 + (lane >> 1)) * ystride + (lane & 1) * 8;
         uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
 
@@ -522,25 +526,35 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
             const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff;
             const uint32_t bpred_lo = mbw4.z, bpred_hi = mbw4.w;
 
-            // ---- neighbours: wait for the above-right macroblock, then build the borders ----
+            // ---- neighbours: the edge record of the above-right macroblock must be there, then build the borders ----
             // create_border_luma / create_border_chroma, prediction.rs:13-123
-            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
-            if (lane < 12) {
-                uint32_t w = 0x7f7f7f7fu;  // first macroblock row: 127 everywhere, corner included
-                if (mby > 0) {
-                    const bool last = mbx == mbw - 1;
-                    if (tcorner && mbx == 0) {
-                        w = 0x81818181u;  // no macroblock to the left: corner = 129
-                    } else {
-                        // above-right of the last macroblock: its own last pixel above, four times
-                        const uint32_t v = ld_cg_u32(top_ptr + (lane == 5 && last ? -4 : 0));
-                        w = lane == 5 && last ? (v >> 24) * 0x01010101u : v;
-                    }
+            if (mby == 0) {
+                // first macroblock row: 127 everywhere, corner and above-right included; constant along the row
+                if (mbx == 0 && lane < 12) {
+                    uint32_t* d = lane < 6 ? yw32 + lane : lane < 9 ? uw32 + (lane - 6) : vw32 + (lane - 9);
+                    *d = 0x7f7f7f7fu;
+                    if (lane == 5) { yw32[4 * 8 + 5] = 0x7f7f7f7fu; yw32[8 * 8 + 5] = 0x7f7f7f7fu; yw32[12 * 8 + 5] = 0x7f7f7f7fu; }
                 }
-                *top_dst = w;
-                if (lane == 5) { yw32[4 * 8 + 5] = w; yw32[8 * 8 + 5] = w; yw32[12 * 8 + 5] = w; }
+            } else {
+                const bool last = mbx == mbw - 1;
+                uint32_t nx = 0;
+                if (lane < 8) {
+                    if (!last) nx = wait_edge(edge_above + (size_t)(mbx + 1) * 8, nxt, tag_above, A.abort_word);
+                    *top_dst = cur;
+                    // corner: no macroblock to the left -> 129, else the last pixel above it
+                    if (corner_lane) *corner_dst = mbx == 0 ? 0x81818181u : prev;
+                    // above-right (luma only): the first 4 pixels above the next macroblock; for the last
+                    // macroblock its own last pixel above, four times (prediction.rs:35-38)
+                    if (lane == (last ? 3 : 0)) {
+                        const uint32_t w = last ? (cur >> 24) * 0x01010101u : nx;
+                        yw32[5] = w; yw32[4 * 8 + 5] = w; yw32[8 * 8 + 5] = w; yw32[12 * 8 + 5] = w;
+                    }
+                    prev = cur;
+                    cur = nx;
+                    // the unit after that, requested now and looked at in the next round
+                    if (mbx + 2 < mbw) nxt = ld_edge(edge_above + (size_t)(mbx + 2) * 8);
+                }
             }
-            top_ptr += top_step;
             if (mbx == 0) *lb_dst = 129;  // left border 129 (prediction.rs:54-57, 104-107)
             __syncwarp();
 
@@ -657,8 +671,9 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
             __syncwarp();
             // right column becomes the next macroblock's left border (mod.rs:700-704, 1309-1314)
             *lb_dst = lb_dst[lb_gap];
-            if (mbx + 1 == mbw || ((mbx + 1) & (A.publish_every - 1)) == 0) publish_row(prog_mine, mbx + 1, lane);
-            else __syncwarp();
+            // bottom row -> edge record for the row below (unfiltered pixels, as intra_predict needs them)
+            if (hand_down && lane < 8) st_edge(edge_mine + (size_t)mbx * 8, *bottom_src, tag_mine);
+            __syncwarp();
         }
     }
 }
@@ -731,8 +746,10 @@ __device__ __forceinline__ void lf_line(uint8_t* p, int st, int kind, int edge_l
 // (32-byte rows): the previous macroblock of the row on the left, the current one on the right.
 // Chroma: 12 rows, two 8-column panels (16-byte rows), per plane.  The previous panel is written
 // back (one 16-byte store per row) only after the current macroblock's left edge has been filtered,
-// then the current panel slides left.  The 4 top rows belong to the row above and are re-read
-// from L2 (they were written by the warp that owns that row).
+// then the current panel slides left.  The 4 top rows belong to the row above: they arrive through
+// that row's edge record (32 units: 16 luma, 8 U, 8 V; one per lane), are filtered here (top
+// macroblock edge) and written to the plane by this row; the bottom 4 rows of this row go the same
+// way to the row below instead of to the plane (the last row of a frame writes its own).
 struct __align__(16) FilterSmem {
     uint8_t y[20 * 32];
     uint8_t c[2][12 * 16];
@@ -745,12 +762,12 @@ struct FilterArgs {
     uint8_t* planes;
     unsigned int* ticket;
     unsigned int* abort_word;
-    int* progress;
+    uint2* edges;             // edge records, 32 units per slot
+    const uint32_t* recbase;  // row id -> first slot of that row
     const uint32_t* rowmap;
     const uint32_t* order;
     const uint8_t* mbinfo;
     uint32_t total_rows;
-    int publish_every;
 };
 
 #ifndef FILTER_MIN_BLOCKS
@@ -771,28 +788,39 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
         const uint32_t img = __ldg(A.rowmap + rid);
         const webpb200_frame_desc* fd = A.frames + img;
         const int frame_level = fd->filter_level;
-        if (frame_level == 0) {  // mod.rs:1195-1198: nothing is filtered in this frame
-            if (lane == 0) st_release(A.progress + rid, (int)fd->mbw);
-            continue;
-        }
+        if (frame_level == 0) continue;  // mod.rs:1195-1198: nothing is filtered in this frame (no row of it runs, none waits)
         const int mbw = fd->mbw;
         const int mby = (int)(rid - fd->row_base);
         const size_t ystride = (size_t)mbw * 16, cstride = (size_t)mbw * 8;
-        const int* prog_above = A.progress + rid - 1;
-        int* prog_mine = A.progress + rid;
-        int seen = 0;
         const size_t mb_row0 = (size_t)fd->mb_base + (size_t)mby * mbw;
         const bool simple = fd->filter_type != 0;
         const int sharp = fd->sharpness;
-        const int row_lo = mby > 0 ? 0 : 4;  // tile rows that exist in the plane
+        const int row_lo = mby > 0 ? 0 : 4;  // first tile row that exists
+        const bool hand_down = mby + 1 < (int)fd->mbh;  // my bottom 4 rows go to the row below, not to the plane
         // my row of the tile in the planes: lanes 0..19 luma rows, lanes 0..23 chroma (plane, row)
         uint8_t* const yrow = A.planes + fd->y_off + (size_t)(mby * 16 - 4 + lane) * ystride;
         const int cpl = lane >= 12, crow = lane - 12 * cpl;
         uint8_t* const crow_ptr = A.planes + (cpl ? fd->v_off : fd->u_off) + (size_t)(mby * 8 - 4 + crow) * cstride;
-        const bool ylane = lane < 20 && lane >= row_lo;
-        const bool clane = !simple && lane < 24 && crow >= row_lo;
+        const bool yown = lane >= 4 && lane < 20;                 // lanes that fetch this row's own pixels
+        const bool cown = !simple && lane < 24 && crow >= 4;
+        const bool clane = !simple && lane < 24;
         uint4* const ytile = reinterpret_cast<uint4*>(S.y + lane * 32);            // [0] previous, [1] current panel
         uint2* const ctile = reinterpret_cast<uint2*>(S.c[cpl] + crow * 16);
+        // edge records.  Consumer side: lane u takes unit u of the record above the current macroblock
+        // into the current panel (units 0..15: luma tile row u/4, word u%4; 16..23: U row, word; 24..31: V).
+        const uint32_t tag_above = (uint32_t)mby, tag_mine = (uint32_t)mby + 1u;
+        const bool up_lane = mby > 0 && (lane < 16 || !simple);
+        uint32_t* const up_dst = lane < 16 ? reinterpret_cast<uint32_t*>(S.y + (lane >> 2) * 32 + 16) + (lane & 3)
+                                           : reinterpret_cast<uint32_t*>(S.c[(lane - 16) >> 3] + (((lane - 16) & 7) >> 1) * 16 + 8) + (lane & 1);
+        const uint2* const edge_above = A.edges + (size_t)__ldg(A.recbase + (mby > 0 ? rid - 1 : rid)) * 32 + lane;
+        // Producer side: the lane that owns a bottom tile row writes that row's units itself (it holds them
+        // in registers for the write-back anyway): luma tile row 16 + r -> units 4r..4r+3, chroma tile row
+        // 8 + r of plane p -> units 16 + 8p + 2r, + 1.
+        uint2* const edge_mine = A.edges + (size_t)__ldg(A.recbase + rid) * 32;
+        uint2* const yedge = edge_mine + (lane - 16) * 4;
+        uint2* const cedge = edge_mine + 16 + cpl * 8 + (crow - 8) * 2;
+        uint2 upv = make_uint2(0u, 0u);
+        if (up_lane) upv = ld_edge(edge_above);
 
         // calculate_filter_parameters, mod.rs:1191-1217, once per row: the level of a macroblock
         // depends only on its segment and on whether it is B_PRED -> 2 x 4 bytes
@@ -813,30 +841,32 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
             lvl_bpred |= (uint32_t)min(max(lb, 0), 63) << (8 * sgi);
         }
 
-        // prefetch of macroblock x + 1: only when the row above is already far enough (it usually
-        // is); otherwise the next iteration loads synchronously after its wait
-        bool have_next = false;
-        uint2 cnext = make_uint2(0, 0);  // chroma of the next macroblock (8-byte cp.async would go through L1, which may be stale)
+        // This row's own pixels were written by k_predict (an earlier launch): macroblock x + 1 is always
+        // prefetched while x is filtered.  Chroma in registers (an 8-byte cp.async would go through L1).
+        uint2 cnext = make_uint2(0, 0);
         uint32_t mbword = __ldg(reinterpret_cast<const uint32_t*>(A.mbs + mb_row0));
         uint32_t mbnz = A.mbinfo[mb_row0];
 
         for (int mbx = 0; mbx < mbw; mbx++) {
-            if (mby > 0 && !wait_row(prog_above, min(mbx + 2, mbw), seen, lane, A.abort_word)) return;
-
-            // ---- the 16 new columns (rows -4..15) into the current panel ----
-            if (have_next) {
+            // ---- the 16 new columns into the current panel: rows 0..15 from the plane ... ----
+            if (mbx > 0) {
                 cp_async_wait_all();
-                if (ylane) ytile[1] = S.ynext[lane];
-                if (clane) ctile[1] = cnext;
+                if (yown) ytile[1] = S.ynext[lane];
+                if (cown) ctile[1] = cnext;
             } else {
-                if (ylane) ytile[1] = ld_cg_u128(yrow + (size_t)mbx * 16);
-                if (clane) ctile[1] = ld_cg_u64(crow_ptr + (size_t)mbx * 8);
+                if (yown) ytile[1] = ld_cg_u128(yrow);
+                if (cown) ctile[1] = ld_cg_u64(crow_ptr);
             }
-            have_next = mbx + 1 < mbw && (mby == 0 || seen >= min(mbx + 3, mbw));
-            if (have_next) {
-                if (ylane) cp_async16(&S.ynext[lane], yrow + (size_t)(mbx + 1) * 16);
-                if (clane) cnext = ld_cg_u64(crow_ptr + (size_t)(mbx + 1) * 8);
+            if (mbx + 1 < mbw) {
+                if (yown) cp_async16(&S.ynext[lane], yrow + (size_t)(mbx + 1) * 16);
+                if (cown) cnext = ld_cg_u64(crow_ptr + (size_t)(mbx + 1) * 8);
                 cp_async_commit();
+            }
+            // ---- ... rows -4..-1 from the edge record of the macroblock above (there once the row above
+            // has filtered the left edge of ITS next macroblock); the record after it is requested now ----
+            if (up_lane) {
+                *up_dst = wait_edge(edge_above + (size_t)mbx * 32, upv, tag_above, A.abort_word);
+                if (mbx + 1 < mbw) upv = ld_edge(edge_above + (size_t)(mbx + 1) * 32);
             }
 
             const int ymode = mbword & 0xff, segment = (mbword >> 16) & 3;
@@ -900,22 +930,50 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                 }
             }
 
-            // ---- the previous macroblock is final now: write it back, slide the current one left ----
+            // ---- the previous macroblock is final now: its rows go to the plane, or (bottom 4 rows, if a
+            // row below exists) into the edge record; then the current panel slides left ----
             const bool last = mbx == mbw - 1;
-            if (ylane) {
+            if (lane < 20) {
                 const uint4 cur = ytile[1];
-                if (mbx > 0) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16 - 16) = ytile[0];
-                if (last) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16) = cur;
+                if (lane >= row_lo) {
+                    const uint4 prv = ytile[0];
+                    if (lane < 16 || !hand_down) {
+                        if (mbx > 0) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16 - 16) = prv;
+                        if (last) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16) = cur;
+                    } else {
+                        if (mbx > 0) {
+                            uint2* r = yedge + (size_t)(mbx - 1) * 32;
+                            st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine); st_edge(r + 2, prv.z, tag_mine); st_edge(r + 3, prv.w, tag_mine);
+                        }
+                        if (last) {
+                            uint2* r = yedge + (size_t)mbx * 32;
+                            st_edge(r, cur.x, tag_mine); st_edge(r + 1, cur.y, tag_mine); st_edge(r + 2, cur.z, tag_mine); st_edge(r + 3, cur.w, tag_mine);
+                        }
+                    }
+                }
                 ytile[0] = cur;
             }
             if (clane) {
                 const uint2 cur = ctile[1];
-                if (mbx > 0) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8 - 8) = ctile[0];
-                if (last) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8) = cur;
+                if (crow >= row_lo) {
+                    const uint2 prv = ctile[0];
+                    if (crow < 8 || !hand_down) {
+                        if (mbx > 0) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8 - 8) = prv;
+                        if (last) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8) = cur;
+                    } else {
+                        if (mbx > 0) {
+                            uint2* r = cedge + (size_t)(mbx - 1) * 32;
+                            st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine);
+                        }
+                        if (last) {
+                            uint2* r = cedge + (size_t)mbx * 32;
+                            st_edge(r, cur.x, tag_mine); st_edge(r + 1, cur.y, tag_mine);
+                        }
+                    }
+                }
                 ctile[0] = cur;
             }
-            if (last || ((mbx + 1) & (A.publish_every - 1)) == 0) publish_row(prog_mine, mbx + 1, lane);
-            else __syncwarp();
+            __syncwarp();
         }
     }
 }
@@ -1349,36 +1407,36 @@ __global__ void k_composite(CompositeArgs a) {
     }
 }
 
-int blocks_for(const void* kernel, int threads, int sm_count) {
-    int per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
-    if (per_sm < 1) per_sm = 1;
-    return per_sm * sm_count;
+}  // namespace
+
+void wavefront_blocks_per_sm(int* predict_blocks, int* filter_blocks) {
+    int p = 0, f = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict), kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&f, reinterpret_cast<const void*>(k_loopfilter), kThreads, 0);
+    *predict_blocks = p < 1 ? 1 : p;
+    *filter_blocks = f < 1 ? 1 : f;
 }
 
-}  // namespace
+// grid of a persistent wavefront kernel: every block resident, no more blocks than rows to hand out
+static int wavefront_grid(const BatchDev& b, int blocks_per_sm) {
+    int grid = (blocks_per_sm > 0 ? blocks_per_sm : 1) * (b.sm_count > 0 ? b.sm_count : 1);
+    const int need = (int)((b.total_rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    if (grid > need) grid = need;
+    return grid < 1 ? 1 : grid;
+}
 
 cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     PredictArgs a;
     a.frames = b.frames; a.mbs = b.mbs; a.levels = b.levels; a.planes = b.planes;
     a.ticket = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off);
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
-    a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_pred_off);
+    a.edges = reinterpret_cast<uint2*>(b.scratch + b.lay.edge_pred_off);
+    a.recbase = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.recbase_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
-    // many images: the row above is usually long finished, so publish progress (a release fence each
-    // time) only every 4th macroblock; few images: rows really wait on each other, publish every one
-    a.publish_every = b.n_frames >= 64 ? 4 : 1;
-    if (const char* e = std::getenv("WEBPB200_PUB_P")) a.publish_every = std::atoi(e);
-    static int blocks = 0;
-    if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_predict), kThreads, b.sm_count);
-    int grid = blocks;
-    const int need = (int)((b.total_rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    if (grid > need) grid = need;
-    if (grid < 1) grid = 1;
-    k_predict<<<grid, kThreads, 0, s>>>(a);
+    k_predict<<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -1387,20 +1445,13 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.frames = b.frames; a.mbs = b.mbs; a.planes = b.planes;
     a.ticket = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 1;
     a.abort_word = reinterpret_cast<unsigned int*>(b.scratch + b.lay.tickets_off) + 2;
-    a.progress = reinterpret_cast<int*>(b.scratch + b.lay.progress_lf_off);
+    a.edges = reinterpret_cast<uint2*>(b.scratch + b.lay.edge_lf_off);
+    a.recbase = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.recbase_off);
     a.rowmap = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.rowmap_off);
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
-    a.publish_every = b.n_frames >= 64 ? 4 : 1;
-    if (const char* e = std::getenv("WEBPB200_PUB_F")) a.publish_every = std::atoi(e);
-    static int blocks = 0;
-    if (!blocks) blocks = blocks_for(reinterpret_cast<const void*>(k_loopfilter), kThreads, b.sm_count);
-    int grid = blocks;
-    const int need = (int)((b.total_rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
-    if (grid > need) grid = need;
-    if (grid < 1) grid = 1;
-    k_loopfilter<<<grid, kThreads, 0, s>>>(a);
+    k_loopfilter<<<wavefront_grid(b, b.filter_blocks), kThreads, 0, s>>>(a);
     return cudaGetLastError();
 }
 

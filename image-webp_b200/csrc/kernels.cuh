@@ -9,19 +9,31 @@
 
 namespace webpb200 {
 
-// Scratch words at the head of the scratch arena (must be zero before a reconstruct pass).
-//   [0] ticket counter of the prediction wavefront   [1] ticket counter of the loop filter
-//   [2] watchdog abort word (non-zero after a pass = a wavefront wait timed out)
-// followed by two int arrays of `total_rows` row-progress counters (prediction, loop filter),
-// indexed by row id = frame.row_base + macroblock row; then `total_rows` uint32 row id -> image,
-// then `total_rows` uint32 ticket -> row id (the order rows are handed out in: any order in which
-// row y of an image comes after its row y-1 is valid; across images, row-major is the fast one),
-// then one byte per macroblock (non_zero_dct).
+// Scratch arena of the wavefront kernels.
+//   words [0] ticket counter of the prediction wavefront, [1] of the loop filter, [2] watchdog abort
+//   word (non-zero after a pass = a wavefront wait timed out), [3] ticket counter of the gradient ALPH
+//   filter; then the EDGE RECORDS through which a macroblock row hands its bottom edge to the row
+//   below (see kernels.cu, "hand-off"); all of this must be zero before a pass (`zero_bytes`).
+// After it: `total_rows` uint32 row id -> image (row id = frame.row_base + macroblock row),
+// `total_rows` uint32 ticket -> row id (the order rows are handed out in: any order in which row y of
+// an image comes after its row y-1 is valid; across images, row-major is the fast one),
+// `total_rows` uint32 row id -> first edge-record slot of that row, then one byte per macroblock
+// (non_zero_dct).
+//
+// Edge-record slots: image i owns 2 * mbw_i consecutive slots starting at 2 * (sum of mbw of the
+// images before it); row y of the image uses the mbw slots of parity y & 1 (row y + 2 may overwrite
+// what row y wrote: by then row y + 1 has consumed it, because row y + 2 only gets to macroblock x
+// after row y + 1 has finished macroblock x + 1).
 struct ScratchLayout {
-    uint64_t tickets_off, progress_pred_off, progress_lf_off, rowmap_off, order_off, mbinfo_off, total;
+    uint64_t tickets_off, edge_pred_off, edge_lf_off, rowmap_off, order_off, recbase_off, mbinfo_off, total;
     uint64_t zero_bytes;  // prefix that must be cleared before every pass
 };
-ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs);
+constexpr uint64_t kEdgePredBytes = 64;   // per slot: 8 x {4 pixels, tag}: bottom luma row, bottom U row, bottom V row
+constexpr uint64_t kEdgeFilterBytes = 256;  // per slot: 32 x {4 pixels, tag}: bottom 4 luma rows, bottom 4 U rows, bottom 4 V rows
+// edge_slots = 2 * sum of mbw over the frames; with_filter = false leaves the loop filter's records out
+ScratchLayout scratch_layout(uint64_t total_rows, uint64_t total_mbs, uint64_t edge_slots, bool with_filter = true);
+// fills rowmap / order / recbase (each total_rows entries) for frames [0, n); returns edge_slots
+uint64_t edge_slots_of(const webpb200_frame_desc* frames, int n);
 
 struct BatchDev {
     const webpb200_frame_desc* frames;  // device
@@ -38,6 +50,7 @@ struct BatchDev {
     uint32_t order_first;   // ... whose tickets start at this index of the order array
     uint32_t max_w, max_h;  // largest frame of the batch (grid sizing)
     int sm_count;
+    int predict_blocks, filter_blocks;  // resident blocks per SM of the two wavefront kernels on this device (wavefront_blocks_per_sm)
     int q_first, q_end;     // k_yuv2rgb: row pairs [q_first, q_end) only; 0, 0 = every row
     // frames with an ALPH plane, grouped by filter method m: alpha_lists[m * n_frames + k]
     const int* alpha_lists;  // device
@@ -51,7 +64,9 @@ struct BatchDev {
 };
 inline uint64_t alpha_handoff_size(uint64_t alpha_bytes) { return ((alpha_bytes >> 3) + 511) & ~(uint64_t)255; }
 
-void upload_tables_once();  // prediction tables -> __constant__ (per device, call with it current)
+cudaError_t upload_tables_once();  // prediction tables -> __constant__ (per device, call with it current)
+// resident blocks per SM of k_predict / k_loopfilter on the current device (an occupancy query; once per context)
+void wavefront_blocks_per_sm(int* predict_blocks, int* filter_blocks);
 
 // dequant + IWHT/IDCT + intra prediction, row-per-warp macroblock wavefront
 cudaError_t launch_predict(const BatchDev& b, cudaStream_t s);

@@ -264,27 +264,35 @@ int webpb200_reconstruct_device(const webpb200_frame_desc* h_frames, const webpb
  * prediction into d_planes) for callers that must not allocate device memory: a process that
  * fixes its GPU memory budget at start-up, or one living inside another runtime's memory pool,
  * where a cudaMalloc would stall the device, dodge the pool's accounting or fail late.  The
- * wavefront's working memory (ticket counter, per-row progress counters, row map, per-macroblock
- * flags) lives in a fixed array inside the library instead of a caller-supplied scratch arena, and
- * this call performs no allocation of any kind.  The price:
- *   - every GPU that loads the library carries that array (about 0.35 MB) until the process exits;
- *   - a call may cover at most WEBPB200_STATIC_MAX_ROWS macroblock rows and
- *     WEBPB200_STATIC_MAX_MBS macroblocks (e.g. 256 images of 512x512); anything larger returns
- *     WEBPB200_ERR_STATIC_SCRATCH_LIMIT and does nothing -- split the batch;
+ * wavefront's working memory (ticket counter, the records through which a macroblock row hands its
+ * bottom edge to the row below, row map, per-macroblock flags) lives in a fixed array inside the
+ * library instead of a caller-supplied scratch arena, and this call performs no allocation of any
+ * kind.  The price:
+ *   - every GPU that loads the library carries that array (about 1.4 MB) until the process exits;
+ *   - a call may cover at most WEBPB200_STATIC_MAX_ROWS macroblock rows, WEBPB200_STATIC_MAX_MBS
+ *     macroblocks and WEBPB200_STATIC_MAX_WIDTH_MBS macroblock columns summed over its frames
+ *     (e.g. 256 images of 512x512); anything larger returns -WEBPB200_ERR_STATIC_SCRATCH_LIMIT and
+ *     does nothing -- split the batch;
  *   - all calls on one GPU share the array and it keeps the last call's contents; the call clears
- *     the counters it needs cleared, but two calls that overlap in time on the same GPU (two
- *     streams, two threads) race on it and produce garbage.  Serialise them;
+ *     what it needs cleared, but two calls that overlap in time on the same GPU (two streams, two
+ *     threads) race on it and produce garbage.  Serialise them;
  *   - the first call on each GPU resolves the array's device address (one-time set-up, with
  *     that GPU current).  Make that first call before you start any stream capture.
  * h_frames / d_frames: the same descriptors in host and device memory (offsets as for
- * webpb200_reconstruct_device); d_nonzero (optional, may be NULL): receives one byte per
- * macroblock, 1 where the loop filter must treat the macroblock as having coefficients
- * (MacroBlock::non_zero_dct).  Asynchronous on `stream` (a cudaStream_t passed as void*). */
+ * webpb200_reconstruct_device; every frame needs at least one macroblock); d_nonzero (optional, may
+ * be NULL): receives one byte per macroblock, 1 where the loop filter must treat the macroblock as
+ * having coefficients (MacroBlock::non_zero_dct).  Asynchronous on `stream` (a cudaStream_t passed
+ * as void*).  Returns 0 or a negative WEBPB200_ERR_*, like webpb200_reconstruct_device.
+ * webpb200_predict_device_static_check waits for `stream` and returns 0 if the last call on the
+ * current GPU ran to completion, -WEBPB200_ERR_CUDA if its wavefront gave up (overlapping calls) or
+ * the stream failed; it allocates nothing either. */
 #define WEBPB200_STATIC_MAX_ROWS 8192
 #define WEBPB200_STATIC_MAX_MBS 262144
+#define WEBPB200_STATIC_MAX_WIDTH_MBS 8192
 int webpb200_predict_device_static(const webpb200_frame_desc* h_frames, const webpb200_frame_desc* d_frames,
                                    int n, const webpb200_mb_desc* d_mbs, const int16_t* d_levels,
                                    uint8_t* d_planes, uint8_t* d_nonzero, void* stream);
+int webpb200_predict_device_static_check(void* stream);
 
 /* All frames of one animated lossy file, composited (extended.rs:30-129), as read_frame
  * would return them one after another: frames reconstruct as one batch, compositing runs

@@ -60,6 +60,8 @@ def _run_both(W, torch, frames, t, sizes, n_mbs):
     rc = W.lib().webpb200_predict_device_static(frames, t["frames"].data_ptr(), n, t["mbs"].data_ptr(), t["levels"].data_ptr(),
                                                 planes_b.data_ptr(), nonzero.data_ptr(), None)
     assert rc == 0
+    # the call only queues work: this waits for the stream and says whether the wavefront ran to its end
+    assert W.lib().webpb200_predict_device_static_check(None) == 0
     torch.cuda.synchronize()
     return planes_a.cpu().numpy(), planes_b.cpu().numpy(), nonzero.cpu().numpy()
 
@@ -101,7 +103,16 @@ def test_static_scratch_rejects_oversized_batches():
     frames[0].mbw, frames[0].mbh = 1024, 1024  # 1 Mi macroblocks: beyond WEBPB200_STATIC_MAX_MBS
     dummy = C.c_void_p(256)                     # never dereferenced: the size check comes first
     rc = W.lib().webpb200_predict_device_static(frames, dummy, 1, dummy, dummy, dummy, None, None)
-    assert rc == 102  # WEBPB200_ERR_STATIC_SCRATCH_LIMIT
+    assert rc == -102  # -WEBPB200_ERR_STATIC_SCRATCH_LIMIT (negative, like webpb200_reconstruct_device)
     frames[0].mbw, frames[0].mbh = 8, 8193      # too many macroblock rows
     rc = W.lib().webpb200_predict_device_static(frames, dummy, 1, dummy, dummy, dummy, None, None)
-    assert rc == 102
+    assert rc == -102
+    many = (W.FrameDesc * 9)()                  # 9 frames of 1024 macroblock columns: beyond WEBPB200_STATIC_MAX_WIDTH_MBS
+    for i in range(9):
+        many[i].width, many[i].height, many[i].mbw, many[i].mbh = 16383, 16, 1024, 1
+        many[i].row_base, many[i].mb_base = i, 1024 * i
+    rc = W.lib().webpb200_predict_device_static(many, dummy, 9, dummy, dummy, dummy, None, None)
+    assert rc == -102
+    frames[0].mbw, frames[0].mbh = 0, 4         # a frame without macroblocks is refused, not walked
+    rc = W.lib().webpb200_predict_device_static(frames, dummy, 1, dummy, dummy, dummy, None, None)
+    assert rc == -23  # -WEBPB200_ERR_INVALID_PARAM
