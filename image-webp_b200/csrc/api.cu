@@ -171,7 +171,7 @@ static_assert(sizeof(webpb200_frame_desc) == 136 && sizeof(webpb200_mb_desc) == 
 struct webpb200_ctx {
     int device = 0;
     int sm_count = 0;
-    int predict_blocks = 1, filter_blocks = 1;  // resident blocks per SM of the wavefront kernels on this device
+    int predict_blocks = 1, predict_blocks_latency = 1, filter_blocks = 1;  // resident blocks per SM of the wavefront kernels on this device
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;      // reconstruction of finished bands while k_entropy still runs
     unsigned int* h_rows = nullptr;      // mapped pinned: [frame * 8 + partition] rows finished (written by k_entropy)
@@ -322,6 +322,7 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
     bd.max_h = max_h;
     bd.sm_count = c->sm_count;
     bd.predict_blocks = c->predict_blocks;
+    bd.predict_blocks_latency = c->predict_blocks_latency;
     bd.filter_blocks = c->filter_blocks;
     bd.lay = scratch_layout(rows, mbs, edge_slots_of(frames, n));
     return 0;
@@ -617,7 +618,7 @@ extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
         return WEBPB200_ERR_CUDA;
     }
     upload_entropy_tables_once();
-    wavefront_blocks_per_sm(&c->predict_blocks, &c->filter_blocks);
+    wavefront_blocks_per_sm(&c->predict_blocks, &c->predict_blocks_latency, &c->filter_blocks);
     if (const char* e = std::getenv("WEBPB200_ENTROPY")) c->entropy_where = std::strcmp(e, "device") == 0 ? WEBPB200_ENTROPY_DEVICE : std::strcmp(e, "host") == 0 ? WEBPB200_ENTROPY_HOST : WEBPB200_ENTROPY_AUTO;
     if (cudaDeviceSynchronize() != cudaSuccess) {
         delete c;
@@ -1476,7 +1477,7 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     bd.frames = d_frames; bd.mbs = d_mbs; bd.levels = d_levels; bd.alpha = d_alpha;
     bd.planes = d_planes; bd.out = d_out; bd.scratch = scratch;
     bd.n_frames = n; bd.total_rows = (uint32_t)rows; bd.sm_count = c->sm_count;
-    bd.predict_blocks = c->predict_blocks; bd.filter_blocks = c->filter_blocks;
+    bd.predict_blocks = c->predict_blocks; bd.predict_blocks_latency = c->predict_blocks_latency; bd.filter_blocks = c->filter_blocks;
     bd.alpha_lists = reinterpret_cast<const int*>(scratch + bd.lay.total);
     if (alpha_end) {
         bd.alpha_handoff = reinterpret_cast<uint16_t*>(scratch + bd.lay.total + align256(16 * (uint64_t)n));

@@ -52,9 +52,30 @@ uint64_t edge_slots_of(const webpb200_frame_desc* frames, int n) {
     return slots;
 }
 
+#ifndef WF_SLEEP_NS
+#define WF_SLEEP_NS 40  // pause between two polls of an edge record
+#endif
+#ifdef WF_TRACE
+// Debug build only (tools/wf_trace.py): global-timer stamps (ns) of four consecutive macroblock rows of the
+// prediction wavefront.  [row - WF_TRACE][stamp 0 step start, 1 after the wait for the row above, 2 step end
+// (edge record written), 3 smid][mbx]
+__device__ long long g_wf_trace[4][4][1024];
+__device__ __forceinline__ long long wf_now() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define WF_STAMP(i, x) do { if (rid >= (uint32_t)(WF_TRACE) && rid < (uint32_t)(WF_TRACE) + 4 && lane == 0 && (x) < 1024) g_wf_trace[rid - (WF_TRACE)][i][x] = wf_now(); } while (0)
+#else
+#define WF_STAMP(i, x) do { } while (0)
+#endif
+
 namespace {
 
-constexpr int kWarpsPerBlock = 8;
+#ifndef BPRED_UNROLL
+#define BPRED_UNROLL 10  // 1 = the ten B_PRED steps as a rolled loop (less code to fetch)
+#endif
+constexpr int kBpredUnroll = BPRED_UNROLL;
+#ifndef WF_WARPS
+#define WF_WARPS 8
+#endif
+constexpr int kWarpsPerBlock = WF_WARPS;
 constexpr int kThreads = kWarpsPerBlock * 32;
 constexpr unsigned kFull = 0xffffffffu;
 
@@ -90,7 +111,9 @@ __device__ __forceinline__ void st_edge(uint2* p, uint32_t pixels, uint32_t tag)
 __device__ __forceinline__ uint32_t wait_edge(const uint2* p, uint2 v, uint32_t tag, unsigned int* abort_word) {
     unsigned spins = 0;
     while (v.y != tag) {
-        __nanosleep(40);
+#if WF_SLEEP_NS > 0
+        __nanosleep(WF_SLEEP_NS);
+#endif
         v = ld_edge(p);
         if ((++spins & 0x3ff) == 0) {
             if (spins > (1u << 24)) atomicExch(abort_word, 1u);
@@ -333,9 +356,11 @@ struct PredictArgs {
     uint32_t total_rows;
 };
 
-#ifndef PREDICT_MIN_BLOCKS
-#define PREDICT_MIN_BLOCKS 4
-#endif
+// Two builds of the same kernel.  kMinBlocks = 3 (80 registers, 24 warps per SM) is the fast one when the batch
+// keeps every resident warp busy (many images: issue-bound).  kMinBlocks = 2 (128 registers, 16 warps per SM)
+// has fewer instructions on each macroblock's dependency chain and is the fast one when the rows of a few
+// large frames wait on each other (latency-bound): cfg3 2.56 -> 1.85 ms, cfg2 0.93 -> 1.02 ms.
+constexpr int kPredictBlocksThroughput = 3, kPredictBlocksLatency = 2;
 
 // levels (800 B) + descriptor (16 B) of macroblocks `mbi` and (if `two`) `mbi + 1` -> the warp's staging
 // buffers, asynchronously
@@ -356,7 +381,8 @@ __device__ __forceinline__ void prefetch_pair(PredictSmem& S, const PredictArgs&
     cp_async_commit();
 }
 
-__global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(PredictArgs A) {
+template <int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A) {
     __shared__ PredictSmem smem[kWarpsPerBlock];
     __shared__ uint32_t s_bpred[160];
     for (int i = threadIdx.x; i < 160; i += kThreads) s_bpred[i] = c_bpred.w[i];
@@ -425,6 +451,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
         const int qcls = lane < 16 ? 0 : lane < 24 ? 1 : 2;
         uint4 desc_odd = make_uint4(0, 0, 0, 0);  // descriptor of the pair's second macroblock, kept for its turn
         for (int mbx = 0; mbx < mbw; mbx++) {
+            WF_STAMP(0, mbx);
             const size_t mbi = mb_row0 + mbx;
             uint4 mbw4 = desc_odd;
             if ((mbx & 1) == 0) {
@@ -555,6 +582,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                     if (mbx + 2 < mbw) nxt = ld_edge(edge_above + (size_t)(mbx + 2) * 8);
                 }
             }
+            WF_STAMP(1, mbx);
             if (mbx == 0) *lb_dst = 129;  // left border 129 (prediction.rs:54-57, 104-107)
             __syncwarp();
 
@@ -566,7 +594,7 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
                 const int pix = (p >> 2) * 32 + (p & 3);                            // my pixel inside a sub-block
                 const int dcoff = (p & 4) ? (p & 3) * 32 - 1 : (p & 3) - 32;       // the edge pixel I add up for B_DC
                 const unsigned long long bp = ((unsigned long long)bpred_hi << 32) | bpred_lo;
-#pragma unroll
+#pragma unroll kBpredUnroll
                 for (int s = 0; s < 10; s++) {
                     // steps with a single sub-block (0, 1, 8, 9): both half-warps compute it and store
                     // the same bytes, which keeps the step free of divergence
@@ -674,6 +702,10 @@ __global__ void __launch_bounds__(kThreads, PREDICT_MIN_BLOCKS) k_predict(Predic
             // bottom row -> edge record for the row below (unfiltered pixels, as intra_predict needs them)
             if (hand_down && lane < 8) st_edge(edge_mine + (size_t)mbx * 8, *bottom_src, tag_mine);
             __syncwarp();
+            WF_STAMP(2, mbx);
+#ifdef WF_TRACE
+            if (mbx == 0 && rid >= (uint32_t)(WF_TRACE) && rid < (uint32_t)(WF_TRACE) + 4 && lane == 0) { unsigned sm; asm volatile("mov.u32 %0, %smid;" : "=r"(sm)); g_wf_trace[rid - (WF_TRACE)][3][0] = sm; }
+#endif
         }
     }
 }
@@ -771,7 +803,7 @@ struct FilterArgs {
 };
 
 #ifndef FILTER_MIN_BLOCKS
-#define FILTER_MIN_BLOCKS 4
+#define FILTER_MIN_BLOCKS 3
 #endif
 
 __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(FilterArgs A) {
@@ -1409,11 +1441,13 @@ __global__ void k_composite(CompositeArgs a) {
 
 }  // namespace
 
-void wavefront_blocks_per_sm(int* predict_blocks, int* filter_blocks) {
-    int p = 0, f = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict), kThreads, 0);
+void wavefront_blocks_per_sm(int* predict_blocks, int* predict_blocks_latency, int* filter_blocks) {
+    int p = 0, l = 0, f = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict<kPredictBlocksThroughput>), kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&l, reinterpret_cast<const void*>(k_predict<kPredictBlocksLatency>), kThreads, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&f, reinterpret_cast<const void*>(k_loopfilter), kThreads, 0);
     *predict_blocks = p < 1 ? 1 : p;
+    *predict_blocks_latency = l < 1 ? 1 : l;
     *filter_blocks = f < 1 ? 1 : f;
 }
 
@@ -1436,7 +1470,11 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
-    k_predict<<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
+    // few rows for the machine (they wait on each other): the build with the shorter dependency chain
+    const int lat_blocks = b.predict_blocks_latency > 0 ? b.predict_blocks_latency : 1;
+    const bool latency_bound = b.predict_blocks_latency > 0 && (uint64_t)b.total_rows <= 2ull * lat_blocks * (b.sm_count > 0 ? b.sm_count : 1) * kWarpsPerBlock;
+    if (latency_bound) k_predict<kPredictBlocksLatency><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
+    else k_predict<kPredictBlocksThroughput><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -1510,6 +1548,12 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches) {
     }
     return cudaGetLastError();
 }
+
+#ifdef WF_TRACE
+extern "C" int webpb200_debug_wf_trace(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_wf_trace, sizeof(g_wf_trace));
+}
+#endif
 
 cudaError_t launch_composite(const CompositeArgs& a, cudaStream_t s) {
     dim3 grid((a.canvas_w + 255) / 256, a.canvas_h);

@@ -50,7 +50,7 @@ struct BatchDev {
     uint32_t order_first;   // ... whose tickets start at this index of the order array
     uint32_t max_w, max_h;  // largest frame of the batch (grid sizing)
     int sm_count;
-    int predict_blocks, filter_blocks;  // resident blocks per SM of the two wavefront kernels on this device (wavefront_blocks_per_sm)
+    int predict_blocks, predict_blocks_latency, filter_blocks;  // resident blocks per SM of the wavefront kernels on this device (wavefront_blocks_per_sm)
     int q_first, q_end;     // k_yuv2rgb: row pairs [q_first, q_end) only; 0, 0 = every row
     // frames with an ALPH plane, grouped by filter method m: alpha_lists[m * n_frames + k]
     const int* alpha_lists;  // device
@@ -66,7 +66,7 @@ inline uint64_t alpha_handoff_size(uint64_t alpha_bytes) { return ((alpha_bytes 
 
 cudaError_t upload_tables_once();  // prediction tables -> __constant__ (per device, call with it current)
 // resident blocks per SM of k_predict / k_loopfilter on the current device (an occupancy query; once per context)
-void wavefront_blocks_per_sm(int* predict_blocks, int* filter_blocks);
+void wavefront_blocks_per_sm(int* predict_blocks, int* predict_blocks_latency, int* filter_blocks);
 
 // dequant + IWHT/IDCT + intra prediction, row-per-warp macroblock wavefront
 cudaError_t launch_predict(const BatchDev& b, cudaStream_t s);

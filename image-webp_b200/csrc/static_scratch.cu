@@ -47,7 +47,7 @@ struct DeviceSlot {
     bool ready = false;
     unsigned char* scratch = nullptr;  // device address of g_wavefront_scratch on this GPU
     int sm_count = 0;
-    int predict_blocks = 1;
+    int predict_blocks = 1, predict_blocks_latency = 1;
 };
 DeviceSlot g_slots[64];
 std::mutex g_slots_mu;
@@ -91,7 +91,7 @@ int slot_for_current_device(DeviceSlot** out) {
             return WEBPB200_ERR_CUDA;
         }
         int filter_blocks = 0;
-        wavefront_blocks_per_sm(&s.predict_blocks, &filter_blocks);
+        wavefront_blocks_per_sm(&s.predict_blocks, &s.predict_blocks_latency, &filter_blocks);
         s.scratch = static_cast<unsigned char*>(p);
         s.ready = true;
     }
@@ -153,6 +153,7 @@ extern "C" int webpb200_predict_device_static(const webpb200_frame_desc* h_frame
     bd.total_rows = (uint32_t)rows;
     bd.sm_count = slot->sm_count;
     bd.predict_blocks = slot->predict_blocks;
+    bd.predict_blocks_latency = slot->predict_blocks_latency;
     if (launch_predict(bd, s) != cudaSuccess) return -WEBPB200_ERR_CUDA;
     if (d_nonzero && cudaMemcpyAsync(d_nonzero, slot->scratch + bd.lay.mbinfo_off, (size_t)mbs, cudaMemcpyDeviceToDevice, s) != cudaSuccess)
         return -WEBPB200_ERR_CUDA;
