@@ -100,8 +100,9 @@ def make_files(rank, per_gpu, threads):
     return S.make_batch(lambda i: S.cfg2_image(lo + i, WIDTH, HEIGHT), per_gpu, threads=threads)
 
 
-def cpu_baseline_run(files, threads, passes):
-    """Full CPU decode (entropy + reconstruction + RGB) with the oracle port, one image per thread."""
+def cpu_baseline_run(files, threads, passes, keep=None):
+    """Full CPU decode (entropy + reconstruction + RGB) with the oracle port, one image per thread.
+    keep: optional list that receives the decoded images of the last pass (the checker for the e2e outputs)."""
     from oracle import oracle as O
     O.build()
     t0 = time.perf_counter()
@@ -109,7 +110,126 @@ def cpu_baseline_run(files, threads, passes):
         outs, st, bad = O.decode_batch(files, threads=threads)
         assert bad == 0
     dt = time.perf_counter() - t0
+    if keep is not None:
+        keep.extend(outs)
     return len(files) * WIDTH * HEIGHT * passes / dt / 1e6, dt
+
+
+# ---- the other BASELINE configurations: one object each inside the main line ----------------
+# algorithmic bytes per macroblock / pixel of the whole pipeline: 800 B levels + 16 B descriptor in,
+# out_bpp bytes per visible pixel out, +1 byte per pixel of alpha residuals in for RGBA
+def pipeline_bytes(mbs, px, bpp):
+    return (800 + 16) * mbs + bpp * px + (px if bpp == 4 else 0)
+
+
+def measure_still_config(W, sh, dist, name, lo, hi, total, bpp, host_threads, device, check=True):
+    """Images [lo, hi) of configuration `name` on this rank: device-resident pass (CUDA events), end to end
+    through webpb200_decode_batch with pinned host buffers, and the CPU oracle on the same files -- timed, and
+    every output image compared with it.  Whole-job figures: sums over ranks, max of the times."""
+    from harness import configs
+    from oracle import oracle as O
+    files = configs.still_batch(name, lo, hi, threads=host_threads)
+    n = len(files)
+    bd = W.BatchDecoder(device)
+    status = bd.prepare(files, host_threads=host_threads)
+    assert all(s == 0 for s in status)
+    bd.upload()
+    bd.sync()
+    size = bd.size()
+    px, mbs = size["pixels"], size["macroblocks"]
+    bd.time(15, iters=3, flush_l2=False)
+    sh.barrier(dist)
+    ms, kernel_ms = bd.time(15, iters=5, flush_l2=False)
+    # end to end, host buffers both ways
+    sizes = [W.WebPDecoder(f).output_buffer_size() for f in files]
+    pin = W.PinnedBuffer(sum(sizes))
+    outs, at = [], 0
+    for sz in sizes:
+        outs.append(pin.array[at:at + sz])
+        at += sz
+    starts, tot = [], 0
+    for f in files:
+        starts.append(tot)
+        tot += (len(f) + 63) & ~63
+    pin_in = W.PinnedBuffer(tot)
+    pinned_files = []
+    for f, o in zip(files, starts):
+        pin_in.array[o:o + len(f)] = np.frombuffer(f, dtype=np.uint8)
+        pinned_files.append(pin_in.array[o:o + len(f)])
+    fl, ol = W.BufferList(pinned_files), W.BufferList(outs)
+    bd.decode(fl, outs=ol, host_threads=host_threads)
+    sh.barrier(dist)
+    t0 = time.perf_counter()
+    steps = 2
+    for _ in range(steps):
+        _, st = bd.decode(fl, outs=ol, host_threads=host_threads)
+    e2e_ms = 1e3 * (time.perf_counter() - t0) / steps
+    assert all(s == 0 for s in st)
+    h2d, d2h, where = bd.last_transfer()
+    # CPU oracle on the same files, chunk by chunk; every image of the e2e outputs compared
+    exact, cpu_s = 1.0, 0.0
+    if check:
+        for c0 in range(0, n, 64):
+            t1 = time.perf_counter()
+            want, wst, bad = O.decode_batch(files[c0:c0 + 64], threads=host_threads)
+            cpu_s += time.perf_counter() - t1
+            for k, wimg in enumerate(want):
+                if wst[k] != 0 or not np.array_equal(outs[c0 + k], wimg.reshape(-1)):
+                    exact = 0.0
+    pin.free()
+    pin_in.free()
+    bd.close()
+    tot_px, max_ms = sh.aggregate(dist, px, ms)
+    tot_mbs, max_e2e = sh.aggregate(dist, mbs, e2e_ms)
+    exact = sh.all_min(dist, exact)
+    peak, _ = measured_peak()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    gbs = pipeline_bytes(tot_mbs, tot_px, bpp) / (max_ms / 1e3) / 1e9
+    names = ["k_predict", "k_loopfilter", "k_yuv2rgb", "k_alpha"]
+    out = {"images": total, "images_this_rank": n, "MPix": tot_px / 1e6, "ms_per_pass": max_ms, "value": tot_px / (max_ms / 1e3) / 1e6, "unit": "MPix/s",
+           "kernel_ms": dict(zip(names, kernel_ms)),
+           "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak * world, "unit": "GB/s", "frac": gbs / (peak * world),
+                        "bytes_per_px": pipeline_bytes(tot_mbs, tot_px, bpp) / tot_px, "note": "SURVEY 8(d) pipeline bytes over the whole pass, aggregate over ranks"},
+           "e2e": {"value": tot_px / (max_e2e / 1e3) / 1e6, "unit": "MPix/s", "ms_per_step": max_e2e, "steps": steps,
+                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "entropy_stage": where},
+           "bit_exact": bool(exact) if check else None, "bit_exact_scope": "every image of every rank's shard vs the CPU oracle" if check else "not checked"}
+    if check and cpu_s > 0:
+        out["cpu_baseline"] = {"value": px / cpu_s / 1e6, "unit": "MPix/s", "cores": host_threads, "kind": "port",
+                               "sample": "rank 0's shard of %d images, full decode incl. entropy (%.1f s)" % (n, cpu_s)}
+    return out
+
+
+def measure_animation(W, name, n_frames, offsets, host_threads, device):
+    """cfg5 on this rank (compositing is sequential over frames: not sharded): all composited canvases through
+    webpb200_decode_animation into pinned host buffers, every one compared with the oracle's read_frame."""
+    from harness import configs
+    from oracle import oracle as O
+    data = configs.cfg5_animation(n_frames, offsets=offsets, threads=host_threads)
+    d = W.WebPDecoder(data)
+    w, h = d.dimensions()
+    per = w * h * 4
+    bd = W.BatchDecoder(device)
+    pin = W.PinnedBuffer(n_frames * per)
+    pouts = [pin.array[k * per:(k + 1) * per] for k in range(n_frames)]
+    bd.decode_animation(data, host_threads=host_threads, outs=pouts)
+    t0 = time.perf_counter()
+    bd.decode_animation(data, host_threads=host_threads, outs=pouts)
+    e2e = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    o = O.WebPDecoder(data)
+    exact = True
+    for k in range(n_frames):
+        want, _ = o.read_frame()
+        exact &= bool(np.array_equal(want.reshape(-1), pouts[k]))
+    cpu = time.perf_counter() - t1
+    px = n_frames * w * h
+    pin.free()
+    bd.close()
+    return {"frames": n_frames, "MPix": px / 1e6, "offset_frames": bool(offsets),
+            "e2e": {"value": px / e2e / 1e6, "unit": "MPix/s", "ms": 1e3 * e2e, "d2h_bytes": n_frames * per, "h2d_bytes": len(data)},
+            "cpu_baseline": {"value": px / cpu / 1e6, "unit": "MPix/s", "cores": 1, "kind": "port", "sample": "the whole animation, read_frame by read_frame (%.1f s)" % cpu},
+            "bit_exact": exact, "bit_exact_scope": "every composited canvas vs the CPU oracle",
+            "scaling": "not sharded: compositing is sequential over frames, rank 0 only"}
 
 
 def run_reference(args, rank, world):
@@ -145,6 +265,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--images", type=int, default=PER_GPU, help="images per GPU (default: the named config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--configs", default="cfg2u,cfg3,cfg4,cfg5",
+                    help="other BASELINE configurations measured into `other_configs` (comma list, or 'none')")
     args = ap.parse_args()
 
     sh = importlib.import_module("image-webp_b200.sharding")
@@ -223,7 +345,28 @@ def main():
     sh.barrier(dist)
     e2e_px, e2e_max_ms = sh.aggregate(dist, px, e2e_ms)
     e2e_value = e2e_px / (e2e_max_ms / 1e3) / 1e6
-    checksum = int(np.bitwise_xor.reduce(pin.array[: per * min(per_gpu, 16)].view(np.uint32)))
+    # ---- the other configurations: every rank takes part (cfg3 / cfg4 are split over the ranks) ----
+    other = {}
+    want_cfgs = [] if args.configs == "none" else [c.strip() for c in args.configs.split(",") if c.strip()]
+    if "cfg2u" in want_cfgs:
+        other["cfg2_uniform"] = dict(measure_still_config(W, sh, dist, "cfg2u", rank * 1024, (rank + 1) * 1024, 1024 * world, 3, host_threads, local_rank),
+                                     workload="1024 x 512x512 per GPU, 'uniform' mode profile (all modes equiprobable), simple filter, RGB", scaling="weak")
+    if "cfg3" in want_cfgs:
+        lo, hi = sh.shard_range(256, rank, world)
+        other["cfg3"] = dict(measure_still_config(W, sh, dist, "cfg3", lo, hi, 256, 3, host_threads, local_rank),
+                             workload="256 x 3840x2160 in all, split over the ranks by image index (sharding.shard_range); normal filter, 4 segments, LF deltas, sharpness 3, 8 DCT partitions, RGB",
+                             scaling="strong")
+    if "cfg4" in want_cfgs:
+        lo, hi = sh.shard_range(256, rank, world)
+        other["cfg4"] = dict(measure_still_config(W, sh, dist, "cfg4", lo, hi, 256, 4, host_threads, local_rank),
+                             workload="256 x 1920x1080 in all, split over the ranks; VP8X + ALPH (VP8L-compressed, alpha filter cycling 0..3, 16 distinct planes with every VP8L transform) + VP8 normal filter, RGBA",
+                             scaling="strong")
+    if "cfg5" in want_cfgs and rank == 0:
+        other["cfg5"] = dict(measure_animation(W, "cfg5", 120, False, host_threads, local_rank),
+                             workload="one animation, 120 ANMF frames 1920x1080 full canvas, ALPH + VP8 per frame, blend on, dispose alternating, RGBA canvases")
+        other["cfg5_offsets"] = dict(measure_animation(W, "cfg5", 24, True, host_threads, local_rank),
+                                     workload="the same with every 4th frame an offset sub-rectangle, 24 frames")
+    sh.barrier(dist)
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -238,7 +381,8 @@ def main():
             "vs_baseline": None, "dtype": "i32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "images_per_gpu": per_gpu, "stages": "dequant+IWHT/IDCT+intra-predict, loop filter, YUV->RGB",
                        "l2": "no flush: one pass touches ~%.1f GB, far more than the 126 MB L2" % ((size["in_bytes"] + 1.5 * px + out_bytes) / 1e9),
-                       "parallelism": "images sharded by index, no collective"},
+                       "parallelism": "images sharded by index, no collective",
+                       "timed_region": "one reconstruct pass incl. its clears of the ticket counters and edge records (first CUDA event precedes them)"},
             "kernel_ms": dict(zip(names, kernel_ms)),
             "roofline": {"bound": "hbm", "kernel": names[dominant], "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic_per_launch(names[dominant]), "peak_kind": peak_kind,
@@ -246,16 +390,22 @@ def main():
                          "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass"},
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
-                    "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads, "checksum": checksum,
+                    "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads,
                     "numa_bound_cpus": len(near) if near else None,
                     "images_left_on_device": {"ms_per_step": dev_out_ms, "value": px / (dev_out_ms / 1e3) / 1e6, "note": "rank 0, outs = NULL: no D2H"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
         if not args.no_cpu_baseline and world >= 1:
-            v, dt = cpu_baseline_run(files, cores, 2)
+            want = []
+            v, dt = cpu_baseline_run(files, cores, 2, keep=want)
             line["cpu_baseline"] = {"value": v, "unit": "MPix/s", "cores": cores, "kind": "port",
                                     "sample": "2 passes over the full batch of %d images, full decode incl. entropy (%.1f s)" % (per_gpu, dt)}
+            # the end-to-end outputs of the last timed step (still in the pinned buffer), every image against the oracle
+            line["e2e"]["bit_exact"] = bool(all(np.array_equal(outs[i], want[i].reshape(-1)) for i in range(per_gpu)))
+            line["e2e"]["bit_exact_scope"] = "all %d images of rank 0's last e2e step vs the CPU oracle" % per_gpu
+        if other:
+            line["other_configs"] = other
         print(json.dumps(line), flush=True)
     pin.free()
     bd.close()

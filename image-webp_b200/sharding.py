@@ -56,6 +56,17 @@ def aggregate(dist, units_local, ms_local):
     return float(t_units.item()), float(t_ms.item())
 
 
+def all_min(dist, value):
+    """Minimum of a per-rank number over all ranks (e.g. 1.0 / 0.0 for 'every rank's outputs were exact')."""
+    if dist is None:
+        return float(value)
+    import torch
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return float(t.item())
+
+
 def bind_near_gpu(pci_bus_id):
     """Pin this process to the CPUs of the NUMA node the GPU hangs off, so that its threads and the
     pinned buffers it allocates afterwards are local to the GPU's PCIe root (with 8 ranks on two sockets
