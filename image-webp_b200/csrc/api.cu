@@ -942,21 +942,13 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         const double est_host_us = (double)c->total_mbs * 3.0 / std::max(1, std::min(host_threads, n));
         if (est_device_us > est_host_us) return kPreferHostEntropy;
     }
-    if (c->alpha_bytes)
-        parallel_for(n, host_threads, [&](int i) {  // ALPH planes are host work in both modes
-            if (!c->items[i].status && frames[i].alpha_mode)
-                if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
-        });
     fill_row_order(frames, 0, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
-    finish_items(c);
     const double t_host = ms_since();
     if (trace) std::fprintf(stderr, "  host: containers %.2f, layout %.2f, headers %.2f, staging %.2f ms\n", t_items, t_layout, t_headers, t_host);
 
     if (trace) cudaEventRecord(c->ev[10], s);
     CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
     CU(c, cudaMemcpyAsync(c->d_ehdr.p, hdrs, sizeof(Vp8EntropyHdr) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D entropy headers");
-    if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
-    CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
     if (int r2 = upload_row_tables(c, c->h_aux.p, cudaMemcpyHostToDevice, s)) return r2;
     c->uploaded = true;
     c->last_entropy = WEBPB200_ENTROPY_DEVICE;
@@ -1025,6 +1017,19 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     // which frames ran out of bits is known only now; their pixels are not handed out
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
     CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
+    // ALPH planes (extended.rs:253-308; VP8L or raw) are host work in both entropy modes: here they are decoded
+    // on the host threads while k_entropy runs, then follow it on the stream together with the per-filter
+    // frame lists (the filter method is in the ALPH chunk header) and the descriptors they may have changed.
+    if (c->alpha_bytes) {
+        parallel_for(n, host_threads, [&](int i) {
+            if (!c->items[i].status && frames[i].alpha_mode)
+                if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
+        });
+        CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
+        CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+    }
+    finish_items(c);
+    CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
     if (nbands) {
         cudaStream_t r = c->stream2;
         CU(c, cudaEventRecord(c->ev[4], s), "event");  // k_entropy (and the status copy) finished
