@@ -108,8 +108,8 @@ def _u24(v):
     return struct.pack("<I", v)[:3]
 
 
-def vp8x_header(width, height, alpha=False, animation=False):
-    flags = (0x10 if alpha else 0) | (0x02 if animation else 0)
+def vp8x_header(width, height, alpha=False, animation=False, icc=False, exif=False, xmp=False):
+    flags = (0x10 if alpha else 0) | (0x02 if animation else 0) | (0x20 if icc else 0) | (0x08 if exif else 0) | (0x04 if xmp else 0)
     return chunk(b"VP8X", bytes([flags, 0, 0, 0]) + _u24(width - 1) + _u24(height - 1))
 
 
@@ -135,12 +135,18 @@ def alph_raw(alpha, filtering=0, preprocessing=0):
     return chunk(b"ALPH", bytes([info]) + res.tobytes())
 
 
-def webp_extended(vp8, width, height, alph_chunk=None):
-    """VP8X + [ALPH] + 'VP8 ' still image."""
-    parts = [vp8x_header(width, height, alpha=alph_chunk is not None)]
+def webp_extended(vp8, width, height, alph_chunk=None, icc=None, exif=None, xmp=None):
+    """VP8X + [ICCP] + [ALPH] + 'VP8 ' + [EXIF] + [XMP ] still image (metadata: raw payload bytes or None)."""
+    parts = [vp8x_header(width, height, alpha=alph_chunk is not None, icc=icc is not None, exif=exif is not None, xmp=xmp is not None)]
+    if icc is not None:
+        parts.append(chunk(b"ICCP", icc))
     if alph_chunk is not None:
         parts.append(alph_chunk)
     parts.append(chunk(b"VP8 ", vp8))
+    if exif is not None:
+        parts.append(chunk(b"EXIF", exif))
+    if xmp is not None:
+        parts.append(chunk(b"XMP ", xmp))
     return riff(parts)
 
 

@@ -87,7 +87,8 @@ SYMBOLS = [
     "webpb200_batch_time", "webpb200_batch_size", "webpb200_batch_get_planes", "webpb200_batch_get_packed",
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
-    "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
+    "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_open_with_options", "webpb200_set_memory_limit",
+    "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
     "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
 ]
 
@@ -122,6 +123,11 @@ def lib():
     L.webpb200_output_buffer_size.argtypes = [vp]; L.webpb200_output_buffer_size.restype = sz
     L.webpb200_set_background_color.argtypes = [vp, vp]
     L.webpb200_set_lossy_upsampling.argtypes = [vp, i32]
+    L.webpb200_open_with_options.argtypes = [vp, sz, vp, C.POINTER(vp)]
+    L.webpb200_set_memory_limit.argtypes = [vp, sz]
+    L.webpb200_background_color_hint.argtypes = [vp, vp]
+    for f in ("icc_profile", "exif_metadata", "xmp_metadata"):
+        getattr(L, "webpb200_" + f).argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     L.webpb200_read_image.argtypes = [vp, vp, sz]
     L.webpb200_read_frame.argtypes = [vp, vp, sz, C.POINTER(u32)]
     L.webpb200_vp8_decode_frame.argtypes = [vp, sz, C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), vp, vp, vp]
@@ -154,6 +160,7 @@ def lib():
     L.webpb200_workspace_sizes.argtypes = [vp, i32] + [C.POINTER(C.c_uint64)] * 3
     L.webpb200_reconstruct_device.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp, vp, C.c_uint, vp]
     L.webpb200_decode_animation.argtypes = [vp, vp, sz, pp, sz, C.POINTER(u32), i32, i32, i32]
+    L.webpb200_decode_animation_opts.argtypes = [vp, vp, sz, pp, sz, C.POINTER(u32), i32, vp, i32]
     L.webpb200_predict_device_static.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
     L.webpb200_predict_device_static_check.argtypes = [vp]
     _lib = L
@@ -208,14 +215,33 @@ def entropy_decode_resumed(data):
     return fd, mbs, levels
 
 
+class Options(C.Structure):
+    """webpb200_options: WebPDecodeOptions (decoder.rs:274-290) + background colour + memory limit."""
+    _fields_ = [("lossy_upsampling", C.c_int32), ("has_background_color", C.c_uint8), ("background_color", C.c_uint8 * 4),
+                ("pad", C.c_uint8 * 3), ("memory_limit", C.c_uint64)]
+
+
+def make_options(lossy_upsampling=BILINEAR, background_color=None, memory_limit=0):
+    o = Options()
+    o.lossy_upsampling = lossy_upsampling
+    if background_color is not None:
+        o.has_background_color = 1
+        o.background_color[:] = background_color
+    o.memory_limit = memory_limit
+    return o
+
+
 class WebPDecoder:
     """image_webp::WebPDecoder (decoder.rs:312-940) over the CUDA path."""
 
-    def __init__(self, data, lossy_upsampling=BILINEAR):
+    def __init__(self, data, lossy_upsampling=BILINEAR, options=None):
         """WebPDecoder::new / new_with_options (decoder.rs:336-363): container scan only."""
         self._data = _as_u8(data)
         h = C.c_void_p()
-        st = lib().webpb200_open(self._data.ctypes.data, self._data.size, lossy_upsampling, C.byref(h))
+        if options is not None:
+            st = lib().webpb200_open_with_options(self._data.ctypes.data, self._data.size, C.byref(options), C.byref(h))
+        else:
+            st = lib().webpb200_open(self._data.ctypes.data, self._data.size, lossy_upsampling, C.byref(h))
         if st:
             raise DecodingError(st)
         self._h = h
@@ -247,6 +273,26 @@ class WebPDecoder:
 
     def set_lossy_upsampling(self, method):
         lib().webpb200_set_lossy_upsampling(self._h, method)
+
+    def set_memory_limit(self, limit):
+        """decoder.rs:554"""
+        lib().webpb200_set_memory_limit(self._h, limit)
+
+    def background_color_hint(self):
+        """decoder.rs:559-565: the ANIM chunk's colour, None for a file that is not extended."""
+        c = (C.c_uint8 * 4)()
+        return None if lib().webpb200_background_color_hint(self._h, c) else tuple(c)
+
+    def _metadata(self, fn):
+        p, n = C.c_void_p(), C.c_size_t()
+        st = fn(self._h, C.byref(p), C.byref(n))
+        if st:
+            raise DecodingError(st)
+        return None if not p.value else C.string_at(p.value, n.value)
+
+    def icc_profile(self): return self._metadata(lib().webpb200_icc_profile)      # decoder.rs:643
+    def exif_metadata(self): return self._metadata(lib().webpb200_exif_metadata)  # decoder.rs:648
+    def xmp_metadata(self): return self._metadata(lib().webpb200_xmp_metadata)    # decoder.rs:653
 
     def _new_buf(self):
         w, h = self.dimensions()
@@ -493,9 +539,10 @@ class BatchDecoder:
     def launch_count(self):
         return lib().webpb200_launch_count(self._h)
 
-    def decode_animation(self, data, lossy_upsampling=BILINEAR, host_threads=0, outs=None):
+    def decode_animation(self, data, lossy_upsampling=BILINEAR, host_threads=0, outs=None, background_color=None):
         """All composited frames of an animated lossy file: (list of canvases, durations).
-        outs: optional list of num_frames uint8 arrays of output_buffer_size() bytes (e.g. pinned)."""
+        outs: optional list of num_frames uint8 arrays of output_buffer_size() bytes (e.g. pinned).
+        background_color: RGBA, as WebPDecoder.set_background_color before read_frame."""
         buf = _as_u8(data)
         d = WebPDecoder(buf)
         nf = d.num_frames()
@@ -503,7 +550,8 @@ class BatchDecoder:
             outs = [d._new_buf() for _ in range(nf)]
         op, _ = self._ptr_arrays(outs)
         dur = (C.c_uint32 * max(nf, 1))()
-        rc = lib().webpb200_decode_animation(self._h, buf.ctypes.data, buf.size, op, outs[0].size if outs else 0, dur, nf,
-                                             lossy_upsampling, host_threads or (os.cpu_count() or 1))
+        opt = make_options(lossy_upsampling, background_color)
+        rc = lib().webpb200_decode_animation_opts(self._h, buf.ctypes.data, buf.size, op, outs[0].size if outs else 0, dur, nf,
+                                                  C.byref(opt), host_threads or (os.cpu_count() or 1))
         self._check(rc)
         return outs, list(dur)[:nf]

@@ -1499,6 +1499,7 @@ struct webpb200_decoder {
     int upsampling = 0;
     bool has_bg = false;
     uint8_t bg[4] = {0, 0, 0, 0};
+    size_t memory_limit = ~size_t(0);  // decoder.rs:314, 354
     // AnimationState, decoder.rs:240-263
     uint32_t next_frame = 0;
     uint64_t next_frame_start = 0;
@@ -1520,6 +1521,19 @@ extern "C" int webpb200_open(const uint8_t* data, size_t len, int upsampling, we
     d->next_frame_start = d->ct.first_anmf;
     *out = d;
     return 0;
+}
+extern "C" int webpb200_open_with_options(const uint8_t* data, size_t len, const webpb200_options* opt, webpb200_decoder** out) {
+    int st = webpb200_open(data, len, opt ? opt->lossy_upsampling : 0, out);
+    if (st || !opt) return st;
+    if (opt->memory_limit) (*out)->memory_limit = (size_t)opt->memory_limit;
+    if (opt->has_background_color) {
+        st = webpb200_set_background_color(*out, opt->background_color);
+        if (st) {
+            webpb200_close(*out);
+            *out = nullptr;
+        }
+    }
+    return st;
 }
 extern "C" void webpb200_close(webpb200_decoder* d) {
     if (!d) return;
@@ -1544,6 +1558,29 @@ extern "C" int webpb200_set_background_color(webpb200_decoder* d, const uint8_t 
     return 0;
 }
 extern "C" void webpb200_set_lossy_upsampling(webpb200_decoder* d, int upsampling) { d->upsampling = upsampling; }
+extern "C" void webpb200_set_memory_limit(webpb200_decoder* d, size_t limit) { d->memory_limit = limit; }
+extern "C" int webpb200_background_color_hint(const webpb200_decoder* d, uint8_t rgba[4]) {
+    if (d->ct.kind != 2) return WEBPB200_ERR_INVALID_PARAM;
+    std::memcpy(rgba, d->ct.background_hint, 4);
+    return 0;
+}
+namespace {
+// read_chunk, decoder.rs:620-640: the range is handed out where it lies in the caller's buffer
+int metadata_chunk(webpb200_decoder* d, int kind, const uint8_t** data, size_t* len) {
+    *data = nullptr;
+    *len = 0;
+    const Range r = d->ct.chunks[kind];
+    if (!r.present) return 0;
+    if (r.size() > (uint64_t)d->memory_limit) return WEBPB200_ERR_MEMORY_LIMIT;
+    if (r.end > d->ct.len) return WEBPB200_ERR_IO;
+    *data = d->ct.data + r.start;
+    *len = (size_t)r.size();
+    return 0;
+}
+}  // namespace
+extern "C" int webpb200_icc_profile(webpb200_decoder* d, const uint8_t** data, size_t* len) { return metadata_chunk(d, CK_ICCP, data, len); }
+extern "C" int webpb200_exif_metadata(webpb200_decoder* d, const uint8_t** data, size_t* len) { return metadata_chunk(d, CK_EXIF, data, len); }
+extern "C" int webpb200_xmp_metadata(webpb200_decoder* d, const uint8_t** data, size_t* len) { return metadata_chunk(d, CK_XMP, data, len); }
 
 namespace {
 
@@ -1697,7 +1734,19 @@ extern "C" int webpb200_vp8_decode_frame(const uint8_t* vp8, size_t len, uint16_
 
 extern "C" int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs, size_t out_len,
                                          uint32_t* durations_ms, int max_frames, int upsampling, int host_threads) {
+    webpb200_options opt;
+    std::memset(&opt, 0, sizeof(opt));
+    opt.lossy_upsampling = upsampling;
+    return webpb200_decode_animation_opts(c, file, len, outs, out_len, durations_ms, max_frames, &opt, host_threads);
+}
+
+extern "C" int webpb200_decode_animation_opts(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs, size_t out_len,
+                                              uint32_t* durations_ms, int max_frames, const webpb200_options* opt, int host_threads) {
     if (!c) return -WEBPB200_ERR_NO_DEVICE;
+    const int upsampling = opt ? opt->lossy_upsampling : 0;
+    const bool has_bg = opt && opt->has_background_color;
+    uint8_t bg[4] = {0, 0, 0, 0};
+    if (has_bg) std::memcpy(bg, opt->background_color, 4);
     cudaSetDevice(c->device);
     Container ct;
     int st = parse_container(file, len, &ct);
@@ -1739,7 +1788,14 @@ extern "C" int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, s
     const size_t cbytes = (size_t)ct.width * ct.height * 4;
     CU(c, c->d_canvas.reserve(cbytes), "canvas");
     CU(c, c->d_frames_out.reserve(out_len * (size_t)nf), "canvas copies");
-    CU(c, cudaMemsetAsync(c->d_canvas.p, 0, cbytes, c->stream), "canvas clear");
+    if (has_bg) {  // decoder.rs:872-882: the canvas starts as the user's colour
+        std::vector<uint8_t> fill(cbytes);
+        for (size_t i = 0; i < cbytes; i += 4) std::memcpy(&fill[i], bg, 4);
+        CU(c, cudaMemcpyAsync(c->d_canvas.p, fill.data(), cbytes, cudaMemcpyHostToDevice, c->stream), "canvas fill");
+        CU(c, cudaStreamSynchronize(c->stream), "sync");  // `fill` goes away
+    } else {
+        CU(c, cudaMemsetAsync(c->d_canvas.p, 0, cbytes, c->stream), "canvas clear");
+    }
     const webpb200_frame_desc* hf = reinterpret_cast<const webpb200_frame_desc*>(c->h_frames.p);
     bool dispose_next = true;
     uint32_t pw = 0, ph = 0, px = 0, py = 0;
@@ -1753,7 +1809,10 @@ extern "C" int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, s
         a.fx = frs[f].x; a.fy = frs[f].y; a.fw = frs[f].w; a.fh = frs[f].h;
         a.px = px; a.py = py; a.pw = pw; a.ph = ph;
         a.frame_has_alpha = frs[f].alph.present;
-        a.has_clear = dispose_next && a.frame_has_alpha;
+        if (dispose_next) {  // decoder.rs:861-869
+            if (has_bg) { a.has_clear = 1; std::memcpy(a.clear, bg, 4); }
+            else if (a.frame_has_alpha) a.has_clear = 1;
+        }
         a.use_blend = frs[f].blend;
         a.out_bpp = out_bpp;
         CU(c, launch_composite(a, c->stream), "k_composite");

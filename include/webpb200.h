@@ -3,9 +3,13 @@
  * The reference (image-rs/image-webp v0.2.4) is a Rust crate with no FFI of its own; this
  * header is the C-ABI seam a Rust `extern "C"` block (or cgo / ctypes) binds to replace the
  * crate's lossy decode path.  Each entry point cites the reference item it stands in for.
- * Plain pointers and sizes only; no CUDA or torch types.  All functions return a status
- * (0 = ok, else a WEBPB200_ERR_* value mirroring DecodingError, decoder.rs:14-168) unless
- * stated otherwise.  The library has NO CPU fallback: without a CUDA device every decode
+ * Plain pointers and sizes only; no CUDA or torch types.  Return values, two conventions:
+ *   - the WebPDecoder surface (webpb200_open ... webpb200_vp8_decode_frame) and the host-only helpers
+ *     return 0 or a POSITIVE WEBPB200_ERR_* value mirroring DecodingError (decoder.rs:14-168);
+ *   - the batched and device-resident entry points (webpb200_decode_batch, webpb200_batch_*,
+ *     webpb200_decode_animation*, webpb200_reconstruct_device, webpb200_predict_device_static*) return
+ *     0 / a non-negative count on success and a NEGATIVE -WEBPB200_ERR_* on a call-level failure.
+ * Each declaration says which applies.  The library has NO CPU fallback: without a CUDA device every decode
  * call fails with WEBPB200_ERR_NO_DEVICE.
  */
 #ifndef WEBPB200_H
@@ -44,6 +48,7 @@ enum {
     WEBPB200_ERR_INVALID_PARAM = 23,     /* InvalidParameter                      */
     WEBPB200_ERR_NOMEM = 24,
     WEBPB200_ERR_NOT_LOSSY = 25,         /* VP8L still/animation frame: outside this library's path */
+    WEBPB200_ERR_MEMORY_LIMIT = 26,      /* MemoryLimitExceeded (decoder.rs:154)  */
     WEBPB200_ERR_NO_DEVICE = 100,        /* no usable CUDA device                 */
     WEBPB200_ERR_CUDA = 101,             /* a CUDA call failed (see webpb200_last_cuda_error) */
     WEBPB200_ERR_STATIC_SCRATCH_LIMIT = 102 /* batch too large for webpb200_predict_device_static */
@@ -110,8 +115,21 @@ typedef struct {
  * ------------------------------------------------------------------------------------- */
 typedef struct webpb200_decoder webpb200_decoder;
 
-/* WebPDecoder::new_with_options, decoder.rs:342-363 (container scan only, no pixel work) */
+/* WebPDecodeOptions (decoder.rs:274-290) plus the two per-decoder settings the crate offers as setters, so
+ * that one struct configures a decoder or a whole-animation call.  Zero-initialise for the defaults. */
+typedef struct {
+    int32_t lossy_upsampling;      /* WEBPB200_UPSAMPLING_*; default Bilinear                                  */
+    uint8_t has_background_color;  /* 1: use background_color as set_background_color would (decoder.rs:568)   */
+    uint8_t background_color[4];   /* RGBA                                                                      */
+    uint8_t pad[3];
+    uint64_t memory_limit;         /* set_memory_limit (decoder.rs:554); 0 = unlimited (the crate's usize::MAX) */
+} webpb200_options;                /* 24 bytes */
+
+/* WebPDecoder::new_with_options, decoder.rs:342-363 (container scan only, no pixel work).  Positive codes. */
 int webpb200_open(const uint8_t* data, size_t len, int upsampling, webpb200_decoder** out);
+/* the same with the full option set; a background colour on a file that is not an extended (VP8X) one is
+ * WEBPB200_ERR_INVALID_PARAM, as set_background_color would answer */
+int webpb200_open_with_options(const uint8_t* data, size_t len, const webpb200_options* opt, webpb200_decoder** out);
 void webpb200_close(webpb200_decoder* d);
 void webpb200_dimensions(const webpb200_decoder* d, uint32_t* w, uint32_t* h); /* decoder.rs:580 */
 int webpb200_has_alpha(const webpb200_decoder* d);        /* decoder.rs:586 */
@@ -123,6 +141,16 @@ uint64_t webpb200_loop_duration(const webpb200_decoder* d); /* decoder.rs:618 */
 size_t webpb200_output_buffer_size(const webpb200_decoder* d); /* decoder.rs:659-664 */
 int webpb200_set_background_color(webpb200_decoder* d, const uint8_t rgba[4]); /* decoder.rs:568 */
 void webpb200_set_lossy_upsampling(webpb200_decoder* d, int upsampling);       /* decoder.rs:938 */
+void webpb200_set_memory_limit(webpb200_decoder* d, size_t limit);             /* decoder.rs:554 */
+/* background_color_hint, decoder.rs:559-565: 0 and the ANIM chunk's colour, or WEBPB200_ERR_INVALID_PARAM
+ * where the crate returns None (not an extended file) */
+int webpb200_background_color_hint(const webpb200_decoder* d, uint8_t rgba[4]);
+/* icc_profile / exif_metadata / xmp_metadata, decoder.rs:643-655 (read_chunk 620-640): *data points into the
+ * caller's file buffer (borrowed, not copied), NULL when the file has no such chunk; a chunk larger than the
+ * memory limit is WEBPB200_ERR_MEMORY_LIMIT.  Positive codes. */
+int webpb200_icc_profile(webpb200_decoder* d, const uint8_t** data, size_t* len);
+int webpb200_exif_metadata(webpb200_decoder* d, const uint8_t** data, size_t* len);
+int webpb200_xmp_metadata(webpb200_decoder* d, const uint8_t** data, size_t* len);
 /* WebPDecoder::read_image, decoder.rs:669-741: tightly packed RGB8 / RGBA8 into buf;
  * len must equal output_buffer_size() else WEBPB200_ERR_IMAGE_TOO_LARGE. */
 int webpb200_read_image(webpb200_decoder* d, uint8_t* buf, size_t len);
@@ -300,6 +328,12 @@ int webpb200_predict_device_static_check(void* stream);
 int webpb200_decode_animation(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs,
                               size_t out_len, uint32_t* durations_ms, int max_frames, int upsampling,
                               int host_threads);
+/* The same with webpb200_options: the background colour is honoured exactly as read_frame does after
+ * set_background_color (initial canvas decoder.rs:872-882, clear colour 861-869).  Both return the number of
+ * frames written (>= 0) or a negative -WEBPB200_ERR_*. */
+int webpb200_decode_animation_opts(webpb200_ctx* c, const uint8_t* file, size_t len, uint8_t* const* outs,
+                                   size_t out_len, uint32_t* durations_ms, int max_frames,
+                                   const webpb200_options* opt, int host_threads);
 
 #ifdef __cplusplus
 }

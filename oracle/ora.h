@@ -46,7 +46,8 @@ enum {
     ORA_ERR_CHUNK_SIZE = 21,        /* InvalidChunkSize                     */
     ORA_ERR_NOT_ANIMATED = 22,      /* reference panics (decoder.rs:753)    */
     ORA_ERR_INVALID_PARAM = 23,     /* InvalidParameter                     */
-    ORA_ERR_NOMEM = 24
+    ORA_ERR_NOMEM = 24,
+    ORA_ERR_MEMORY_LIMIT = 26       /* MemoryLimitExceeded (decoder.rs:154)  */
 };
 
 /* ---- VP8 keyframe (lossy/mod.rs) ------------------------------------------------- */
@@ -159,6 +160,12 @@ uint32_t ora_loop_count(const ora_decoder*);     /* 0 = forever */
 uint64_t ora_loop_duration(const ora_decoder*);
 size_t ora_output_buffer_size(const ora_decoder*);
 int ora_set_background_color(ora_decoder*, const uint8_t color[4]);
+/* set_memory_limit decoder.rs:554; background_color_hint 559-565 (returns 0 and fills rgba, or
+ * ORA_ERR_INVALID_PARAM for "None"); icc_profile / exif_metadata / xmp_metadata 643-655 through read_chunk
+ * 620-640: *data = NULL when the chunk is absent, ORA_ERR_MEMORY_LIMIT when it is larger than the limit */
+void ora_set_memory_limit(ora_decoder*, size_t limit);
+int ora_background_color_hint(const ora_decoder*, uint8_t rgba[4]);
+int ora_metadata(ora_decoder*, int which /* 0 ICCP 1 EXIF 2 XMP */, const uint8_t** data, size_t* len);
 void ora_set_lossy_upsampling(ora_decoder*, int upsampling);
 int ora_read_image(ora_decoder*, uint8_t* buf, size_t len);
 int ora_read_frame(ora_decoder*, uint8_t* buf, size_t len, uint32_t* duration_ms);

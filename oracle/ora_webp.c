@@ -163,6 +163,7 @@ struct ora_decoder {
     uint32_t num_frames, loop_count; uint64_t loop_duration;
     range_t chunks[CK_N];
     int upsampling;           /* 0 bilinear 1 simple */
+    size_t memory_limit;      /* decoder.rs:314, usize::MAX by default (354) */
     /* AnimationState, decoder.rs:240-263 */
     uint32_t next_frame; uint64_t next_frame_start; int dispose_next_frame;
     uint32_t prev_w, prev_h, prev_x, prev_y;
@@ -292,6 +293,7 @@ int ora_open(const uint8_t* data, size_t len, int upsampling, ora_decoder** out)
     if (!d) return ORA_ERR_NOMEM;
     d->r = data; d->len = len; d->upsampling = upsampling;
     d->loop_count = 1; d->dispose_next_frame = 1;
+    d->memory_limit = (size_t)-1;
     int e = read_data(d);
     if (e) { free(d); *out = NULL; return e; }
     *out = d;
@@ -312,6 +314,23 @@ int ora_set_background_color(ora_decoder* d, const uint8_t c[4]) {
     return 0;
 }
 void ora_set_lossy_upsampling(ora_decoder* d, int u) { d->upsampling = u; }
+void ora_set_memory_limit(ora_decoder* d, size_t limit) { d->memory_limit = limit; } /* decoder.rs:554 */
+int ora_background_color_hint(const ora_decoder* d, uint8_t rgba[4]) { /* decoder.rs:559-565 */
+    if (d->kind != 2) return ORA_ERR_INVALID_PARAM;
+    memcpy(rgba, d->bg_hint, 4);
+    return 0;
+}
+/* read_chunk, decoder.rs:620-640, for ICCP / EXIF / XMP (643-655) */
+int ora_metadata(ora_decoder* d, int which, const uint8_t** data, size_t* len) {
+    const int kind = which == 0 ? CK_ICCP : which == 1 ? CK_EXIF : CK_XMP;
+    *data = NULL; *len = 0;
+    if (!d->chunks[kind].present) return 0;
+    range_t r = d->chunks[kind];
+    if (r.end - r.start > (uint64_t)d->memory_limit) return ORA_ERR_MEMORY_LIMIT;
+    if (r.end > d->len) return ORA_ERR_IO; /* read_exact past the end */
+    *data = d->r + r.start; *len = (size_t)(r.end - r.start);
+    return 0;
+}
 
 static int range_ok(const ora_decoder* d, range_t r) { return r.start <= r.end && r.end <= d->len; }
 

@@ -64,6 +64,9 @@ def lib():
         L.ora_loop_duration.argtypes = [C.c_void_p]; L.ora_loop_duration.restype = C.c_uint64
         L.ora_output_buffer_size.argtypes = [C.c_void_p]; L.ora_output_buffer_size.restype = C.c_size_t
         L.ora_set_background_color.argtypes = [C.c_void_p, C.c_void_p]
+        L.ora_set_memory_limit.argtypes = [C.c_void_p, C.c_size_t]
+        L.ora_background_color_hint.argtypes = [C.c_void_p, C.c_void_p]
+        L.ora_metadata.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
         L.ora_set_lossy_upsampling.argtypes = [C.c_void_p, C.c_int]
         L.ora_read_image.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.ora_read_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint32)]
@@ -149,6 +152,24 @@ class WebPDecoder:
 
     def set_lossy_upsampling(self, upsampling):
         lib().ora_set_lossy_upsampling(self._h, 0 if upsampling == "bilinear" else 1)
+
+    def set_memory_limit(self, limit):
+        lib().ora_set_memory_limit(self._h, limit)
+
+    def background_color_hint(self):
+        c = (C.c_uint8 * 4)()
+        return None if lib().ora_background_color_hint(self._h, c) else tuple(c)
+
+    def _metadata(self, which):
+        p, n = C.c_void_p(), C.c_size_t()
+        st = lib().ora_metadata(self._h, which, C.byref(p), C.byref(n))
+        if st:
+            raise OracleError(st)
+        return None if not p.value else C.string_at(p.value, n.value)
+
+    def icc_profile(self): return self._metadata(0)
+    def exif_metadata(self): return self._metadata(1)
+    def xmp_metadata(self): return self._metadata(2)
 
     def _shape(self):
         w, h = self.dimensions()

@@ -205,8 +205,14 @@ def test_synthetic_animation(W, bd, oracle, synth, alpha):
     o2, d2 = oracle.WebPDecoder(data), W.WebPDecoder(data)
     o2.set_background_color((10, 20, 30, 40))
     d2.set_background_color((10, 20, 30, 40))
+    want_bg = []
     for _ in specs:
-        assert np.array_equal(o2.read_frame()[0], d2.read_frame()[0])
+        want_bg.append(o2.read_frame()[0])
+        assert np.array_equal(want_bg[-1], d2.read_frame()[0])
+    # the same colour through webpb200_options on the whole-animation call
+    frames_bg, _ = bd.decode_animation(data, background_color=(10, 20, 30, 40))
+    for a, b in zip(want_bg, frames_bg):
+        assert np.array_equal(a, b)
 
 
 # ---- batch-scale properties ----------------------------------------------------------------------

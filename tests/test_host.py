@@ -189,3 +189,55 @@ def test_header_handover_on_synthetic_and_truncated(W, synth):
         assert sa == sb, cut
         if sa == 0:
             assert np.array_equal(ma, mb) and np.array_equal(la, lb), cut
+
+
+def test_metadata_memory_limit_and_options(W, oracle, synth, fixtures):
+    """icc_profile / exif_metadata / xmp_metadata (decoder.rs:643-655), set_memory_limit (554, enforced in
+    read_chunk 629), background_color_hint (559), new_with_options (342): product against the oracle."""
+    vp8 = synth.vp8_frame(48, 32, seed=5)
+    icc, exif, xmp = bytes(range(200)), b"Exif\0\0II*\0" + b"\x01" * 31, b"<x:xmpmeta/>"
+    files = [synth.webp_extended(vp8, 48, 32, icc=icc, exif=exif, xmp=xmp), synth.webp_extended(vp8, 48, 32, exif=exif),
+             synth.webp_simple(vp8), bytes(fixtures["webp/animated/random_lossy"]), bytes(fixtures["webp/gallery2/1_webp_a"])]
+    for data in files:
+        a, b = oracle.WebPDecoder(data), W.WebPDecoder(data)
+        assert a.background_color_hint() == b.background_color_hint()
+        for name in ("icc_profile", "exif_metadata", "xmp_metadata"):
+            assert getattr(a, name)() == getattr(b, name)(), name
+        for limit in (0, 30, 199, 200, 1 << 40):
+            a.set_memory_limit(limit)
+            b.set_memory_limit(limit)
+            for name in ("icc_profile", "exif_metadata", "xmp_metadata"):
+                try:
+                    x = getattr(a, name)()
+                except oracle.OracleError as e:
+                    x = ("error", e.code)
+                try:
+                    y = getattr(b, name)()
+                except W.DecodingError as e:
+                    y = ("error", e.code)
+                assert x == y, (name, limit)
+    got = W.WebPDecoder(files[0])
+    assert got.icc_profile() == icc and got.exif_metadata() == exif and got.xmp_metadata() == xmp
+    got.set_memory_limit(100)
+    with pytest.raises(W.DecodingError) as e:
+        got.icc_profile()
+    assert e.value.code == 26  # MemoryLimitExceeded
+    # options: memory limit and background colour through new_with_options; the colour only on extended files
+    d = W.WebPDecoder(files[0], options=W.make_options(memory_limit=100))
+    with pytest.raises(W.DecodingError):
+        d.icc_profile()
+    assert d.xmp_metadata() == xmp
+    with pytest.raises(W.DecodingError) as e:
+        W.WebPDecoder(files[2], options=W.make_options(background_color=(1, 2, 3, 4)))
+    assert e.value.code == 23  # InvalidParameter, as set_background_color answers (decoder.rs:568-577)
+    W.WebPDecoder(files[3], options=W.make_options(background_color=(1, 2, 3, 4)))
+    assert C.sizeof(W.Options) == 24
+
+
+def test_return_code_signs(W):
+    """The header's two conventions: decoder surface positive codes, batched / device-resident entry points negative."""
+    h = C.c_void_p()
+    junk = np.frombuffer(b"RIFX\0\0\0\0WEBP", np.uint8)
+    assert W.lib().webpb200_open(junk.ctypes.data, junk.size, 0, C.byref(h)) == 2          # positive: RIFF signature
+    assert W.lib().webpb200_decode_batch(None, None, None, 0, None, None, None, 0, 1) == -100  # negative: no context
+    assert W.lib().webpb200_decode_animation(None, None, 0, None, 0, None, 0, 0, 1) == -100
