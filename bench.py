@@ -58,6 +58,15 @@ def traffic_per_launch(kernel):
         return None
 
 
+def numa_note():
+    """Why sharding.bind_near_gpu did or did not bind: how many NUMA nodes the host exposes."""
+    try:
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        return "%d NUMA node(s) exposed%s" % (len(nodes), "" if len(nodes) > 1 else ": nothing to bind to")
+    except OSError:
+        return "no NUMA topology in sysfs"
+
+
 class ClockSampler:
     """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -336,6 +345,14 @@ def main():
     assert all(s == 0 for s in st)
     h2d_bytes, d2h_bytes, entropy_where = bd.last_transfer()
     entropy_ms = bd.last_entropy_ms()
+    # copy-only ceiling: the step's whole output arena device -> the same pinned buffers, all ranks at once
+    # (what the host's memory system gives N concurrent downloads; no kernel runs)
+    sh.barrier(dist)
+    t2 = time.perf_counter()
+    bd.download(outs)
+    d2h_only_ms = 1e3 * (time.perf_counter() - t2)
+    sh.barrier(dist)
+    _, d2h_ceiling_ms = sh.aggregate(dist, 0, d2h_only_ms)
     # for information: the same call with the images left in device memory (no download), as a GPU consumer would use it
     bd.decode_to_device(file_list, host_threads=host_threads)
     t1 = time.perf_counter()
@@ -391,7 +408,9 @@ def main():
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
                     "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": e2e_steps, "host_threads": host_threads,
-                    "numa_bound_cpus": len(near) if near else None,
+                    "numa_bound_cpus": len(near) if near else None, "numa_note": numa_note(),
+                    "d2h_ceiling_ms": d2h_ceiling_ms, "frac_of_d2h_ceiling": d2h_ceiling_ms / e2e_max_ms,
+                    "d2h_ceiling_note": "max over ranks of a copy-only pass: the same output bytes device -> the same pinned buffers, all ranks at the same time, no kernels",
                     "images_left_on_device": {"ms_per_step": dev_out_ms, "value": px / (dev_out_ms / 1e3) / 1e6, "note": "rank 0, outs = NULL: no D2H"}},
             "gpu_launches": int(launches),
             "clocks": clocks,

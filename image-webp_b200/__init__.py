@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_open_with_options", "webpb200_set_memory_limit",
-    "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
+    "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_decode_batch_multi", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
     "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
 ]
 
@@ -138,6 +138,7 @@ def lib():
     L.webpb200_host_free.argtypes = [vp]
     pp, ps, pi = C.POINTER(vp), C.POINTER(sz), C.POINTER(i32)
     L.webpb200_decode_batch.argtypes = [vp, pp, ps, i32, pp, ps, pi, i32, i32]
+    L.webpb200_decode_batch_multi.argtypes = [pp, i32, pp, ps, i32, pp, ps, pi, i32, i32, pi]
     L.webpb200_batch_prepare.argtypes = [vp, pp, ps, i32, pi, i32, i32]
     L.webpb200_batch_upload.argtypes = [vp]
     L.webpb200_batch_reconstruct.argtypes = [vp, C.c_uint]
@@ -386,6 +387,30 @@ class BufferList:
 
     def __len__(self):
         return len(self.bufs)
+
+
+def decode_batch_multi(decoders, files, outs=None, lossy_upsampling=BILINEAR, host_threads=0):
+    """One batch over several BatchDecoder contexts (one per GPU): webpb200_decode_batch_multi.
+    Returns (outs, status list, split) where split[k]..split[k+1] is the index range context k decoded."""
+    bufs = [_as_u8(f) for f in files]
+    n = len(bufs)
+    if outs is None:
+        outs = []
+        for b in bufs:
+            try:
+                outs.append(WebPDecoder(b)._new_buf())
+            except DecodingError:
+                outs.append(np.zeros(0, dtype=np.uint8))
+    fp, fl = BatchDecoder._ptr_arrays(bufs)
+    op, ol = BatchDecoder._ptr_arrays(outs)
+    status = (C.c_int * max(n, 1))()
+    split = (C.c_int * (len(decoders) + 1))()
+    ctxs = (C.c_void_p * len(decoders))(*[d._h for d in decoders])
+    rc = lib().webpb200_decode_batch_multi(ctxs, len(decoders), fp, fl, n, op, ol, status, lossy_upsampling,
+                                           host_threads or (os.cpu_count() or 1), split)
+    if rc < 0:
+        raise DecodingError(-rc)
+    return outs, list(status)[:n], list(split)
 
 
 class BatchDecoder:

@@ -1222,6 +1222,55 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     return decode_items(c, std::move(items), outs, out_lens, status, upsampling, host_threads);
 }
 
+// Several contexts (GPUs), one host thread each, contiguous ranges balanced by macroblock count.
+extern "C" int webpb200_decode_batch_multi(webpb200_ctx* const* ctxs, int n_ctx, const uint8_t* const* files, const size_t* lens, int n,
+                                           uint8_t* const* outs, const size_t* out_lens, int* status, int upsampling, int host_threads,
+                                           int* split) {
+    if (!ctxs || n_ctx < 1 || n < 0) return -WEBPB200_ERR_INVALID_PARAM;
+    for (int k = 0; k < n_ctx; k++)
+        if (!ctxs[k]) return -WEBPB200_ERR_NO_DEVICE;
+    // weights: macroblocks per file from the frame header (a bad file weighs nothing)
+    std::vector<uint64_t> prefix((size_t)n + 1, 0);
+    {
+        std::vector<uint64_t> w((size_t)n, 0);
+        parallel_for(n, host_threads, [&](int i) {
+            Container ct;
+            if (parse_container(files[i], lens[i], &ct) || ct.animated || !ct.chunks[CK_VP8].present) return;
+            const Range r = ct.chunks[CK_VP8];
+            Vp8Dims d{0, 0, 0, 0};
+            if (r.end <= lens[i] && !vp8_probe(files[i] + r.start, (size_t)r.size(), &d)) w[i] = (uint64_t)d.mbw * d.mbh;
+        });
+        for (int i = 0; i < n; i++) prefix[i + 1] = prefix[i] + w[i] + 1;  // +1: files without macroblocks still spread out
+    }
+    std::vector<int> cut((size_t)n_ctx + 1, n);
+    cut[0] = 0;
+    for (int k = 1; k < n_ctx; k++) {
+        const uint64_t target = prefix[n] * (uint64_t)k / (uint64_t)n_ctx;
+        cut[k] = (int)(std::lower_bound(prefix.begin(), prefix.end(), target) - prefix.begin());
+        cut[k] = std::max(cut[k], cut[k - 1]);
+    }
+    if (split)
+        for (int k = 0; k <= n_ctx; k++) split[k] = cut[k];
+    std::vector<int> rc((size_t)n_ctx, 0);
+    const int per = std::max(1, host_threads / n_ctx);
+    auto run = [&](int k) {
+        const int i0 = cut[k], m = cut[k + 1] - cut[k];
+        if (m <= 0) return;
+        rc[k] = webpb200_decode_batch(ctxs[k], files + i0, lens + i0, m, outs ? outs + i0 : nullptr, out_lens ? out_lens + i0 : nullptr,
+                                      status ? status + i0 : nullptr, upsampling, per);
+    };
+    std::vector<std::thread> th;
+    for (int k = 1; k < n_ctx; k++) th.emplace_back(run, k);
+    run(0);
+    for (auto& t : th) t.join();
+    int bad = 0;
+    for (int k = 0; k < n_ctx; k++) {
+        if (rc[k] < 0) return rc[k];
+        bad += rc[k];
+    }
+    return bad;
+}
+
 namespace {
 int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, uint8_t* const* outs, const size_t* out_lens, int* status,
                               int upsampling, int host_threads) {

@@ -223,6 +223,17 @@ int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const si
                           uint8_t* const* outs, const size_t* out_lens, int* status,
                           int upsampling, int host_threads);
 
+/* The batch split over several contexts (normally one per GPU of the box; SURVEY 8(e): images are
+ * independent, decoder.rs:312-331, so there is no exchange between the devices).  Files are dealt out as
+ * contiguous index ranges with about equal macroblock counts (sizes come from a header probe), each
+ * context runs webpb200_decode_batch on its range from its own host thread with host_threads / n_ctx
+ * worker threads, and outs / status are filled exactly as one webpb200_decode_batch over everything would
+ * fill them.  split (optional, n_ctx + 1 entries) receives the range boundaries.  Returns the number of
+ * failed files, or a negative -WEBPB200_ERR_* if any context failed at call level. */
+int webpb200_decode_batch_multi(webpb200_ctx* const* ctxs, int n_ctx, const uint8_t* const* files, const size_t* lens, int n,
+                                uint8_t* const* outs, const size_t* out_lens, int* status, int upsampling,
+                                int host_threads, int* split);
+
 /* The same in stages, so the device-resident part can be timed alone:
  *   prepare  = host side of decode_frame (header + per-macroblock entropy decode,
  *              lossy/mod.rs:510-671, 785-963) into pinned packed arrays

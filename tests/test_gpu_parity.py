@@ -275,3 +275,27 @@ def test_device_resident_seam(W, bd, oracle, synth):
         want = oracle.WebPDecoder(f).read_image()
         got = out[frames[i].out_off: frames[i].out_off + want.size].reshape(want.shape)
         assert np.array_equal(got, want)
+
+
+def test_batch_split_over_contexts(W, oracle, synth, fixtures):
+    """webpb200_decode_batch_multi: the batch dealt out over several contexts (one per GPU where the box has
+    several, else two contexts on the one device), ranges balanced by macroblock count; every image equals
+    the oracle's and a bad file keeps its own status."""
+    files = [synth.webp_simple(synth.vp8_frame(64 + 16 * (i % 9), 48 + 16 * (i % 5), seed=500 + i, filter_type=i % 2, filter_level=10 + i % 40,
+                                                 log2_parts=i % 3)) for i in range(40)]
+    files.append(synth.cfg3_image(7, 1280, 720))      # one heavy file: the split must not be by count
+    files.insert(5, bytes(fixtures["webp/gallery2/2_webp_a"]))
+    files.insert(11, b"RIFF\x10\0\0\0WEBPjunkjunkjunk")
+    ndev = max(1, min(W.device_count(), 4))
+    ctxs = [W.BatchDecoder(k % ndev) for k in range(max(2, ndev))]
+    outs, status, split = W.decode_batch_multi(ctxs, files, host_threads=8)
+    assert split[0] == 0 and split[-1] == len(files) and all(a <= b for a, b in zip(split, split[1:]))
+    assert split[1] > len(files) // 2   # the 720p frame at the end weighs as much as all the small ones
+    for i, f in enumerate(files):
+        if i == 11:
+            assert status[i] != 0
+            continue
+        assert status[i] == 0, i
+        assert np.array_equal(outs[i], oracle.WebPDecoder(f).read_image()), i
+    for c in ctxs:
+        c.close()
