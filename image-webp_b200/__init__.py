@@ -88,7 +88,7 @@ SYMBOLS = [
     "webpb200_launch_count", "webpb200_host_entropy_decode", "webpb200_debug_bpred_eval",
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_open_with_options", "webpb200_set_memory_limit",
-    "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_decode_batch_multi", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
+    "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_decode_batch_multi", "webpb200_decode_batch_begin", "webpb200_decode_batch_end", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
     "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
 ]
 
@@ -138,6 +138,8 @@ def lib():
     L.webpb200_host_free.argtypes = [vp]
     pp, ps, pi = C.POINTER(vp), C.POINTER(sz), C.POINTER(i32)
     L.webpb200_decode_batch.argtypes = [vp, pp, ps, i32, pp, ps, pi, i32, i32]
+    L.webpb200_decode_batch_begin.argtypes = [vp, pp, ps, i32, pp, ps, pi, i32, i32, C.POINTER(vp)]
+    L.webpb200_decode_batch_end.argtypes = [vp]
     L.webpb200_decode_batch_multi.argtypes = [pp, i32, pp, ps, i32, pp, ps, pi, i32, i32, pi]
     L.webpb200_batch_prepare.argtypes = [vp, pp, ps, i32, pi, i32, i32]
     L.webpb200_batch_upload.argtypes = [vp]
@@ -469,6 +471,22 @@ class BatchDecoder:
         status = (C.c_int * n)()
         self._check(lib().webpb200_decode_batch(self._h, fp, fl, n, op, ol, status, lossy_upsampling, host_threads or (os.cpu_count() or 1)))
         return outs, list(status)
+
+    def decode_begin(self, files, outs, lossy_upsampling=BILINEAR, host_threads=0):
+        """webpb200_decode_batch_begin: files / outs are BufferList objects (they must outlive decode_end).
+        Returns a handle for decode_end; one call in flight per BatchDecoder."""
+        n = len(files)
+        status = (C.c_int * max(n, 1))()
+        h = C.c_void_p()
+        self._check(lib().webpb200_decode_batch_begin(self._h, files.ptrs, files.lens, n, outs.ptrs, outs.lens, status, lossy_upsampling,
+                                                      host_threads or (os.cpu_count() or 1), C.byref(h)))
+        return (h, status, n, files, outs)
+
+    def decode_end(self, handle):
+        """webpb200_decode_batch_end: waits; returns the status list of the batch."""
+        h, status, n, _, _ = handle
+        self._check(lib().webpb200_decode_batch_end(h))
+        return list(status)[:n]
 
     # staged API (bench + tests)
     def prepare(self, files, lossy_upsampling=BILINEAR, host_threads=0):

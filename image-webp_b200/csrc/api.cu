@@ -180,6 +180,7 @@ struct webpb200_ctx {
     cudaEvent_t ev[12] = {};
     std::string err;
     uint64_t launches = 0;
+    std::atomic<bool> in_flight{false};  // a webpb200_decode_batch_begin has not been ended yet
 
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
     uint64_t last_h2d = 0, last_d2h = 0;  // bytes the last decode_batch copied each way
@@ -1220,6 +1221,35 @@ extern "C" int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* file
     std::vector<WorkItem> items;
     items_from_files(files, lens, n, host_threads, &items);
     return decode_items(c, std::move(items), outs, out_lens, status, upsampling, host_threads);
+}
+
+struct webpb200_pending {
+    std::thread worker;
+    int rc = 0;
+    webpb200_ctx* ctx = nullptr;
+};
+
+extern "C" int webpb200_decode_batch_begin(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n, uint8_t* const* outs,
+                                           const size_t* out_lens, int* status, int upsampling, int host_threads, webpb200_pending** pending) {
+    if (!pending) return -WEBPB200_ERR_INVALID_PARAM;
+    *pending = nullptr;
+    if (!c) return -WEBPB200_ERR_NO_DEVICE;
+    bool expected = false;
+    if (!c->in_flight.compare_exchange_strong(expected, true)) return -WEBPB200_ERR_INVALID_PARAM;  // one call in flight per context
+    webpb200_pending* p = new webpb200_pending();
+    p->ctx = c;
+    p->worker = std::thread([=]() { p->rc = webpb200_decode_batch(c, files, lens, n, outs, out_lens, status, upsampling, host_threads); });
+    *pending = p;
+    return 0;
+}
+
+extern "C" int webpb200_decode_batch_end(webpb200_pending* p) {
+    if (!p) return -WEBPB200_ERR_INVALID_PARAM;
+    p->worker.join();
+    const int rc = p->rc;
+    p->ctx->in_flight.store(false);
+    delete p;
+    return rc;
 }
 
 // Several contexts (GPUs), one host thread each, contiguous ranges balanced by macroblock count.

@@ -223,6 +223,20 @@ int webpb200_decode_batch(webpb200_ctx* c, const uint8_t* const* files, const si
                           uint8_t* const* outs, const size_t* out_lens, int* status,
                           int upsampling, int host_threads);
 
+/* webpb200_decode_batch without blocking the caller, so that two batches can be in flight on one GPU: the
+ * boolean-entropy kernel of a batch is one long dependency chain per frame and leaves about half of the
+ * GPU's issue slots idle, which the next batch's chains can use while this batch reconstructs and
+ * downloads.  _begin starts the call on a library thread and returns at once; _end waits for it and returns
+ * what webpb200_decode_batch would have (failed-file count, or a negative code).  Every argument array must
+ * stay valid until _end.  One call in flight per context: use two contexts on the device (each owns its
+ * streams and arenas) and alternate between them.  No counterpart in the reference (a WebPDecoder is
+ * synchronous); independent decoders on separate threads are its equivalent (decoder.rs:312-331). */
+typedef struct webpb200_pending webpb200_pending;
+int webpb200_decode_batch_begin(webpb200_ctx* c, const uint8_t* const* files, const size_t* lens, int n,
+                                uint8_t* const* outs, const size_t* out_lens, int* status,
+                                int upsampling, int host_threads, webpb200_pending** pending);
+int webpb200_decode_batch_end(webpb200_pending* pending);
+
 /* The batch split over several contexts (normally one per GPU of the box; SURVEY 8(e): images are
  * independent, decoder.rs:312-331, so there is no exchange between the devices).  Files are dealt out as
  * contiguous index ranges with about equal macroblock counts (sizes come from a header probe), each

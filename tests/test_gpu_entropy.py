@@ -279,3 +279,36 @@ def test_uniform_size_random_parameters_and_ragged_count(W, dev, host, synth):
                 assert np.array_equal(o_dev[i], o_host[i]), (parts, i)
         good = [i for i in range(n) if s_dev[i] == 0]
         _check_packed(W, dev, [files[i] for i in good[:3]], [0, 0, 0]) if good[:3] == [0, 1, 2] else None
+
+
+def test_two_batches_in_flight(W, synth, oracle):
+    """webpb200_decode_batch_begin / _end: two contexts on one device, batches alternating between them so that
+    two are always in flight; every image of every batch equals the oracle's, and a second begin on a busy
+    context is refused."""
+    n, w, h = 96, 256, 192
+    batches = [[synth.webp_simple(synth.vp8_frame(w, h, seed=7000 + 100 * b + i, filter_type=(b + i) % 2, filter_level=10 + i % 30))
+                for i in range(n)] for b in range(4)]
+    ctxs = [W.BatchDecoder(0), W.BatchDecoder(0)]
+    for c in ctxs:
+        c.set_entropy(c.ENTROPY_DEVICE)
+    per = w * h * 3
+    bufs = [_contiguous_outs(n, per)[1] for _ in range(4)]
+    lists = [(W.BufferList([np.frombuffer(f, np.uint8) for f in batches[b]]), W.BufferList(bufs[b])) for b in range(4)]
+    pending = [None, None]
+    for b in range(4):
+        k = b % 2
+        if pending[k] is not None:
+            assert ctxs[k].decode_end(pending[k]) == [0] * n
+        pending[k] = ctxs[k].decode_begin(lists[b][0], lists[b][1])
+        if b == 1:  # both busy now: a third begin on a busy context must be refused, not queued
+            with pytest.raises(W.DecodingError):
+                ctxs[k].decode_begin(lists[b][0], lists[b][1])
+    for k in range(2):
+        assert ctxs[k].decode_end(pending[k]) == [0] * n
+    for b in range(4):
+        want, st, bad = oracle.decode_batch(batches[b], threads=8)
+        assert bad == 0
+        for i in range(n):
+            assert np.array_equal(bufs[b][i], want[i].reshape(-1)), (b, i)
+    for c in ctxs:
+        c.close()
