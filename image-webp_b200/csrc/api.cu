@@ -929,6 +929,15 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     const double t_headers = ms_since();
     int max_parts = 1;
     for (int i = 0; i < n; i++) max_parts = std::max<int>(max_parts, hdrs[i].num_parts);
+    bool same_probs = true;  // no frame updates its token probabilities differently from the others (usually: none does at all)
+    {
+        int first = -1;
+        for (int i = 0; i < n && same_probs; i++) {
+            if (!hdrs[i].num_parts) continue;
+            if (first < 0) first = i;
+            else same_probs = std::memcmp(hdrs[i].probs, hdrs[first].probs, sizeof(hdrs[i].probs)) == 0;
+        }
+    }
     if (c->entropy_where == WEBPB200_ENTROPY_AUTO) {
         // The device decodes every partition of every frame at once but each one slowly (one lane,
         // about 33 us per macroblock on B200); the host decodes fast (about 3 us per macroblock)
@@ -1011,7 +1020,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
-                             reinterpret_cast<int*>(c->d_status.p), max_parts, nbands ? c->d_rows : nullptr, s), "k_entropy");
+                             reinterpret_cast<int*>(c->d_status.p), max_parts, same_probs, nbands ? c->d_rows : nullptr, s), "k_entropy");
         c->launches++;
     }
     cudaEventRecord(c->ev[6], s);

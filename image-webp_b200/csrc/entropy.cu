@@ -285,6 +285,7 @@ struct EntropyArgs {
     int max_mbw;
     int n_frames;
     int frames_per_block;
+    int shared_probs;  // every frame of the launch carries the same token probabilities: one table per block instead of one per frame
     unsigned int* rows_done;  // host-mapped, [frame * 8 + partition] = macroblock rows that partition has finished; or null
 };
 
@@ -295,8 +296,9 @@ struct EntropyCtl {
     uint32_t lut[17]; // coefficient n -> byte offset of band(n)'s context-0 row | zigzag(n) * 2 << 16  (ENT_LUT)
 };
 constexpr int kCtlBytes = 128;
-__host__ __device__ inline size_t entropy_smem_per_frame(int max_parts, int max_mbw) {
-    return (kProbBytes + kCtlBytes + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw + 15) & ~(size_t)15;
+// per frame: [TokenProb[1056] unless the block shares one table] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
+__host__ __device__ inline size_t entropy_smem_per_frame(int max_parts, int max_mbw, bool own_probs) {
+    return ((own_probs ? kProbBytes : 0) + kCtlBytes + 4 * (size_t)max_mbw + 2 * (size_t)(max_parts + 1) * (size_t)max_mbw + 15) & ~(size_t)15;
 }
 
 // spin on a shared-memory word until it reaches `need` or the frame is aborted
@@ -329,36 +331,49 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     const int warp_all = threadIdx.x >> 5;
     const int slot = F == 1 ? 0 : (warp_all & 3);             // which of the block's frames this warp serves
     const int warp = F == 1 ? warp_all : (warp_all < 4 ? 1 : 0);  // role: 0 = modes, 1.. = token partition + 1
-    const size_t per_frame = entropy_smem_per_frame(A.max_parts, A.max_mbw);
+    // Batches whose frames all carry the same token probabilities (no probability updates: the usual case)
+    // keep ONE table per block: 17 KB instead of 68 KB of shared memory for four frames, so that twice as many
+    // blocks fit an SM and the chains of a second batch can run beside the first one's.
+    const bool own = !A.shared_probs;
+    const size_t per_frame = entropy_smem_per_frame(A.max_parts, A.max_mbw, own);
+    const size_t frames_at = own ? 0 : kProbBytes;
+    const size_t ctl_at = own ? kProbBytes : 0;  // offset of EntropyCtl inside a frame's region
+
+    // which of the block's frames the shared table is filled from: the first one the host did not drop
+    // (a dropped frame's header is all zero)
+    int table_from = 0;
+    if (!own)
+        for (int sl = F - 1; sl >= 0; sl--)
+            if (blockIdx.x * F + sl < A.n_frames && A.hdrs[A.frame_first + blockIdx.x * F + sl].num_parts) table_from = sl;
 
     // shared tables of all the block's frames, filled by the whole block
     for (int sl = 0; sl < F; sl++) {
         const int fi = blockIdx.x * F + sl;
         if (fi >= A.n_frames) break;
-        uint8_t* sm = smem_all + sl * per_frame;
+        uint8_t* sm = smem_all + frames_at + sl * per_frame;
         const Vp8EntropyHdr& Hs = A.hdrs[A.frame_first + fi];
-        TokenProb* pr = reinterpret_cast<TokenProb*>(sm);
-        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(sm + kProbBytes);
-        uint32_t* tb = reinterpret_cast<uint32_t*>(sm + kProbBytes + kCtlBytes);
-        for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) pr[i] = make_token_prob(Hs.probs[i]);
+        TokenProb* pr = reinterpret_cast<TokenProb*>(own ? sm : smem_all);
+        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(sm + ctl_at);
+        uint32_t* tb = reinterpret_cast<uint32_t*>(sm + ctl_at + kCtlBytes);
+        if (own || sl == table_from)
+            for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) pr[i] = make_token_prob(Hs.probs[i]);
         for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(cs)[i] = 0;
         for (int i = threadIdx.x; i < A.max_mbw; i += blockDim.x) tb[i] = 0;
     }
     __syncthreads();
     for (int sl = 0; sl < F; sl++) {
-        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(smem_all + sl * per_frame + kProbBytes);
+        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(smem_all + frames_at + sl * per_frame + ctl_at);
         if (threadIdx.x < 17) cs->lut[threadIdx.x] = band_of(threadIdx.x) * 33u * (uint32_t)sizeof(TokenProb) | (zigzag_of(threadIdx.x & 15) * 2u) << 16;
     }
     __syncthreads();
 
     const int fi = blockIdx.x * F + slot;
     if ((threadIdx.x & 31) != 0 || fi >= A.n_frames) return;  // one working lane per partition
-    uint8_t* smem = smem_all + slot * per_frame;
-    // layout per frame: TokenProb[1056] | EntropyCtl | top_bpred u32[max_mbw] | top_nz u16[(P+1)][max_mbw]
-    TokenProb* s_probs = reinterpret_cast<TokenProb*>(smem);
-    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + kProbBytes);
-    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + kProbBytes + kCtlBytes);
-    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + kProbBytes + kCtlBytes + 4 * (size_t)A.max_mbw);
+    uint8_t* smem = smem_all + frames_at + slot * per_frame;
+    TokenProb* s_probs = reinterpret_cast<TokenProb*>(own ? smem : smem_all);
+    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + ctl_at);
+    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + ctl_at + kCtlBytes);
+    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + ctl_at + kCtlBytes + 4 * (size_t)A.max_mbw);
 
     const int f = A.frame_first + fi;
     const Vp8EntropyHdr& H = A.hdrs[f];
@@ -556,7 +571,7 @@ void upload_entropy_tables_once() {
 }
 
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, unsigned int* rows_done, cudaStream_t s) {
+                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, cudaStream_t s) {
     if (b.n_frames <= 0) return cudaSuccess;
     EntropyArgs a;
     a.frames = b.frames; a.hdrs = d_hdrs; a.bits = d_bits; a.mbs = d_mbs; a.levels = d_levels; a.status = d_status;
@@ -566,7 +581,8 @@ cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const
     a.n_frames = b.n_frames;
     a.frames_per_block = max_parts == 1 && b.n_frames >= 8 ? 4 : 1;
     a.rows_done = rows_done;
-    const size_t smem = entropy_smem_per_frame(max_parts, a.max_mbw) * (size_t)a.frames_per_block;
+    a.shared_probs = same_probs ? 1 : 0;
+    const size_t smem = entropy_smem_per_frame(max_parts, a.max_mbw, !same_probs) * (size_t)a.frames_per_block + (same_probs ? kProbBytes : 0);
     static_assert(sizeof(EntropyCtl) <= kCtlBytes, "EntropyCtl outgrew its slot");
     if (smem > 48 * 1024) {  // per device and function: cheap enough to repeat
         cudaError_t e = cudaFuncSetAttribute(k_entropy, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -81,11 +81,12 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches);
 // [b.frame_first, +b.n_frames) from the staged bitstreams into d_mbs / d_levels (both cleared by
 // the caller); d_status[frame] is set to WEBPB200_ERR_BITSTREAM for a frame that ran out of bits
 void upload_entropy_tables_once();
+// same_probs: every frame of the launch has the same token probabilities (one shared-memory table per block);
 // rows_done (may be null): host-mapped array, [frame * 8 + partition] = number of macroblock rows that
 // token partition has finished (plain store after a system-scope fence), so the host can start
 // reconstructing the top of the frames while the bottom is still being decoded
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, unsigned int* rows_done, cudaStream_t s);
+                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, cudaStream_t s);
 
 struct CompositeArgs {  // one composite_frame call, reference extended.rs:30-129
     uint8_t* canvas;       // canvas_w * canvas_h * 4, device
