@@ -699,9 +699,32 @@ extern "C" int webpb200_batch_download_packed(webpb200_ctx* c, int image, webpb2
     CU(c, cudaStreamSynchronize(c->stream), "sync");
     if (m == 0) return 0;
     if (mbs) CU(c, cudaMemcpy(mbs, c->d_mbs.p + sizeof(webpb200_mb_desc) * (size_t)fd.mb_base, sizeof(webpb200_mb_desc) * m, cudaMemcpyDeviceToHost), "D2H mbs");
-    if (levels)
+    if (levels) {
         CU(c, cudaMemcpy(levels, c->d_levels.p + sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)fd.mb_base,
                          sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * m, cudaMemcpyDeviceToHost), "D2H levels");
+        if (c->bd.levels_packed) {
+            // k_entropy's packed records -> the dense boundary format the caller expects: slots in decode order
+            // (Y2 first, then blocks 0..23) for the blocks whose nflags bit is set, everything else zero
+            std::vector<webpb200_mb_desc> tmp;
+            const webpb200_mb_desc* d = mbs;
+            if (!d) {
+                tmp.resize(m);
+                CU(c, cudaMemcpy(tmp.data(), c->d_mbs.p + sizeof(webpb200_mb_desc) * (size_t)fd.mb_base, sizeof(webpb200_mb_desc) * m, cudaMemcpyDeviceToHost), "D2H mbs");
+                d = tmp.data();
+            }
+            int16_t packed[WEBPB200_LEVELS_PER_MB];
+            for (size_t i = 0; i < m; i++) {
+                int16_t* rec = levels + i * WEBPB200_LEVELS_PER_MB;
+                std::memcpy(packed, rec, sizeof(packed));
+                std::memset(rec, 0, sizeof(packed));
+                int slot = 0;
+                for (int k = -1; k < 24; k++) {
+                    const int blk = k < 0 ? 24 : k;
+                    if ((d[i].nflags >> blk) & 1u) std::memcpy(rec + blk * 16, packed + 16 * slot++, 32);
+                }
+            }
+        }
+    }
     return 0;
 }
 
@@ -869,8 +892,9 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     // clear the outputs of the entropy stage while the host parses headers
     if (trace) cudaEventRecord(c->ev[8], s);
     if (c->total_mbs) {
+        // descriptors only: the levels are written packed (a block that carries tokens clears its own slot,
+        // the others are never touched), so the 800 bytes per macroblock need no clearing
         CU(c, cudaMemsetAsync(c->d_mbs.p, 0, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, s), "clear mbs");
-        CU(c, cudaMemsetAsync(c->d_levels.p, 0, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, s), "clear levels");
     }
     CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * (size_t)std::max(n, 1), s), "clear status");
     if (trace) cudaEventRecord(c->ev[9], s);
@@ -961,6 +985,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     CU(c, cudaMemcpyAsync(c->d_ehdr.p, hdrs, sizeof(Vp8EntropyHdr) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D entropy headers");
     if (int r2 = upload_row_tables(c, c->h_aux.p, cudaMemcpyHostToDevice, s)) return r2;
     c->uploaded = true;
+    c->bd.levels_packed = 1;
     c->last_entropy = WEBPB200_ENTROPY_DEVICE;
     c->last_h2d = sizeof(webpb200_frame_desc) * (uint64_t)n + sizeof(Vp8EntropyHdr) * (uint64_t)n + bits_bytes + c->alpha_bytes + c->aux_bytes;
     // Band pipelining: when every frame has the same size and the caller's buffers are evenly spaced,

@@ -34,9 +34,7 @@
 // saves), a packed per-block table for the context bit positions instead of arithmetic (+2 %),
 // folding the "window empty" test into the one-arm through a saturating shift (+8 %), requesting the
 // EOB / zero / one probabilities of the next rows (16-byte entries, no extraction) ahead of use (+7 %).
-#ifndef ENT_ONE_SITE
-#define ENT_ONE_SITE 1   // one inlined copy of the block decoder (25-block loop) instead of three: less code to fetch (-2 %)
-#endif
+// (one inlined copy of the block decoder in a 25-block loop instead of three copies: less code to fetch, -2 %)
 #ifndef ENT_WIDE
 #define ENT_WIDE 2       // token probabilities stored as {p << 24, (256 - p) << 24}: split = hi32(range * a + b), one IMAD.WIDE; 2 = 16-byte entries
 #endif
@@ -481,63 +479,32 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
             } else {
                 int16_t* lv = levels + (size_t)mbi * WEBPB200_LEVELS_PER_MB;
                 uint32_t nflags = 0;
-#if ENT_ONE_SITE
                 // 25 blocks in bitstream order: Y2 (if any), 16 Y, 4 U, 4 V.  Context bit of block k:
                 // top  = 1 + column (Y), 5 + column (U), 7 + column (V), 0 (Y2); left likewise with rows.
+                // Levels go out PACKED (the section 8(f) wire format): a block takes a 32-byte slot of its
+                // macroblock's 800-byte record only if it carries tokens, slots in this decode order; nflags
+                // says which blocks those are.  A slot is cleared right before it is decoded into, so nothing
+                // has to be cleared ahead of the kernel and the blocks without tokens are never written or read.
                 const bool has_y2 = ymode != 4;
+                int16_t* slot = lv;
+                bool clean = false;
 #pragma unroll 1
                 for (int k = has_y2 ? -1 : 0; k < 24; k++) {
                     int tb, lb, plane, first = 0, blk = k;
                     if (k < 0) { tb = 0; lb = 0; plane = 1; blk = 24; }
                     else if (k < 16) { tb = 1 + (k & 3); lb = 1 + (k >> 2); plane = has_y2 ? 0 : 3; first = has_y2; }
                     else { const int c = k - 16; tb = 5 + 2 * (c >> 2) + (c & 1); lb = 5 + 2 * (c >> 2) + ((c >> 1) & 1); plane = 2; }
-                    const int n = read_block(br, s_probs + plane * 264, ctl->lut, ((t >> tb) & 1) + ((l >> lb) & 1), first, lv + blk * 16);
+                    if (!clean) {
+                        reinterpret_cast<uint4*>(slot)[0] = make_uint4(0u, 0u, 0u, 0u);
+                        reinterpret_cast<uint4*>(slot)[1] = make_uint4(0u, 0u, 0u, 0u);
+                        clean = true;
+                    }
+                    const int n = read_block(br, s_probs + plane * 264, ctl->lut, ((t >> tb) & 1) + ((l >> lb) & 1), first, slot);
                     nflags |= (uint32_t)n << blk;
                     t = (t & ~(1u << tb)) | ((uint32_t)n << tb);
                     l = (l & ~(1u << lb)) | ((uint32_t)n << lb);
+                    if (n) { slot += 16; clean = false; }
                 }
-#else
-                int plane = 3, first = 0;
-                if (ymode != 4) {
-                    const int n = read_block(br, s_probs + 1 * 264, ctl->lut, (t & 1) + (l & 1), 0, lv + 24 * 16);
-                    t = (t & ~1u) | n;
-                    l = (l & ~1u) | n;
-                    nflags |= (uint32_t)n << 24;
-                    plane = 0;
-                    first = 1;
-                }
-                const TokenProb* yp = s_probs + plane * 264;
-#pragma unroll 1
-                for (int y = 0; y < 4; y++) {
-                    int ll = (l >> (1 + y)) & 1;
-#pragma unroll 1
-                    for (int x = 0; x < 4; x++) {
-                        const int k = y * 4 + x;
-                        const int n = read_block(br, yp, ctl->lut, ((t >> (1 + x)) & 1) + ll, first, lv + k * 16);
-                        nflags |= (uint32_t)n << k;
-                        ll = n;
-                        t = (t & ~(2u << x)) | ((uint32_t)n << (1 + x));
-                    }
-                    l = (l & ~(2u << y)) | ((uint32_t)ll << (1 + y));
-                }
-#pragma unroll 1
-                for (int j = 5; j <= 7; j += 2) {
-                    const int blk0 = j == 5 ? 16 : 20;
-#pragma unroll 1
-                    for (int y = 0; y < 2; y++) {
-                        int ll = (l >> (y + j)) & 1;
-#pragma unroll 1
-                        for (int x = 0; x < 2; x++) {
-                            const int k = blk0 + y * 2 + x;
-                            const int n = read_block(br, s_probs + 2 * 264, ctl->lut, ((t >> (x + j)) & 1) + ll, 0, lv + k * 16);
-                            nflags |= (uint32_t)n << k;
-                            ll = n;
-                            t = (t & ~(1u << (x + j))) | ((uint32_t)n << (x + j));
-                        }
-                        l = (l & ~(1u << (y + j))) | ((uint32_t)ll << (y + j));
-                    }
-                }
-#endif
                 mbs[mbi].nflags = nflags;
                 if (br.eof) {
                     A.status[f] = WEBPB200_ERR_BITSTREAM;

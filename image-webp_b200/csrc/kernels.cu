@@ -337,7 +337,7 @@ struct __align__(16) PredictSmem {
     int32_t wht[2][16];
     uint32_t quant[16];                  // this frame's quantisers: [segment * 4 + class] = dc | ac << 16
     int16_t lv[2][32 * 16];              // the next pair's levels (25 x 16 used each), prefetched with cp.async
-    uint4 desc[2];                       // and their descriptors
+    uint4 desc[2][2];                    // descriptors: [pair parity][macroblock of the pair], fetched two pairs ahead
     uint8_t map[64];                     // transform slot -> (macroblock of the pair) << 5 | block
 };
 
@@ -362,26 +362,38 @@ struct PredictArgs {
 // large frames wait on each other (latency-bound): cfg3 2.56 -> 1.85 ms, cfg2 0.93 -> 1.02 ms.
 constexpr int kPredictBlocksThroughput = 3, kPredictBlocksLatency = 2;
 
-// levels (800 B) + descriptor (16 B) of macroblocks `mbi` and (if `two`) `mbi + 1` -> the warp's staging
-// buffers, asynchronously
-__device__ __forceinline__ void prefetch_pair(PredictSmem& S, const PredictArgs& A, size_t mbi, bool two, int lane) {
+// Level records.  Dense (the boundary format of include/webpb200.h, what the host entropy decoder and
+// webpb200_reconstruct_device callers supply): block b of a macroblock at b * 32 bytes of its 800-byte record.
+// Packed (what k_entropy writes, the section 8(f) format): only the blocks that carry tokens, 32 bytes each, in
+// decode order (Y2 first, then 0..23) from the start of the record; the descriptor's nflags says which.
+template <bool kPacked>
+__device__ __forceinline__ int level_slot(uint32_t nflags, int blk) {
+    if (!kPacked) return blk;
+    return blk == 24 ? 0 : (int)((nflags >> 24) & 1u) + __popc(nflags & ((1u << blk) - 1u));
+}
+
+// levels of macroblocks `mbi` (n0 slots) and `mbi + 1` (n1 slots, 0 = no such macroblock) -> the warp's
+// staging buffers, asynchronously; descriptors of the pair two further on (if `dmbi` != 0 count) into `dslot`
+__device__ __forceinline__ void prefetch_pair(PredictSmem& S, const PredictArgs& A, size_t mbi, int n0, int n1, int dslot, size_t dmbi, int dcount,
+                                              int lane) {
     if (lane < 25) {
         const char* src = reinterpret_cast<const char*>(A.levels + mbi * WEBPB200_LEVELS_PER_MB) + lane * 32;
         char* dst = reinterpret_cast<char*>(S.lv[0]) + lane * 32;
-        cp_async16(dst, src);
-        cp_async16(dst + 16, src + 16);
-        if (two) {
+        if (lane < n0) {
+            cp_async16(dst, src);
+            cp_async16(dst + 16, src + 16);
+        }
+        if (lane < n1) {
             cp_async16(dst + sizeof(S.lv[0]), src + 2 * WEBPB200_LEVELS_PER_MB);
             cp_async16(dst + sizeof(S.lv[0]) + 16, src + 2 * WEBPB200_LEVELS_PER_MB + 16);
         }
-    } else if (lane == 25) {
-        cp_async16(&S.desc[0], A.mbs + mbi);
-        if (two) cp_async16(&S.desc[1], A.mbs + mbi + 1);
+    } else if (lane - 25 < dcount) {  // lanes 25, 26
+        cp_async16(&S.desc[dslot][lane - 25], A.mbs + dmbi + (lane - 25));
     }
     cp_async_commit();
 }
 
-template <int kMinBlocks>
+template <int kMinBlocks, bool kPacked>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A) {
     __shared__ PredictSmem smem[kWarpsPerBlock];
     __shared__ uint32_t s_bpred[160];
@@ -437,7 +449,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
         uint8_t* const yout = Y + (size_t)(mby * 16 + (lane >> 1)) * ystride + (lane & 1) * 8;
         uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
 
-        prefetch_pair(S, A, mb_row0, mbw > 1, lane);
+        // first pair: whole records (the packed slots in use are not known yet), with its descriptors and the next pair's
+        prefetch_pair(S, A, mb_row0, 25, mbw > 1 ? 25 : 0, 0, mb_row0, min(mbw, 2), lane);
+        if (mbw > 2) prefetch_pair(S, A, mb_row0, 0, 0, 1, mb_row0 + 2, min(mbw - 2, 2), lane);
         // the frame's quantisers, once per row (class 0 = Y, 1 = U/V, 2 = Y2): descriptor loads would
         // miss L1 on every macroblock because the acquire fences keep invalidating it
         if (lane < 16) {
@@ -462,18 +476,25 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
                 const bool two = mbx + 1 < mbw;
                 cp_async_wait_all();
                 __syncwarp();
-                mbw4 = S.desc[0];
-                desc_odd = two ? S.desc[1] : make_uint4(0x01000000u, 0, 0, 0);  // a missing partner counts as skipped
+                const int dsl = (mbx >> 1) & 1;
+                mbw4 = S.desc[dsl][0];
+                desc_odd = two ? S.desc[dsl][1] : make_uint4(0x01000000u, 0, 0, 0);  // a missing partner counts as skipped
                 const uint32_t d0 = mbw4.x, d1 = desc_odd.x;
                 const bool use0 = !((d0 >> 24) & 1), use1 = !((d1 >> 24) & 1);       // not skipped
                 const bool y2_0 = use0 && (d0 & 0xff) != 4, y2_1 = use1 && (d1 & 0xff) != 4;
                 // Y2 first (iwht, transform.rs:54-86): lane 24 for the even macroblock, lane 25 for the odd one
                 if ((lane == 24 && y2_0) || (lane == 25 && y2_1)) {
                     const int wh = lane - 24;
-                    const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + 24 * 16);
+                    // (packed: the Y2 block has a slot, the first, only if it carried tokens)
+                    const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + level_slot<kPacked>(wh ? desc_odd.y : mbw4.y, 24) * 16);
                     int c[16];
-                    unpack8(lp[0], c);
-                    unpack8(lp[1], c + 8);
+                    if (!kPacked || (((wh ? desc_odd.y : mbw4.y) >> 24) & 1u)) {
+                        unpack8(lp[0], c);
+                        unpack8(lp[1], c + 8);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; i++) c[i] = 0;
+                    }
                     const uint32_t qw = S.quant[(((wh ? d1 : d0) >> 16) & 3) * 4 + 2];
                     const int dcq = qw & 0xffff, acq = qw >> 16;
                     c[0] *= dcq;
@@ -490,8 +511,10 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
                 // (most luma blocks of a 16x16-predicted macroblock) then do not take a lane of the IDCT pass.
                 bool nz0 = false, nz1 = false, need0 = false, need1 = false;
                 if (lane < 24) {
-                    const int dc0 = (y2_0 && lane < 16) ? S.wht[0][lane] : (int)S.lv[0][lane * 16];
-                    const int dc1 = (y2_1 && lane < 16) ? S.wht[1][lane] : (int)S.lv[1][lane * 16];
+                    // the DC of a block WITHOUT the flag (the only case it is used below): from the Y2 block; else, packed,
+                    // 0 (a block has levels only if it had tokens), dense, whatever the caller's record holds
+                    const int dc0 = (y2_0 && lane < 16) ? S.wht[0][lane] : kPacked ? 0 : (int)S.lv[0][lane * 16];
+                    const int dc1 = (y2_1 && lane < 16) ? S.wht[1][lane] : kPacked ? 0 : (int)S.lv[1][lane * 16];
                     need0 = use0 && ((mbw4.y >> lane) & 1);
                     need1 = use1 && ((desc_odd.y >> lane) & 1);
                     nz0 = need0 || (use0 && dc0 != 0);
@@ -525,7 +548,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
                     if (slot < total) {
                         const int mm = S.map[slot], wh = mm >> 5, blk = mm & 31;
                         const uint32_t dw = wh ? d1 : d0;
-                        const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + blk * 16);
+                        const uint4* lp = reinterpret_cast<const uint4*>(S.lv[wh] + level_slot<kPacked>(wh ? desc_odd.y : mbw4.y, blk) * 16);
                         int c[16];
                         unpack8(lp[0], c);
                         unpack8(lp[1], c + 8);
@@ -547,7 +570,14 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
                     }
                 }
                 __syncwarp();
-                if (mbx + 2 < mbw) prefetch_pair(S, A, mbi + 2, mbx + 3 < mbw, lane);
+                if (mbx + 2 < mbw) {
+                    // the next pair's levels (its descriptors arrived with this pair's levels) and the descriptors
+                    // of the pair after it, into the descriptor slot this pair has just left
+                    const uint32_t nf0 = S.desc[dsl ^ 1][0].y, nf1 = mbx + 3 < mbw ? S.desc[dsl ^ 1][1].y : 0u;
+                    const int n0 = kPacked ? __popc(nf0 & 0x1ffffffu) : 25;
+                    const int n1 = mbx + 3 < mbw ? (kPacked ? __popc(nf1 & 0x1ffffffu) : 25) : 0;
+                    prefetch_pair(S, A, mbi + 2, n0, n1, dsl, mbi + 4, max(0, min(mbw - mbx - 4, 2)), lane);
+                }
             }
             const int16_t* const res = S.res[mbx & 1];
             const int ymode = mbw4.x & 0xff, uvmode = (mbw4.x >> 8) & 0xff;
@@ -1443,8 +1473,8 @@ __global__ void k_composite(CompositeArgs a) {
 
 void wavefront_blocks_per_sm(int* predict_blocks, int* predict_blocks_latency, int* filter_blocks) {
     int p = 0, l = 0, f = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict<kPredictBlocksThroughput>), kThreads, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&l, reinterpret_cast<const void*>(k_predict<kPredictBlocksLatency>), kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict<kPredictBlocksThroughput, false>), kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&l, reinterpret_cast<const void*>(k_predict<kPredictBlocksLatency, false>), kThreads, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&f, reinterpret_cast<const void*>(k_loopfilter), kThreads, 0);
     *predict_blocks = p < 1 ? 1 : p;
     *predict_blocks_latency = l < 1 ? 1 : l;
@@ -1473,8 +1503,13 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     // few rows for the machine (they wait on each other): the build with the shorter dependency chain
     const int lat_blocks = b.predict_blocks_latency > 0 ? b.predict_blocks_latency : 1;
     const bool latency_bound = b.predict_blocks_latency > 0 && (uint64_t)b.total_rows <= 2ull * lat_blocks * (b.sm_count > 0 ? b.sm_count : 1) * kWarpsPerBlock;
-    if (latency_bound) k_predict<kPredictBlocksLatency><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
-    else k_predict<kPredictBlocksThroughput><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
+    if (latency_bound) {
+        if (b.levels_packed) k_predict<kPredictBlocksLatency, true><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
+        else k_predict<kPredictBlocksLatency, false><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
+    } else {
+        if (b.levels_packed) k_predict<kPredictBlocksThroughput, true><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
+        else k_predict<kPredictBlocksThroughput, false><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
+    }
     return cudaGetLastError();
 }
 

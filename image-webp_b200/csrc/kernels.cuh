@@ -39,6 +39,7 @@ struct BatchDev {
     const webpb200_frame_desc* frames;  // device
     const webpb200_mb_desc* mbs;
     const int16_t* levels;
+    int levels_packed;      // levels are in k_entropy's packed form (kernels.cu, "Level records"), not the dense boundary format
     const uint8_t* alpha;  // alpha residual planes (may be null)
     uint8_t* planes;
     uint8_t* out;
