@@ -301,6 +301,9 @@ def main():
     bd.sync()
     size = bd.size()
     px, mbs = size["pixels"], size["macroblocks"]
+    # blocks per macroblock that carry tokens (sample of 64 images): what the packed level format stores and reads
+    sample = [bd.packed(i)[1]["nflags"] for i in range(min(per_gpu, 64))]
+    blocks_per_mb = float(np.mean([np.unpackbits((f & 0x1ffffff).astype("<u4").view(np.uint8)).sum() / max(len(f), 1) for f in sample]))
 
     # ---- device-resident hot path: W warm-up steps, then exactly K timed steps ----
     warm = max(args.warmup, 3)
@@ -387,6 +390,9 @@ def main():
     for _ in range(e2e_steps):
         bd.decode_to_device(file_list, host_threads=host_threads)
     dev_out_ms = 1e3 * (time.perf_counter() - t1) / e2e_steps
+    # the device-resident pass again on the batch as decode_batch leaves it: levels written by k_entropy in the
+    # packed form (only the blocks that carry tokens), read by the packed build of k_predict
+    ms_packed, kernel_ms_packed = bd.time(15, iters=args.steps, flush_l2=False)
     sh.barrier(dist)
     e2e_px, e2e_max_ms = sh.aggregate(dist, px, e2e_ms)
     e2e_value = e2e_px / (e2e_max_ms / 1e3) / 1e6
@@ -432,7 +438,13 @@ def main():
             "roofline": {"bound": "hbm", "kernel": names[dominant], "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic_per_launch(names[dominant]), "peak_kind": peak_kind,
                          "pipeline_achieved": pipeline_gbs, "pipeline_frac": pipeline_gbs / peak,
-                         "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass"},
+                         "note": "achieved = algorithmic bytes of the dominant kernel per launch / its CUDA-event time; pipeline_* = SURVEY 8(d) bytes (6.19 B/px here) over the whole pass",
+                         "packed_levels": {"what": "the same pass on the batch as webpb200_decode_batch leaves it: k_entropy writes only the blocks that carry tokens (32 B each), k_predict reads only those",
+                                           "blocks_per_mb": blocks_per_mb, "level_bytes_per_mb": 32 * blocks_per_mb, "dense_level_bytes_per_mb": 800,
+                                           "ms_per_pass": ms_packed, "k_predict_ms": kernel_ms_packed[0],
+                                           "pipeline_bytes_per_mb": 16 + 32 * blocks_per_mb + 768,
+                                           "pipeline_achieved": (16 + 32 * blocks_per_mb + 768) * mbs / (ms_packed / 1e3) / 1e9,
+                                           "pipeline_frac": (16 + 32 * blocks_per_mb + 768) * mbs / (ms_packed / 1e3) / 1e9 / peak}},
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
                     "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": pipe_steps if pipelined else e2e_steps, "host_threads": host_threads,

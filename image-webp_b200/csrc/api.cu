@@ -182,12 +182,17 @@ struct webpb200_ctx {
     uint64_t launches = 0;
     std::atomic<bool> in_flight{false};  // a webpb200_decode_batch_begin has not been ended yet
 
-    PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status;
+    PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status, h_vp8l_px, h_vp8l_planes, h_vp8l_aux;
     uint64_t last_h2d = 0, last_d2h = 0;  // bytes the last decode_batch copied each way
     int last_entropy = WEBPB200_ENTROPY_HOST;  // where its entropy stage ran
     float last_entropy_ms = 0;  // device time of k_entropy in the last decode_batch (0 if it ran on the host)
     int entropy_where = WEBPB200_ENTROPY_AUTO;  // WEBPB200_ENTROPY_*: where decode_batch runs the boolean decode
-    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status;
+    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status, d_vp8l_px, d_vp8l_planes, d_vp8l_aux, d_vp8l_hand;
+    // VP8L-compressed ALPH planes of the current batch (entropy-decoded on the host, transforms undone on the device)
+    std::vector<int> vp8l_of_item;          // item -> plane index, -1 = none
+    std::vector<uint64_t> vp8l_aux_off;     // plane -> word offset of its transform data in the aux arena
+    uint64_t vp8l_px_words = 0, vp8l_aux_words = 0, vp8l_hand_units = 0;
+    int vp8l_n = 0;
 
     // current batch
     int n = 0;
@@ -308,6 +313,43 @@ int layout_items(webpb200_ctx* c, std::vector<WorkItem>&& in_items, int upsampli
         CU(c, c->h_levels.reserve(sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)std::max<uint64_t>(mbs, 1)), "pinned levels");
     }
     CU(c, c->h_alpha.reserve((size_t)std::max<uint64_t>(aoff, 1)), "pinned alpha");
+    // VP8L-compressed ALPH planes (the compression method is the low two bits of the chunk's first byte,
+    // extended.rs:259-266): a slot each in the pixel, aux and hand-off arenas, sized for the worst case
+    c->vp8l_of_item.assign((size_t)n, -1);
+    c->vp8l_aux_off.clear();
+    c->vp8l_n = 0;
+    c->vp8l_px_words = c->vp8l_aux_words = c->vp8l_hand_units = 0;
+    {
+        std::vector<uint64_t> px_off, hand_off;
+        for (int i = 0; i < n; i++) {
+            const WorkItem& it = items[i];
+            if (it.status || !frames[i].alpha_mode || !it.alph || it.alph_len < 1 || (it.alph[0] & 3) != 1) continue;
+            const uint64_t w = frames[i].width, h = frames[i].height;
+            c->vp8l_of_item[i] = c->vp8l_n++;
+            px_off.push_back(c->vp8l_px_words);
+            c->vp8l_px_words += (w * h + 1 + 63) & ~uint64_t(63);
+            c->vp8l_aux_off.push_back(c->vp8l_aux_words);
+            c->vp8l_aux_words += (2 * ((w + 3) / 4) * ((h + 3) / 4) + 256 + 63) & ~uint64_t(63);
+            hand_off.push_back(c->vp8l_hand_units);
+            c->vp8l_hand_units += 2 * w;
+        }
+        if (c->vp8l_n) {
+            CU(c, c->h_vp8l_px.reserve(4 * (size_t)c->vp8l_px_words), "pinned VP8L pixels");
+            CU(c, c->h_vp8l_aux.reserve(4 * (size_t)c->vp8l_aux_words), "pinned VP8L transform data");
+            CU(c, c->h_vp8l_planes.reserve(sizeof(Vp8lPlane) * (size_t)c->vp8l_n), "pinned VP8L planes");
+            Vp8lPlane* planes = reinterpret_cast<Vp8lPlane*>(c->h_vp8l_planes.p);
+            std::memset(planes, 0, sizeof(Vp8lPlane) * (size_t)c->vp8l_n);
+            for (int i = 0; i < n; i++) {
+                const int k = c->vp8l_of_item[i];
+                if (k < 0) continue;
+                planes[k].width = frames[i].width;
+                planes[k].height = frames[i].height;
+                for (int b = 0; b < 3; b++) planes[k].buf_off[b] = (uint64_t)b * c->vp8l_px_words + px_off[k];
+                planes[k].hand_off = hand_off[k];
+                planes[k].alpha_off = frames[i].alpha_off;
+            }
+        }
+    }
     c->aux_rowmap_off = 0;
     c->aux_order_off = (size_t)align256(4 * rows);
     c->aux_recbase_off = c->aux_order_off + (size_t)align256(4 * rows);
@@ -340,7 +382,31 @@ int alpha_one(webpb200_ctx* c, int i, webpb200_frame_desc& fd) {
     if (!st && want != have) st = WEBPB200_ERR_INCONSISTENT_SIZE;
     if (!st) {
         fd.alpha_filter = (uint8_t)filter;
-        if (compressed) st = vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, dst);
+        const int k = i < (int)c->vp8l_of_item.size() ? c->vp8l_of_item[i] : -1;
+        if (compressed && k >= 0) {
+            // prefix codes / LZ77 here, the inverse transforms on the device (vp8l.cu): the plane's slot of the pixel
+            // arena gets the image in the transformed domain, its plane record the transforms to undo
+            Vp8lPlane& P = reinterpret_cast<Vp8lPlane*>(c->h_vp8l_planes.p)[k];
+            uint32_t* px = reinterpret_cast<uint32_t*>(c->h_vp8l_px.p) + P.buf_off[0];
+            uint32_t* aux = reinterpret_cast<uint32_t*>(c->h_vp8l_aux.p);
+            Vp8lPlan plan;
+            st = vp8l_decode_entropy(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, px, &plan);
+            P.n_stages = 0;
+            if (!st) {
+                uint64_t at = c->vp8l_aux_off[k];
+                for (int q = 0; q < plan.n_stages; q++) {
+                    Vp8lStage& S = P.st[q];
+                    S.kind = (uint32_t)plan.st[q].kind;
+                    S.bits = (uint32_t)plan.st[q].bits;
+                    S.table_size = (uint32_t)plan.st[q].table_size;
+                    S.w_in = (uint32_t)plan.st[q].w_in;
+                    S.data_off = at;
+                    if (!plan.st[q].data.empty()) std::memcpy(aux + at, plan.st[q].data.data(), 4 * plan.st[q].data.size());
+                    at += plan.st[q].data.size();
+                }
+                P.n_stages = (uint32_t)plan.n_stages;
+            }
+        } else if (compressed) st = vp8l_decode_green(it.alph + 1, it.alph_len - 1, it.alph_w, it.alph_h, dst);
         else if (it.alph_len - 1 < want) st = WEBPB200_ERR_IO;
         else std::memcpy(dst, it.alph + 1, want);
     }
@@ -411,6 +477,12 @@ int reserve_device(webpb200_ctx* c) {
     CU(c, c->d_out.reserve((size_t)std::max<uint64_t>(c->out_bytes, 1)), "device out");
     CU(c, c->d_scratch.reserve((size_t)c->bd.lay.total), "device scratch");
     if (c->alpha_bytes) CU(c, c->d_handoff.reserve((size_t)alpha_handoff_size(c->alpha_bytes)), "device alpha handoff");
+    if (c->vp8l_n) {
+        CU(c, c->d_vp8l_px.reserve(3 * 4 * (size_t)c->vp8l_px_words), "device VP8L pixels");
+        CU(c, c->d_vp8l_aux.reserve(4 * (size_t)std::max<uint64_t>(c->vp8l_aux_words, 1)), "device VP8L transform data");
+        CU(c, c->d_vp8l_planes.reserve(sizeof(Vp8lPlane) * (size_t)c->vp8l_n), "device VP8L planes");
+        CU(c, c->d_vp8l_hand.reserve(8 * (size_t)std::max<uint64_t>(c->vp8l_hand_units, 1)), "device VP8L hand-off");
+    }
     BatchDev& bd = c->bd;
     bd.frames = reinterpret_cast<const webpb200_frame_desc*>(c->d_frames.p);
     bd.mbs = reinterpret_cast<const webpb200_mb_desc*>(c->d_mbs.p);
@@ -422,6 +494,49 @@ int reserve_device(webpb200_ctx* c) {
     bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + c->aux_lists_off);
     bd.alpha_handoff = c->alpha_bytes ? reinterpret_cast<uint16_t*>(c->d_handoff.p) : nullptr;
     bd.alpha_handoff_bytes = c->alpha_bytes ? alpha_handoff_size(c->alpha_bytes) : 0;
+    std::memset(&bd.vp8l, 0, sizeof(bd.vp8l));
+    bd.vp8l_hand_bytes = 0;
+    if (c->vp8l_n) {
+        bd.vp8l.planes = reinterpret_cast<const Vp8lPlane*>(c->d_vp8l_planes.p);
+        bd.vp8l.n_planes = c->vp8l_n;
+        bd.vp8l.max_stages = 4;  // a stage index beyond a plane's own count is skipped by the kernel
+        bd.vp8l.max_height = bd.max_h;
+        bd.vp8l.pixels = reinterpret_cast<uint32_t*>(c->d_vp8l_px.p);
+        bd.vp8l.aux = reinterpret_cast<const uint32_t*>(c->d_vp8l_aux.p);
+        bd.vp8l.handoff = reinterpret_cast<uint2*>(c->d_vp8l_hand.p);
+        bd.vp8l.alpha = c->d_alpha.p;
+        bd.vp8l.ticket = reinterpret_cast<unsigned int*>(c->d_scratch.p) + 4;
+        bd.vp8l.abort_word = reinterpret_cast<unsigned int*>(c->d_scratch.p) + 2;
+        bd.vp8l.sm_count = c->sm_count;
+        bd.vp8l_hand_bytes = 8 * c->vp8l_hand_units;
+    }
+    return 0;
+}
+
+// the VP8L planes [p0, p1) of the batch: transformed-domain pixels, plane records and transform data -> device
+int upload_vp8l(webpb200_ctx* c, int p0, int p1, cudaStream_t s) {
+    if (p1 <= p0) return 0;
+    const Vp8lPlane* planes = reinterpret_cast<const Vp8lPlane*>(c->h_vp8l_planes.p);
+    const uint64_t w0 = planes[p0].buf_off[0], w1 = p1 < c->vp8l_n ? planes[p1].buf_off[0] : c->vp8l_px_words;
+    CU(c, cudaMemcpyAsync(c->d_vp8l_px.p + 4 * w0, c->h_vp8l_px.p + 4 * w0, 4 * (size_t)(w1 - w0), cudaMemcpyHostToDevice, s), "H2D VP8L pixels");
+    const uint64_t a0 = c->vp8l_aux_off[p0], a1 = p1 < c->vp8l_n ? c->vp8l_aux_off[p1] : c->vp8l_aux_words;
+    CU(c, cudaMemcpyAsync(c->d_vp8l_aux.p + 4 * a0, c->h_vp8l_aux.p + 4 * a0, 4 * (size_t)(a1 - a0), cudaMemcpyHostToDevice, s), "H2D VP8L transform data");
+    CU(c, cudaMemcpyAsync(c->d_vp8l_planes.p + sizeof(Vp8lPlane) * (size_t)p0, c->h_vp8l_planes.p + sizeof(Vp8lPlane) * (size_t)p0,
+                          sizeof(Vp8lPlane) * (size_t)(p1 - p0), cudaMemcpyHostToDevice, s), "H2D VP8L planes");
+    c->last_h2d += 4 * (w1 - w0) + 4 * (a1 - a0);
+    return 0;
+}
+
+// undo the VP8L transforms of the planes [p0, p1) (alpha stage, before the un-filter kernels)
+int run_vp8l(webpb200_ctx* c, const BatchDev& bd, int p0, int p1, cudaStream_t s) {
+    if (p1 <= p0 || !bd.vp8l.n_planes) return 0;
+    Vp8lBatch v = bd.vp8l;
+    v.planes += p0;
+    v.n_planes = p1 - p0;
+    CU(c, cudaMemsetAsync(v.handoff, 0, (size_t)bd.vp8l_hand_bytes, s), "clear VP8L hand-off");
+    int l = 0;
+    CU(c, launch_vp8l_inverse(v, s, &l), "k_vp8l");
+    c->launches += (uint64_t)l;
     return 0;
 }
 
@@ -447,6 +562,7 @@ int upload(webpb200_ctx* c) {
         CU(c, cudaMemcpyAsync(c->d_levels.p, c->h_levels.p, sizeof(int16_t) * WEBPB200_LEVELS_PER_MB * (size_t)c->total_mbs, cudaMemcpyHostToDevice, s), "H2D levels");
     }
     if (c->alpha_bytes) CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+    if (int r = upload_vp8l(c, 0, c->vp8l_n, s)) return r;
     CU(c, cudaMemcpyAsync(c->d_aux.p, c->h_aux.p, c->aux_bytes, cudaMemcpyHostToDevice, s), "H2D aux");
     if (int r = upload_row_tables(c, c->d_aux.p, cudaMemcpyDeviceToDevice, s)) return r;
     c->uploaded = true;
@@ -469,6 +585,7 @@ int reconstruct(webpb200_ctx* c, const BatchDev& bd, unsigned stages, cudaStream
     if (stages & 4) { CU(c, launch_yuv2rgb(bd, s), "k_yuv2rgb"); c->launches++; }
     if (events) cudaEventRecord(events[3], s);
     if (stages & 8) {
+        if (int r = run_vp8l(c, bd, 0, bd.vp8l.n_planes, s)) return r;
         int l = 0;
         CU(c, launch_alpha(bd, s, &l), "k_alpha");
         c->launches += (uint64_t)l;
@@ -634,8 +751,8 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
-    for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status}) b->release();
-    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status})
+    for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status, &c->h_vp8l_px, &c->h_vp8l_planes, &c->h_vp8l_aux}) b->release();
+    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status, &c->d_vp8l_px, &c->d_vp8l_planes, &c->d_vp8l_aux, &c->d_vp8l_hand})
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
@@ -1062,6 +1179,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         });
         CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
         CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
+        if (int r2 = upload_vp8l(c, 0, c->vp8l_n, s)) return r2;
     }
     finish_items(c);
     CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
@@ -1431,6 +1549,15 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
             if (bd.alpha_counts[0] + bd.alpha_counts[1] + bd.alpha_counts[2] + bd.alpha_counts[3]) {
                 const uint64_t a0 = frames[i0].alpha_off, a1 = i1 < n ? frames[i1].alpha_off : c->alpha_bytes;
                 if (a1 > a0) fail(cudaMemcpyAsync(c->d_alpha.p + a0, c->h_alpha.p + a0, (size_t)(a1 - a0), cudaMemcpyHostToDevice, s), "H2D alpha");
+                {   // this chunk's VP8L planes: upload what the host threads decoded, undo the transforms
+                    int p0 = c->vp8l_n, p1 = 0;
+                    for (int i = i0; i < i1; i++)
+                        if (c->vp8l_of_item[i] >= 0) { p0 = std::min(p0, c->vp8l_of_item[i]); p1 = std::max(p1, c->vp8l_of_item[i] + 1); }
+                    if (p1 > p0 && !err) {
+                        if (int r = upload_vp8l(c, p0, p1, s)) err = r;
+                        if (!err) if (int r = run_vp8l(c, c->bd, p0, p1, s)) err = r;
+                    }
+                }
                 const size_t lo = c->aux_lists_off + sizeof(int) * 4 * (size_t)i0;
                 fail(cudaMemcpyAsync(c->d_aux.p + lo, c->h_aux.p + lo, sizeof(int) * 4 * (size_t)nc, cudaMemcpyHostToDevice, s), "H2D lists");
                 bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + lo);

@@ -450,6 +450,32 @@ struct Decoder {
         }
     }
 
+    // the entropy-coded part only: `im` receives the image in the transformed domain (xs x height), `plan` the
+    // transforms in the order they have to be undone
+    int run_entropy(uint32_t* im, Vp8lPlan* plan) {
+        int xs;
+        int st = read_transforms(&xs);
+        if (st) return st;
+        st = read_pixels(xs, height, true, im);
+        if (st) return st;
+        plan->n_stages = 0;
+        int w = xs;
+        for (int k = norder - 1; k >= 0; k--) {
+            Xform& t = xf[order[k]];
+            Vp8lPlan::Stage& ps = plan->st[plan->n_stages++];
+            ps.kind = t.kind;
+            ps.bits = t.bits;
+            ps.table_size = t.table_size;
+            ps.w_in = w;
+            ps.data.swap(t.data);
+            if (t.kind == 3) {
+                ps.bits = t.table_size <= 2 ? 3 : t.table_size <= 4 ? 2 : t.table_size <= 16 ? 1 : 0;
+                w = width;
+            }
+        }
+        return 0;
+    }
+
     int run(uint32_t* im) {
         int xs;
         int st = read_transforms(&xs);
@@ -494,6 +520,16 @@ int vp8l_decode_green(const uint8_t* data, size_t len, int width, int height, ui
     if (st) return st;
     for (size_t i = 0; i < (size_t)width * height; i++) green[i] = (uint8_t)((im[i] >> 8) & 0xff);
     return 0;
+}
+
+int vp8l_decode_entropy(const uint8_t* data, size_t len, int width, int height, uint32_t* argb, Vp8lPlan* plan) {
+    if (width <= 0 || height <= 0) return WEBPB200_ERR_INVALID_PARAM;
+    Decoder d;
+    d.br.p = data;
+    d.br.end = data + len;
+    d.width = width;
+    d.height = height;
+    return d.run_entropy(argb, plan);
 }
 
 }  // namespace webpb200

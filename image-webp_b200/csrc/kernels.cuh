@@ -6,6 +6,7 @@
 
 #include "../../include/webpb200.h"
 #include "entropy.h"
+#include "vp8l.cuh"
 
 namespace webpb200 {
 
@@ -62,6 +63,9 @@ struct BatchDev {
     // frame f start at entry f.alpha_off >> 4; alpha_handoff_size(end of the alpha arena) bytes.
     uint16_t* alpha_handoff;
     uint64_t alpha_handoff_bytes;
+    // VP8L-compressed ALPH planes whose transforms are undone on the device before the un-filter (vp8l.cuh); n_planes = 0: none
+    Vp8lBatch vp8l;
+    uint64_t vp8l_hand_bytes;  // size of vp8l.handoff, cleared before every pass
 };
 inline uint64_t alpha_handoff_size(uint64_t alpha_bytes) { return ((alpha_bytes >> 3) + 511) & ~(uint64_t)255; }
 

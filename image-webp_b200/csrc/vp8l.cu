@@ -1,0 +1,246 @@
+// vp8l.cu -- sm_100a kernels that undo the VP8L transforms of compressed ALPH planes (see vp8l.cuh).
+// Arithmetic follows reference lossless/decoder/reverse_transform.rs; pixels are ARGB words (the reference keeps
+// RGBA bytes: its pixel[0..3] = bits 16-23, 8-15, 0-7, 24-31 here).
+#include "vp8l.cuh"
+
+namespace webpb200 {
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kWarps = 4;
+
+// per-channel wrapping add (reverse_transform.rs: `wrapping_add` on every byte)
+__device__ __forceinline__ uint32_t add4(uint32_t a, uint32_t b) {
+    return (((a & 0xff00ff00u) + (b & 0xff00ff00u)) & 0xff00ff00u) | (((a & 0x00ff00ffu) + (b & 0x00ff00ffu)) & 0x00ff00ffu);
+}
+// average2 (reverse_transform.rs:580-590): floor((a + b) / 2) per channel
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return (((a ^ b) & 0xfefefefeu) >> 1) + (a & b); }
+__device__ __forceinline__ int chan(uint32_t p, int c) { return (int)((p >> (8 * c)) & 0xffu); }
+// clamp_add_subtract_full (593-597)
+__device__ __forceinline__ uint32_t clamp_full(uint32_t l, uint32_t t, uint32_t tl) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int c = 0; c < 4; c++) r |= (uint32_t)min(max(chan(l, c) + chan(t, c) - chan(tl, c), 0), 255) << (8 * c);
+    return r;
+}
+// clamp_add_subtract_half (600-604) of (l + t) / 2 and tl; the i16 division truncates towards zero
+__device__ __forceinline__ uint32_t clamp_half(uint32_t l, uint32_t t, uint32_t tl) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const int a = (chan(l, c) + chan(t, c)) >> 1;
+        const int d = a - chan(tl, c);
+        r |= (uint32_t)min(max(a + (d < 0 ? -((-d) >> 1) : d >> 1), 0), 255) << (8 * c);
+    }
+    return r;
+}
+// predictor 11 (235-290): left if sum |t - tl| < sum |l - tl| over the four channels, else top
+__device__ __forceinline__ uint32_t select4(uint32_t l, uint32_t t, uint32_t tl) {
+    return __vsadu4(t, tl) < __vsadu4(l, tl) ? l : t;
+}
+
+__device__ __forceinline__ uint32_t predict(int mode, uint32_t L, uint32_t T, uint32_t TL, uint32_t TR) {
+    switch (mode) {
+        case 0: return 0xff000000u;
+        case 1: return L;
+        case 2: return T;
+        case 3: return TR;
+        case 4: return TL;
+        case 5: return avg4(avg4(L, TR), T);
+        case 6: return avg4(L, TL);
+        case 7: return avg4(L, T);
+        case 8: return avg4(TL, T);
+        case 9: return avg4(T, TR);
+        case 10: return avg4(avg4(L, TL), avg4(T, TR));
+        case 11: return select4(L, T, TL);
+        case 12: return clamp_full(L, T, TL);
+        default: return clamp_half(L, T, TL);  // 13
+    }
+}
+
+__device__ __forceinline__ uint2 ld_unit(const uint2* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return make_uint2((uint32_t)v, (uint32_t)(v >> 32));
+}
+__device__ __forceinline__ void st_unit(uint2* p, uint32_t px, uint32_t tag) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"((unsigned long long)px | ((unsigned long long)tag << 32)) : "memory");
+}
+
+struct StageArgs {
+    Vp8lBatch b;
+    int stage;
+};
+
+// which of the plane's buffers holds the image before stage s (vp8l.cuh): the upload, then [1] and [2] in turn
+__device__ __forceinline__ int buffer_before(int s) { return s == 0 ? 0 : 1 + ((s - 1) & 1); }
+
+// One stage of every plane.  Work unit = a band of 32 rows of one plane, handed out band-major across the planes
+// by a ticket counter, so that a predictor band only ever waits for a band with a lower ticket.
+//   predictor: lane j owns row 32g + j and runs two columns behind lane j-1, so that top-right, top and top-left
+//   arrive by one shuffle per step; lane 0 takes them from the hand-off records of the band above (8-byte units
+//   {pixel, tag}, the same protocol as the macroblock wavefront's edge records), the band's last row writes them.
+//   colour / subtract-green / palette: the warp sweeps its 32 rows, lanes along x.
+__global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
+    const int lane = threadIdx.x & 31;
+    const Vp8lBatch& B = A.b;
+    const int s = A.stage;
+    const unsigned max_bands = (B.max_height + 31) >> 5;
+    const unsigned total = max_bands * (unsigned)B.n_planes;
+    for (;;) {
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(B.ticket, 1u);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= total) return;
+        const int g = (int)(t / (unsigned)B.n_planes);
+        const Vp8lPlane& P = B.planes[t % (unsigned)B.n_planes];
+        if (s >= (int)P.n_stages || g * 32 >= (int)P.height) continue;
+        const Vp8lStage& S = P.st[s];
+        const int h = (int)P.height, w = (int)S.w_in;
+        const uint32_t* im = B.pixels + P.buf_off[buffer_before(s)];
+        uint32_t* om = B.pixels + P.buf_off[1 + (s & 1)];
+        const uint32_t* data = B.aux + S.data_off;
+        const int y0 = g * 32, rows = min(32, h - y0);
+
+        if (S.kind == VP8L_SUBTRACT_GREEN) {  // reverse_transform.rs:393-398
+            for (int r = 0; r < rows; r++) {
+                const uint32_t* row = im + (size_t)(y0 + r) * w;
+                uint32_t* orow = om + (size_t)(y0 + r) * w;
+                for (int x = lane; x < w; x += 32) {
+                    const uint32_t p = row[x], gg = (p >> 8) & 0xffu;
+                    orow[x] = (p & 0xff00ff00u) | (((p & 0x00ff00ffu) + (gg << 16 | gg)) & 0x00ff00ffu);
+                }
+            }
+        } else if (S.kind == VP8L_COLOR) {  // apply_color_transform, 353-391
+            const int bx = (w + (1 << S.bits) - 1) >> S.bits;
+            for (int r = 0; r < rows; r++) {
+                const int y = y0 + r;
+                const uint32_t* row = im + (size_t)y * w;
+                uint32_t* orow = om + (size_t)y * w;
+                const uint32_t* mrow = data + (size_t)(y >> S.bits) * bx;
+                for (int x = lane; x < w; x += 32) {
+                    const uint32_t m = mrow[x >> S.bits], p = row[x];
+                    const int g2r = (int)(int8_t)(m & 0xff), g2b = (int)(int8_t)((m >> 8) & 0xff), r2b = (int)(int8_t)((m >> 16) & 0xff);
+                    const int gg = (int)(int8_t)((p >> 8) & 0xff);
+                    int rr = (int)((p >> 16) & 0xff), bb = (int)(p & 0xff);
+                    rr = (rr + ((g2r * gg) >> 5)) & 0xff;
+                    bb = (bb + ((g2b * gg) >> 5)) & 0xff;
+                    bb = (bb + ((r2b * (int)(int8_t)rr) >> 5)) & 0xff;
+                    orow[x] = (p & 0xff00ff00u) | ((uint32_t)rr << 16) | (uint32_t)bb;
+                }
+            }
+        } else if (S.kind == VP8L_PALETTE) {  // apply_color_indexing_transform, 400-578: into the other buffer
+            uint32_t* out = om;
+            const int W = (int)P.width, n = (int)S.table_size;
+            const int pack = (int)S.bits, bpe = 8 >> pack, mask = (1 << bpe) - 1;
+            for (int r = 0; r < rows; r++) {
+                const uint32_t* row = im + (size_t)(y0 + r) * w;
+                uint32_t* orow = out + (size_t)(y0 + r) * W;
+                for (int x = lane; x < W; x += 32) {
+                    const int byte = (int)((row[x >> pack] >> 8) & 0xffu);
+                    const int k = (byte >> ((x & ((1 << pack) - 1)) * bpe)) & mask;
+                    orow[x] = k < n ? data[k] : 0u;
+                }
+            }
+        } else {  // predictor transform, apply_predictor_transform 24-78 + the fourteen predictors 79-351
+            const int bx = (w + (1 << S.bits) - 1) >> S.bits;
+            const int y = y0 + lane;
+            const bool row_ok = lane < rows;
+            const uint32_t* row = im + (size_t)(row_ok ? y : y0) * w;
+            uint32_t* orow = om + (size_t)(row_ok ? y : y0) * w;
+            const uint32_t* mrow = data + (size_t)((row_ok ? y : y0) >> S.bits) * bx;
+            const uint32_t tag_in = ((uint32_t)(s + 1) << 16) | (uint32_t)g, tag_out = ((uint32_t)(s + 1) << 16) | (uint32_t)(g + 1);
+            const uint2* above = B.handoff + P.hand_off + (size_t)((g + 1) & 1) * w;  // written by band g - 1
+            uint2* below = B.handoff + P.hand_off + (size_t)(g & 1) * w;
+            const bool hands = lane == rows - 1 && y0 + rows < h;                      // the band's last row, if a band follows
+            uint32_t L = 0, T = 0, TL = 0, mine = 0, first = 0;
+            uint2 nxt = make_uint2(0u, 0u);
+            unsigned spins_total = 0;
+            auto wait_unit = [&](const uint2* u, uint2 v) -> uint32_t {
+                unsigned spins = 0;
+                while (v.y != tag_in) {
+                    __nanosleep(40);
+                    v = ld_unit(u);
+                    if ((++spins & 0x3ff) == 0) {
+                        spins_total += 0x400;
+                        if (spins_total > (1u << 24)) atomicExch(B.abort_word, 1u);
+                        if (*reinterpret_cast<volatile unsigned int*>(B.abort_word)) break;
+                    }
+                }
+                return v.x;
+            };
+            if (lane == 0 && g > 0) {
+                // lane 0's "lane above" is the last row of the band above: its pixel 0 goes into the pipeline as
+                // `top` now, the others arrive one per step as `top-right`
+                T = wait_unit(above, ld_unit(above));
+                if (w > 1) nxt = ld_unit(above + 1);
+            }
+            const int steps = w + 2 * 31;
+            for (int i = 0; i < steps; i++) {
+                // top-right of my column: what the lane above finished in the previous step (its column x + 1)
+                uint32_t tr = __shfl_up_sync(kFull, mine, 1);
+                const int x = i - 2 * lane;
+                if (lane == 0) {
+                    if (g > 0 && x + 1 < w) {
+                        tr = wait_unit(above + x + 1, nxt);  // requested one step earlier
+                        if (x + 2 < w) nxt = ld_unit(above + x + 2);
+                    } else {
+                        tr = 0;
+                    }
+                }
+                const uint32_t TRv = tr;
+                if (row_ok && x >= 0 && x < w) {
+                    const uint32_t res = row[x];
+                    uint32_t pred;
+                    if (y == 0) pred = x == 0 ? 0xff000000u : L;          // top row: left; first pixel: opaque black
+                    else if (x == 0) pred = T;                              // left column: top
+                    else {
+                        const int mode = (int)((mrow[x >> S.bits] >> 8) & 0xffu);
+                        // the last column's top-right is the first pixel of the CURRENT row (memory order, 3 | 108-116)
+                        pred = mode < 14 ? predict(mode, L, T, TL, x == w - 1 ? first : TRv) : 0u;
+                        if (mode >= 14) pred = 0u;  // the reference leaves such pixels as they are
+                    }
+                    mine = add4(res, pred);
+                    orow[x] = mine;
+                    if (x == 0) first = mine;
+                    L = mine;
+                    if (hands) st_unit(below + x, mine, tag_out);
+                }
+                // shift the pipeline: next step's top-left = this step's top, top = this step's top-right
+                TL = T;
+                T = TRv;
+            }
+        }
+    }
+}
+
+__global__ void k_vp8l_green(Vp8lBatch B) {
+    const Vp8lPlane& P = B.planes[blockIdx.y];
+    const size_t n = (size_t)P.width * P.height;
+    const uint32_t* im = B.pixels + P.buf_off[buffer_before((int)P.n_stages)];
+    uint8_t* a = B.alpha + P.alpha_off;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) a[i] = (uint8_t)(im[i] >> 8);
+}
+
+}  // namespace
+
+cudaError_t launch_vp8l_inverse(const Vp8lBatch& b, cudaStream_t s, int* launches) {
+    if (b.n_planes <= 0) return cudaSuccess;
+    const unsigned bands = ((b.max_height + 31) >> 5) * (unsigned)b.n_planes;
+    const unsigned want = (bands + kWarps - 1) / kWarps;
+    const unsigned grid = want < (unsigned)b.sm_count * 8u ? want : (unsigned)b.sm_count * 8u;
+    for (int st = 0; st < b.max_stages; st++) {
+        cudaError_t e = cudaMemsetAsync(b.ticket, 0, 4, s);
+        if (e != cudaSuccess) return e;
+        StageArgs a;
+        a.b = b;
+        a.stage = st;
+        k_vp8l_stage<<<grid ? grid : 1, kWarps * 32, 0, s>>>(a);
+        ++*launches;
+    }
+    k_vp8l_green<<<dim3(b.sm_count * 2, b.n_planes), 256, 0, s>>>(b);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace webpb200

@@ -299,3 +299,55 @@ def test_batch_split_over_contexts(W, oracle, synth, fixtures):
         assert np.array_equal(outs[i], oracle.WebPDecoder(f).read_image()), i
     for c in ctxs:
         c.close()
+
+
+@pytest.mark.parametrize("size", [(37, 23), (1, 9), (9, 1), (200, 31), (64, 48), (131, 77), (33, 70)])
+def test_vp8l_alpha_transforms_on_device(W, bd, oracle, synth, size):
+    """VP8L-compressed ALPH planes: prefix codes on the host, inverse transforms on the device (vp8l.cu) --
+    predictor (all fourteen modes, block sizes 2..5), colour, subtract-green, colour indexing with 1, 2 and 4
+    bit packing and without, alone and chained, with every alpha filter; every pixel against the oracle
+    (reverse_transform.rs:24-578, extended.rs:131-191, 284-294)."""
+    from harness import vp8l_writer as V
+    w, h = size
+    rng = np.random.default_rng(w * 1000 + h)
+    alpha = synth.smooth_alpha(w, h, 3)
+    few = (rng.integers(0, 4, (h, w)) * 85).astype(np.uint8)
+
+    def pal(a, flt):
+        res = np.frombuffer(synth.alph_raw(a, filtering=flt)[9:9 + a.size], np.uint8)
+        return 0xff000000 | (np.unique(res).astype(np.uint32) << 8)
+
+    def blocks(bits, hi, lo=0, last=None):
+        shape = (V.subsample(h, bits), V.subsample(w, bits)) + (() if last is None else (last,))
+        return rng.integers(lo, hi, shape)
+
+    cases = [(alpha, 0, ()), (alpha, 1, (("predictor", 2, blocks(2, 14)),)), (alpha, 2, (("predictor", 5, blocks(5, 14)),)),
+             (alpha, 3, (("subtract_green",), ("predictor", 3, 11))), (alpha, 0, (("color", 2, blocks(2, 128, -128, 3)), ("predictor", 4, 12))),
+             (alpha, 1, (("predictor", 3, 13), ("color", 3, (5, -7, 100)), ("subtract_green",))),
+             (few, 0, (("palette", pal(few, 0)),)), (few, 2, (("palette", pal(few, 2)), ("predictor", 2, 11))),
+             ((few > 100).astype(np.uint8) * 255, 0, (("palette", pal((few > 100).astype(np.uint8) * 255, 0)),)),
+             (alpha, 3, (("palette", pal(alpha, 3)), ("predictor", 4, 5)))]
+    files = []
+    for k, (a, flt, tr) in enumerate(cases):
+        vp8 = synth.vp8_frame(w, h, seed=900 + k, filter_type=k % 2, filter_level=15)
+        files.append(synth.webp_extended(vp8, w, h, synth.chunk(b"ALPH", V.alph_chunk_payload(a, flt, tr))))
+    for where in (bd.ENTROPY_HOST, bd.ENTROPY_DEVICE):
+        bd.set_entropy(where)
+        outs, status = bd.decode(files)
+        assert status == [0] * len(files)
+        for k, f in enumerate(files):
+            want = oracle.WebPDecoder(f).read_image()
+            assert np.array_equal(outs[k], want), (where, k)
+            assert np.array_equal(W.WebPDecoder(f).read_image(), want), k
+    bd.set_entropy(bd.ENTROPY_AUTO)
+    # a repeated device-resident pass gives the same bytes (the uploaded pixels are never written by a kernel)
+    bd.prepare(files)
+    bd.upload()
+    for _ in range(2):
+        bd.reconstruct(15)
+    bd.sync()
+    again = [oracle.WebPDecoder(f).read_image() for f in files]
+    outs2 = [np.zeros_like(a) for a in again]
+    bd.download([o.reshape(-1) for o in outs2])
+    for a, b in zip(again, outs2):
+        assert np.array_equal(a, b)
