@@ -24,10 +24,22 @@ struct Bits {  // LSB-first bit reader (decoder/mod.rs:697-774)
     const uint8_t* end;
     uint64_t acc = 0;
     int n = 0;
+    // BitReader::fill with the reference's exact bookkeeping (decoder/mod.rs:718-738): with 8 or more bytes left a
+    // 64-bit lookahead is ORed in, the position moves by (63 - n) / 8 bytes and n |= 56; otherwise byte by byte
+    // while n < 56.  So 56..63 bits count as available after a fill -- which decides what the reference REJECTS:
+    // a backward reference can need 58 bits (15 + 10 + 15 + 18) and get_copy_distance (619-633) does not refill.
     void fill() {
-        while (n <= 56 && p < end) {
-            acc |= (uint64_t)*p++ << n;
-            n += 8;
+        if (end - p >= 8) {
+            uint64_t look;
+            std::memcpy(&look, p, 8);  // little-endian host
+            p += (63 - n) / 8;
+            acc |= look << n;
+            n |= 56;
+        } else {
+            while (p < end && n < 56) {
+                acc |= (uint64_t)*p++ << n;
+                n += 8;
+            }
         }
     }
     bool drop(int k) {
@@ -276,9 +288,8 @@ struct Decoder {
                 size_t length, dcode;
                 if (!copy_value(s - 256, &length)) return WEBPB200_ERR_BITSTREAM;
                 uint32_t ds;
-                // a length code and its extra bits may have used 25 of the 57 bits fill() guarantees; the
-                // distance code and its extra bits can need 33 more
-                if (br.n < 33) br.fill();
+                // (no refill here: the reference has none either, decoder/mod.rs:536-541, so a reference that needs
+                // more bits than one fill left is a BitStreamError there and here)
                 NEED(g->c[4].get(br, &ds));
                 if (!copy_value(ds, &dcode)) return WEBPB200_ERR_BITSTREAM;
                 size_t dist;

@@ -19,10 +19,22 @@ typedef struct {
     uint64_t buffer; int nbits;
 } bitrd;
 
-static void br_fill(bitrd* b) { /* 718-738: ends with >= 56 bits unless input is exhausted */
-    while (b->nbits <= 56 && b->pos < b->len) {
-        b->buffer |= (uint64_t)b->p[b->pos++] << b->nbits;
-        b->nbits += 8;
+/* fill, 718-738, with the reference's exact bookkeeping: with 8 or more bytes left it ORs a 64-bit lookahead in,
+ * advances by (63 - nbits) / 8 bytes and sets nbits |= 56 (so 56..63 bits count as available, although more are
+ * in the buffer); otherwise byte by byte while nbits < 56.  It matters for what the reference REJECTS: a backward
+ * reference may need 58 bits (15 + 10 + 15 + 18) between two fills and get_copy_distance (619-633) does not refill. */
+static void br_fill(bitrd* b) {
+    if (b->len - b->pos >= 8) {
+        uint64_t look = 0;
+        for (int i = 7; i >= 0; i--) look = (look << 8) | b->p[b->pos + i];
+        b->pos += (size_t)((63 - b->nbits) / 8);
+        b->buffer |= look << b->nbits;
+        b->nbits |= 56;
+    } else {
+        while (b->pos < b->len && b->nbits < 56) {
+            b->buffer |= (uint64_t)b->p[b->pos++] << b->nbits;
+            b->nbits += 8;
+        }
     }
 }
 static uint64_t br_peek(const bitrd* b, int n) { return b->buffer & (((uint64_t)1 << n) - 1); }

@@ -241,3 +241,47 @@ def test_return_code_signs(W):
     assert W.lib().webpb200_open(junk.ctypes.data, junk.size, 0, C.byref(h)) == 2          # positive: RIFF signature
     assert W.lib().webpb200_decode_batch(None, None, None, 0, None, None, None, 0, 1) == -100  # negative: no context
     assert W.lib().webpb200_decode_animation(None, None, 0, None, 0, None, 0, 0, 1) == -100
+
+
+def test_vp8l_longest_backward_reference(W, oracle, synth):
+    """A backward reference whose length and distance symbols both have 15-bit codes and the most extra bits
+    (10 and 18) needs 58 bits in one go.  The reference's bit reader counts 56..63 bits as available after a
+    fill (`nbits |= 56`, decoder/mod.rs:718-738) and get_copy_distance (619-633) does not refill, so the
+    reference decodes such a stream at most bit alignments and answers BitStreamError at the others.  Oracle and product follow it in both: same verdict at every alignment, same pixels where it decodes."""
+    from harness import vp8l_writer as V
+    w, h = 2048, 640
+    n = w * h
+    # explicit code lengths: a complete code 1, 2, ..., 14, 15, 15 over 16 symbols, the two symbols of interest at 15 bits
+    green = [0] * 280
+    for k, sym in enumerate([0, 7] + list(range(8, 21)) + [256 + 23]):
+        green[sym] = min(k + 1, 15)
+    distl = [0] * 40
+    for k, sym in enumerate(list(range(0, 15)) + [39]):
+        distl[sym] = min(k + 1, 15)
+    length, dist = 4096, 1_048_456                   # length prefix 23 (10 extra bits), distance code prefix 39 (18 extra bits)
+    vp8 = synth.vp8_frame(w, h, seed=3, filter_level=0)
+    verdicts = []
+    for shift in range(8):                            # the reference lands on every bit alignment of the reader's window
+        rng = np.random.default_rng(5)
+        g = rng.integers(0, 2, n).astype(np.uint32) * 7
+        pos = 1_100_000 + shift
+        g[pos - 8:pos] = 0                            # one-bit literals right before it: `shift` moves the bit position by one each
+        g[pos:pos + length] = g[pos - dist:pos - dist + length]
+        stream = V.encode((0xff000000 | (g << 8)).reshape(h, w), header=False, refs=[(pos, length, dist + 120)], force_lengths={0: green, 4: distl})
+        payload = bytes([1]) + stream                 # ALPH header: compression 1, no filter
+        f = synth.webp_extended(vp8, w, h, synth.chunk(b"ALPH", payload))
+        want = np.zeros((h, w), np.uint8)
+        flt = C.c_int()
+        ch = np.frombuffer(payload, np.uint8)
+        a = oracle.lib().ora_read_alpha_chunk(ch.ctypes.data, ch.size, w, h, want.ctypes.data, C.byref(flt))
+        try:
+            fd, mbs, levels, alpha = W.host_entropy_decode(f)
+            b = 0
+        except W.DecodingError as e:
+            b = e.code
+        assert a == b, shift
+        verdicts.append(a)
+        if a == 0:
+            assert np.array_equal(want.reshape(-1), g.astype(np.uint8))
+            assert np.array_equal(alpha.reshape(-1), want.reshape(-1)), shift
+    assert sorted(set(verdicts)) == [0, 9], verdicts  # both happen; which alignments fail follows from the bits left over before the fill
