@@ -950,7 +950,24 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
             const int mbedge = (level + 2) * 2 + interior, subedge = level * 2 + interior;
             __syncwarp();
 
+            // The previous macroblock's bottom 4 rows are final as soon as this macroblock's LEFT edge has been
+            // filtered (nothing after that touches the previous panel): they go into the edge record right then,
+            // not at the end of the step, which takes most of a step off the lag between consecutive rows.
+            auto hand_prev = [&]() {
+                if (mbx == 0 || !hand_down) return;
+                if (lane >= 16 && lane < 20) {
+                    const uint4 prv = ytile[0];
+                    uint2* r = yedge + (size_t)(mbx - 1) * 32;
+                    st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine); st_edge(r + 2, prv.z, tag_mine); st_edge(r + 3, prv.w, tag_mine);
+                }
+                if (clane && crow >= 8) {
+                    const uint2 prv = ctile[0];
+                    uint2* r = cedge + (size_t)(mbx - 1) * 32;
+                    st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine);
+                }
+            };
             // ---- loop_filter, mod.rs:966-1188: four edge groups in the reference's order ----
+            if (level == 0) hand_prev();
             if (level > 0) {
                 uint8_t* const y0 = S.y + 4 * 32 + 16;  // pixel (0, 0) of the current macroblock
                 if (simple) {
@@ -960,6 +977,7 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                     if (e0 == 0 ? mbx > 0 : do_sub) lf_line(y0 + r * 32 + 4 * e0, 1, 0, e0 == 0 ? mbedge : subedge, 0, 0);
                     if (do_sub) lf_line(y0 + r * 32 + 4 * e0 + 4, 1, 0, subedge, 0, 0);
                     __syncwarp();
+                    hand_prev();
                     if (e0 == 0 ? mby > 0 : do_sub) lf_line(y0 + (4 * e0) * 32 + r, 32, 0, e0 == 0 ? mbedge : subedge, 0, 0);
                     if (do_sub) lf_line(y0 + (4 * e0 + 4) * 32 + r, 32, 0, subedge, 0, 0);
                     __syncwarp();
@@ -971,6 +989,7 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                     else { base = S.c[(lane - 16) >> 3] + 4 * 16 + 8; st_row = 16; idx = (lane - 16) & 7; }
                     if (mbx > 0) lf_line(base + idx * st_row, 1, 2, mbedge, interior, hev_thr);
                     __syncwarp();
+                    hand_prev();
                     if (do_sub) {
                         lf_line(base + idx * st_row + 4, 1, 1, subedge, interior, hev_thr);
                         __syncwarp();
@@ -1002,11 +1021,7 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                     if (lane < 16 || !hand_down) {
                         if (mbx > 0) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16 - 16) = prv;
                         if (last) *reinterpret_cast<uint4*>(yrow + (size_t)mbx * 16) = cur;
-                    } else {
-                        if (mbx > 0) {
-                            uint2* r = yedge + (size_t)(mbx - 1) * 32;
-                            st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine); st_edge(r + 2, prv.z, tag_mine); st_edge(r + 3, prv.w, tag_mine);
-                        }
+                    } else {  // (the previous panel's went out right after the left edge, see hand_prev)
                         if (last) {
                             uint2* r = yedge + (size_t)mbx * 32;
                             st_edge(r, cur.x, tag_mine); st_edge(r + 1, cur.y, tag_mine); st_edge(r + 2, cur.z, tag_mine); st_edge(r + 3, cur.w, tag_mine);
@@ -1023,10 +1038,6 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
                         if (mbx > 0) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8 - 8) = prv;
                         if (last) *reinterpret_cast<uint2*>(crow_ptr + (size_t)mbx * 8) = cur;
                     } else {
-                        if (mbx > 0) {
-                            uint2* r = cedge + (size_t)(mbx - 1) * 32;
-                            st_edge(r, prv.x, tag_mine); st_edge(r + 1, prv.y, tag_mine);
-                        }
                         if (last) {
                             uint2* r = cedge + (size_t)mbx * 32;
                             st_edge(r, cur.x, tag_mine); st_edge(r + 1, cur.y, tag_mine);
