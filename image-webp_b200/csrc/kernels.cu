@@ -360,7 +360,13 @@ struct PredictArgs {
 // keeps every resident warp busy (many images: issue-bound).  kMinBlocks = 2 (128 registers, 16 warps per SM)
 // has fewer instructions on each macroblock's dependency chain and is the fast one when the rows of a few
 // large frames wait on each other (latency-bound): cfg3 2.56 -> 1.85 ms, cfg2 0.93 -> 1.02 ms.
-constexpr int kPredictBlocksThroughput = 3, kPredictBlocksLatency = 2;
+#ifndef PREDICT_BLOCKS_T
+#define PREDICT_BLOCKS_T 3
+#endif
+#ifndef PREDICT_BLOCKS_L
+#define PREDICT_BLOCKS_L 2
+#endif
+constexpr int kPredictBlocksThroughput = PREDICT_BLOCKS_T, kPredictBlocksLatency = PREDICT_BLOCKS_L;
 
 // Level records.  Dense (the boundary format of include/webpb200.h, what the host entropy decoder and
 // webpb200_reconstruct_device callers supply): block b of a macroblock at b * 32 bytes of its 800-byte record.

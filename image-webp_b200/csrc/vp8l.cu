@@ -39,23 +39,26 @@ __device__ __forceinline__ uint32_t select4(uint32_t l, uint32_t t, uint32_t tl)
     return __vsadu4(t, tl) < __vsadu4(l, tl) ? l : t;
 }
 
-__device__ __forceinline__ uint32_t predict(int mode, uint32_t L, uint32_t T, uint32_t TL, uint32_t TR) {
-    switch (mode) {
-        case 0: return 0xff000000u;
-        case 1: return L;
-        case 2: return T;
-        case 3: return TR;
-        case 4: return TL;
-        case 5: return avg4(avg4(L, TR), T);
-        case 6: return avg4(L, TL);
-        case 7: return avg4(L, T);
-        case 8: return avg4(TL, T);
-        case 9: return avg4(T, TR);
-        case 10: return avg4(avg4(L, TL), avg4(T, TR));
-        case 11: return select4(L, T, TL);
-        case 12: return clamp_full(L, T, TL);
-        default: return clamp_half(L, T, TL);  // 13
-    }
+// The fourteen predictors (reverse_transform.rs:79-351).  The lanes of a warp sit in different blocks of the
+// predictor image (their columns are skewed), so a `switch` on the mode would run every case that occurs, one
+// after the other (measured: 2400 cycles per step on random modes); instead the candidates are computed
+// straight-line (they share their averages) and the mode picks one.
+__device__ __forceinline__ uint32_t predict_mixed(int mode, uint32_t L, uint32_t T, uint32_t TL, uint32_t TR) {
+    const uint32_t a_l_tl = avg4(L, TL), a_t_tr = avg4(T, TR);
+    uint32_t p = 0xff000000u;                       // 0
+    p = mode == 1 ? L : p;
+    p = mode == 2 ? T : p;
+    p = mode == 3 ? TR : p;
+    p = mode == 4 ? TL : p;
+    p = mode == 5 ? avg4(avg4(L, TR), T) : p;
+    p = mode == 6 ? a_l_tl : p;
+    p = mode == 7 ? avg4(L, T) : p;
+    p = mode == 8 ? avg4(TL, T) : p;
+    p = mode == 9 ? a_t_tr : p;
+    p = mode == 10 ? avg4(a_l_tl, a_t_tr) : p;
+    p = mode == 11 ? select4(L, T, TL) : p;
+    if (mode >= 12) p = mode == 12 ? clamp_full(L, T, TL) : clamp_half(L, T, TL);  // the two per-channel ones: rarer, kept behind a branch
+    return p;
 }
 
 __device__ __forceinline__ uint2 ld_unit(const uint2* p) {
@@ -82,7 +85,11 @@ __device__ __forceinline__ int buffer_before(int s) { return s == 0 ? 0 : 1 + ((
 //   {pixel, tag}, the same protocol as the macroblock wavefront's edge records), the band's last row writes them.
 //   colour / subtract-green / palette: the warp sweeps its 32 rows, lanes along x.
 __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
+    // predictor stage: per lane (= row) a ring of 16 residuals, filled 8 at a time one block of 8 ahead of use
+    // (17-word rows: lanes fall into different banks)
+    __shared__ uint32_t s_res[kWarps][32][17];
     const int lane = threadIdx.x & 31;
+    uint32_t* const ring = s_res[threadIdx.x >> 5][lane];
     const Vp8lBatch& B = A.b;
     const int s = A.stage;
     const unsigned max_bands = (B.max_height + 31) >> 5;
@@ -106,9 +113,15 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
             for (int r = 0; r < rows; r++) {
                 const uint32_t* row = im + (size_t)(y0 + r) * w;
                 uint32_t* orow = om + (size_t)(y0 + r) * w;
-                for (int x = lane; x < w; x += 32) {
-                    const uint32_t p = row[x], gg = (p >> 8) & 0xffu;
-                    orow[x] = (p & 0xff00ff00u) | (((p & 0x00ff00ffu) + (gg << 16 | gg)) & 0x00ff00ffu);
+                for (int x0 = lane; x0 < w; x0 += 128) {
+                    uint32_t p[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) p[k] = x0 + 32 * k < w ? row[x0 + 32 * k] : 0u;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const uint32_t gg = (p[k] >> 8) & 0xffu;
+                        if (x0 + 32 * k < w) orow[x0 + 32 * k] = (p[k] & 0xff00ff00u) | (((p[k] & 0x00ff00ffu) + (gg << 16 | gg)) & 0x00ff00ffu);
+                    }
                 }
             }
         } else if (S.kind == VP8L_COLOR) {  // apply_color_transform, 353-391
@@ -118,8 +131,15 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                 const uint32_t* row = im + (size_t)y * w;
                 uint32_t* orow = om + (size_t)y * w;
                 const uint32_t* mrow = data + (size_t)(y >> S.bits) * bx;
-                for (int x = lane; x < w; x += 32) {
-                    const uint32_t m = mrow[x >> S.bits], p = row[x];
+                for (int x0 = lane; x0 < w; x0 += 128) {
+                  uint32_t pp[4];
+#pragma unroll
+                  for (int k = 0; k < 4; k++) pp[k] = x0 + 32 * k < w ? row[x0 + 32 * k] : 0u;
+#pragma unroll
+                  for (int k = 0; k < 4; k++) {
+                    const int x = x0 + 32 * k;
+                    if (x >= w) break;
+                    const uint32_t m = mrow[x >> S.bits], p = pp[k];
                     const int g2r = (int)(int8_t)(m & 0xff), g2b = (int)(int8_t)((m >> 8) & 0xff), r2b = (int)(int8_t)((m >> 16) & 0xff);
                     const int gg = (int)(int8_t)((p >> 8) & 0xff);
                     int rr = (int)((p >> 16) & 0xff), bb = (int)(p & 0xff);
@@ -127,6 +147,7 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                     bb = (bb + ((g2b * gg) >> 5)) & 0xff;
                     bb = (bb + ((r2b * (int)(int8_t)rr) >> 5)) & 0xff;
                     orow[x] = (p & 0xff00ff00u) | ((uint32_t)rr << 16) | (uint32_t)bb;
+                  }
                 }
             }
         } else if (S.kind == VP8L_PALETTE) {  // apply_color_indexing_transform, 400-578: into the other buffer
@@ -136,10 +157,17 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
             for (int r = 0; r < rows; r++) {
                 const uint32_t* row = im + (size_t)(y0 + r) * w;
                 uint32_t* orow = out + (size_t)(y0 + r) * W;
-                for (int x = lane; x < W; x += 32) {
-                    const int byte = (int)((row[x >> pack] >> 8) & 0xffu);
-                    const int k = (byte >> ((x & ((1 << pack) - 1)) * bpe)) & mask;
-                    orow[x] = k < n ? data[k] : 0u;
+                for (int x0 = lane; x0 < W; x0 += 128) {
+                    uint32_t q[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) q[k] = x0 + 32 * k < W ? row[(x0 + 32 * k) >> pack] : 0u;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int x = x0 + 32 * j;
+                        if (x >= W) break;
+                        const int k = ((int)((q[j] >> 8) & 0xffu) >> ((x & ((1 << pack) - 1)) * bpe)) & mask;
+                        orow[x] = k < n ? data[k] : 0u;
+                    }
                 }
             }
         } else {  // predictor transform, apply_predictor_transform 24-78 + the fourteen predictors 79-351
@@ -175,6 +203,23 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                 T = wait_unit(above, ld_unit(above));
                 if (w > 1) nxt = ld_unit(above + 1);
             }
+            // residuals: block b (columns 8b..8b+7) of my row sits in the ring while it is used, block b + 1 is in
+            // flight in `ahead` and is put into the ring when block b + 1 begins, block b + 2 is requested then
+            uint32_t ahead[8];
+            auto load8 = [&](int xb) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) ahead[k] = (row_ok && xb + k < w) ? row[xb + k] : 0u;
+            };
+            auto store8 = [&](int xb) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) ring[(xb + k) & 15] = ahead[k];
+            };
+            load8(0);
+            store8(0);
+            load8(8);
+            // predictor mode of my row's current block and of the next one
+            uint32_t mode_w = mrow[0], mode_next = bx > 1 ? mrow[1] : 0u;
+            const int bmask = (1 << S.bits) - 1;
             const int steps = w + 2 * 31;
             for (int i = 0; i < steps; i++) {
                 // top-right of my column: what the lane above finished in the previous step (its column x + 1)
@@ -190,14 +235,23 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                 }
                 const uint32_t TRv = tr;
                 if (row_ok && x >= 0 && x < w) {
-                    const uint32_t res = row[x];
+                    if ((x & 7) == 0 && x > 0) {
+                        store8(x);
+                        load8(x + 8);
+                    }
+                    if ((x & bmask) == 0 && x > 0) {
+                        mode_w = mode_next;
+                        const int nb = (x >> S.bits) + 1;
+                        mode_next = nb < bx ? mrow[nb] : 0u;
+                    }
+                    const uint32_t res = ring[x & 15];
                     uint32_t pred;
                     if (y == 0) pred = x == 0 ? 0xff000000u : L;          // top row: left; first pixel: opaque black
                     else if (x == 0) pred = T;                              // left column: top
                     else {
-                        const int mode = (int)((mrow[x >> S.bits] >> 8) & 0xffu);
+                        const int mode = (int)((mode_w >> 8) & 0xffu);
                         // the last column's top-right is the first pixel of the CURRENT row (memory order, 3 | 108-116)
-                        pred = mode < 14 ? predict(mode, L, T, TL, x == w - 1 ? first : TRv) : 0u;
+                        pred = predict_mixed(mode, L, T, TL, x == w - 1 ? first : TRv);
                         if (mode >= 14) pred = 0u;  // the reference leaves such pixels as they are
                     }
                     mine = add4(res, pred);

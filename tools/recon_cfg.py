@@ -1,13 +1,13 @@
 #!/usr/bin/env python3
 """Device-resident reconstruct pass of one BASELINE configuration: per-kernel CUDA-event times.
-usage: tools/recon_cfg.py cfg2|cfg2u|cfg3|cfg4 [n_images] [iters]
+usage: tools/recon_cfg.py cfg2|cfg2u|cfg3|cfg4|cfg4c [n_images] [iters]
 Also the command that is run under ncu for the per-configuration captures in profiles/."""
 import importlib, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 W = importlib.import_module("image-webp_b200")
 from harness import synth as S
 
-DEFAULT_N = {"cfg2": 1024, "cfg2u": 1024, "cfg3": 32, "cfg4": 64}
+DEFAULT_N = {"cfg2": 1024, "cfg2u": 1024, "cfg3": 32, "cfg4": 64, "cfg4c": 64}
 
 
 def files_for(cfg, n, threads):
@@ -19,6 +19,9 @@ def files_for(cfg, n, threads):
         return S.make_batch(S.cfg3_image, n, threads=threads)
     if cfg == "cfg4":
         return S.make_batch(S.cfg4_image, n, threads=threads)
+    if cfg == "cfg4c":  # VP8L-compressed ALPH (harness/configs.py), as bench.py's cfg4
+        from harness import configs
+        return configs.cfg4_batch(0, n, threads=threads)
     raise SystemExit("unknown configuration " + cfg)
 
 
