@@ -349,27 +349,28 @@ def main():
     h2d_bytes, d2h_bytes, entropy_where = bd.last_transfer()
     entropy_ms = bd.last_entropy_ms()
     serial_ms = e2e_ms
-    # the same steps with TWO in flight (webpb200_decode_batch_begin / _end on two contexts of this GPU): a step's
+    # the same steps with several in flight (webpb200_decode_batch_begin / _end on as many contexts of this GPU): a step's
     # k_entropy is one dependency chain per frame and leaves issue slots idle, the next step's chains fill them
     # while this step's bands reconstruct and download.  Every step still uploads its inputs from pinned memory
     # and downloads its 805 MB of pixels inside the timed region.
-    bd2 = W.BatchDecoder(local_rank)
-    pin2 = W.PinnedBuffer(out_bytes)
-    outs2 = [pin2.array[i * per:(i + 1) * per] for i in range(per_gpu)]
-    out_list2 = W.BufferList(outs2)
-    slots = [(bd, out_list), (bd2, out_list2)]
-    for b_, o_ in slots:  # warm-up, also sizes bd2's arenas
+    in_flight = max(2, int(os.environ.get("WEBPB200_BENCH_IN_FLIGHT", "2")))
+    extra_ctx = [W.BatchDecoder(local_rank) for _ in range(in_flight - 1)]
+    extra_pin = [W.PinnedBuffer(out_bytes) for _ in range(in_flight - 1)]
+    slots = [(bd, out_list)]
+    for b_, p_ in zip(extra_ctx, extra_pin):
+        slots.append((b_, W.BufferList([p_.array[i * per:(i + 1) * per] for i in range(per_gpu)])))
+    for b_, o_ in slots:  # warm-up, also sizes the new contexts' arenas
         b_.decode(file_list, outs=o_, host_threads=host_threads)
     sh.barrier(dist)
-    pipe_steps = 2 * e2e_steps
-    pending = [None, None]
+    pipe_steps = in_flight * e2e_steps
+    pending = [None] * in_flight
     t0 = time.perf_counter()
     for k in range(pipe_steps):
-        b_, o_ = slots[k % 2]
-        if pending[k % 2] is not None:
-            st = b_.decode_end(pending[k % 2])
-        pending[k % 2] = b_.decode_begin(file_list, o_, host_threads=host_threads)
-    for k in range(2):
+        b_, o_ = slots[k % in_flight]
+        if pending[k % in_flight] is not None:
+            st = b_.decode_end(pending[k % in_flight])
+        pending[k % in_flight] = b_.decode_begin(file_list, o_, host_threads=host_threads)
+    for k in range(in_flight):
         st2 = slots[k][0].decode_end(pending[k])
         assert all(s == 0 for s in st2)
     e2e_ms = 1e3 * (time.perf_counter() - t0) / pipe_steps
@@ -448,7 +449,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "MPix/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "entropy_stage": "k_entropy on the GPU (compressed chunks cross PCIe)" if entropy_where == "device" else "host threads (packed levels cross PCIe)",
                     "k_entropy_ms": entropy_ms, "ms_per_step": e2e_max_ms, "steps": pipe_steps if pipelined else e2e_steps, "host_threads": host_threads,
-                    "in_flight": 2 if pipelined else 1,
+                    "in_flight": in_flight if pipelined else 1,
                     "one_call_at_a_time": {"ms_per_step": serial_ms, "value": px / (serial_ms / 1e3) / 1e6, "note": "rank 0, webpb200_decode_batch called back to back"},
                     "numa_bound_cpus": len(near) if near else None, "numa_note": numa_note(),
                     "d2h_ceiling_ms": d2h_ceiling_ms, "frac_of_d2h_ceiling": d2h_ceiling_ms / e2e_max_ms,
@@ -469,8 +470,10 @@ def main():
             line["other_configs"] = other
         print(json.dumps(line), flush=True)
     pin.free()
-    pin2.free()
-    bd2.close()
+    for p_ in extra_pin:
+        p_.free()
+    for b_ in extra_ctx:
+        b_.close()
     bd.close()
     if dist is not None:
         dist.destroy_process_group()
