@@ -423,6 +423,19 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
     const uint32_t* const bottom_src = lane < 4 ? yw32 + 16 * 8 + 1 + lane : lane < 6 ? uw32 + 8 * 4 + (lane - 3) : vw32 + 8 * 4 + (lane - 5);
     uint8_t* const lb_dst = lane < 16 ? S.yw + (1 + lane) * 32 + 3 : lane < 24 ? S.uw + (lane - 15) * 16 + 3 : S.vw + (lane - 23) * 16 + 3;
     const int lb_gap = lane < 16 ? 16 : 8;  // right column = left border + gap
+    // B_PRED per-lane constants: half-warp, pixel inside a sub-block, the edge pixel summed for B_DC; `_h` = as seen
+    // from the half-warp's own sub-block of a two-sub-block step (the lower one sits 4 rows down, 2 sub-blocks left)
+    const int bp_half = lane >> 4, bp_p = lane & 15;
+    const int bp_pixoff = (bp_p >> 2) * 32 + (bp_p & 3);
+    const int bp_dcoff = (bp_p & 4) ? (bp_p & 3) * 32 - 1 : (bp_p & 3) - 32;
+    const uint8_t* const bp_yw_h = S.yw + bp_half * 120;
+    const uint8_t* const bp_dc = S.yw + bp_dcoff;
+    const uint8_t* const bp_dc_h = bp_yw_h + bp_dcoff;
+    uint8_t* const bp_pix = S.yw + bp_pixoff;
+    uint8_t* const bp_pix_h = S.yw + bp_half * 120 + bp_pixoff;
+    const int16_t* const bp_res = &S.res[0][0] + bp_p;
+    const int16_t* const bp_res_h = bp_res + bp_half * 32;
+    const uint32_t* const bp_tab = s_bpred + bp_p;
 
     for (;;) {
         unsigned int t = 0;
@@ -625,33 +638,34 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
             // ---- luma ----
             if (ymode == 4) {
                 // predict_4x4 (prediction.rs:159-183) as a 10-step sx + 2*sy wavefront over the
-                // 16 sub-blocks; half-warp h works on sub-block row sy_lo + h, one lane per pixel
-                const int half = lane >> 4, p = lane & 15;
-                const int pix = (p >> 2) * 32 + (p & 3);                            // my pixel inside a sub-block
-                const int dcoff = (p & 4) ? (p & 3) * 32 - 1 : (p & 3) - 32;       // the edge pixel I add up for B_DC
+                // 16 sub-blocks; half-warp h works on sub-block row sy_lo + h, one lane per pixel.
+                // Everything that depends on the lane only (which half, which pixel) is folded into
+                // base pointers once (bp_*), so that a step's addresses are constants off those.
                 const unsigned long long bp = ((unsigned long long)bpred_hi << 32) | bpred_lo;
+                const unsigned long long bph = bp >> (8 * bp_half);  // the lower sub-block of a two-sub-block step is 2 further on
 #pragma unroll kBpredUnroll
                 for (int s = 0; s < 10; s++) {
                     // steps with a single sub-block (0, 1, 8, 9): both half-warps compute it and store
                     // the same bytes, which keeps the step free of divergence
                     const int sy_lo = s < 2 ? 0 : (s - 2) >> 1, sy_hi = (s >> 1) < 3 ? (s >> 1) : 3;
-                    const int sy = sy_hi > sy_lo ? sy_lo + half : sy_lo, sx = s - 2 * sy;
-                    const int sb = sy * 4 + sx;
-                    const int mode = (int)(bp >> (4 * sb)) & 15;
-                    const int org = (1 + 4 * sy) * 32 + 4 + 4 * sx;
+                    const bool two = sy_hi > sy_lo;
+                    const int sx = s - 2 * sy_lo, sb = sy_lo * 4 + sx;  // the upper (or only) sub-block; the lower one: sb + 2
+                    const int org = (1 + 4 * sy_lo) * 32 + 4 + 4 * sx;  // ... its origin; the lower one: + 4 * 32 - 8
+                    const uint8_t* const ew = two ? bp_yw_h : S.yw;     // workspace seen from my sub-block
+                    const int mode = (int)((two ? bph : bp) >> (4 * sb)) & 15;
                     // B_DC, predict_bdcpred prediction.rs:271-288: lanes p and p^8 hold the same edge pixel
-                    int dc = S.yw[org + dcoff];
+                    int dc = (two ? bp_dc_h : bp_dc)[org];
                     dc += __shfl_xor_sync(kFull, dc, 1);
                     dc += __shfl_xor_sync(kFull, dc, 2);
                     dc += __shfl_xor_sync(kFull, dc, 4);
-                    const uint32_t w = s_bpred[mode * 16 + p];
-                    const int a = S.yw[org + (int)(int8_t)(w & 0xff)];
-                    const int b = S.yw[org + (int)(int8_t)((w >> 8) & 0xff)];
-                    const int cc = S.yw[org + (int)(int8_t)((w >> 16) & 0xff)];
+                    const uint32_t w = bp_tab[mode * 16];
+                    const int a = ew[org + (int)(int8_t)(w & 0xff)];
+                    const int b = ew[org + (int)(int8_t)((w >> 8) & 0xff)];
+                    const int cc = ew[org + (int)(int8_t)((w >> 16) & 0xff)];
                     int pred = (w >> 24) ? clamp255(a + b - cc) : (a + 2 * b + cc + 2) >> 2;
                     if (mode == 0) pred = (dc + 4) >> 3;
-                    const int r = res[sb * 16 + p];
-                    S.yw[org + pix] = (uint8_t)clamp255(pred + r);  // add_residue
+                    const int r = (two ? bp_res_h : bp_res)[(mbx & 1) * (24 * 16) + sb * 16];
+                    (two ? bp_pix_h : bp_pix)[org] = (uint8_t)clamp255(pred + r);  // add_residue
                     __syncwarp();
                 }
             } else {
