@@ -7,10 +7,12 @@
  *   src/lossy/prediction.rs, src/lossy/loop_filter.rs, src/lossy/yuv.rs.
  * Parity pinned on the reference's golden images (see ora.h).
  */
+#define _POSIX_C_SOURCE 200809L
 #include "ora.h"
 #include "vp8_tables.h"
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 /* ------------------------------------------------------------------------------------
  * Boolean decoder.  arithmetic_decoder.rs:39-320.  The reference loads 4 bytes at a time
@@ -979,6 +981,19 @@ void ora_frame_free(ora_frame* f) {
 }
 
 /* decode_frame_, mod.rs:1252-1297 */
+/* Optional per-stage wall-clock split of the CPU baseline (bench.py): when ora_stage_timing is set, every decode
+ * adds its nanoseconds to ora_stage_ns[0] boolean-entropy decode incl. dequantisation and inverse transforms (the
+ * reference does those inside read_residual_data), [1] intra prediction, [2] loop filter, [3] YUV -> RGB(A). */
+int ora_stage_timing = 0;
+long long ora_stage_ns[4] = {0, 0, 0, 0};
+static long long stage_now(void) {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec;
+}
+void ora_stage_add(int k, long long ns) { __atomic_fetch_add(&ora_stage_ns[k], ns, __ATOMIC_RELAXED); }
+long long ora_stage_clock(void) { return stage_now(); }
+
 int ora_vp8_decode(const uint8_t* data, size_t len, int keep, ora_frame* out) {
     vp8dec d;
     memset(&d, 0, sizeof(d));
@@ -1008,6 +1023,7 @@ int ora_vp8_decode(const uint8_t* data, size_t len, int keep, ora_frame* out) {
         for (int mbx = 0; mbx < mbw; mbx++) {
             ora_mb* mb = &d.macroblocks[(size_t)mby * mbw + mbx];
             int32_t blocks[384];
+            const long long t_a = ora_stage_timing ? stage_now() : 0;
             e = read_mb_header(&d, mbx, mb);
             if (e) goto fail;
             if (!mb->coeffs_skipped) {
@@ -1026,8 +1042,14 @@ int ora_vp8_decode(const uint8_t* data, size_t len, int keep, ora_frame* out) {
                 memset(blocks, 0, sizeof(blocks));
             }
             if (keep) memcpy(out->residue + ((size_t)mby * mbw + mbx) * 384, blocks, sizeof(blocks));
+            const long long t_b = ora_stage_timing ? stage_now() : 0;
             intra_predict_luma(&d, mbx, mby, mb, blocks);
             intra_predict_chroma(&d, mbx, mby, mb, blocks);
+            if (ora_stage_timing) {
+                const long long t_c = stage_now();
+                ora_stage_add(0, t_b - t_a);
+                ora_stage_add(1, t_c - t_b);
+            }
         }
         memset(d.left_border_y, 129, 17);
         memset(d.left_border_u, 129, 9);
@@ -1043,9 +1065,11 @@ int ora_vp8_decode(const uint8_t* data, size_t len, int keep, ora_frame* out) {
         memcpy(out->ubuf0, out->ubuf, csz);
         memcpy(out->vbuf0, out->vbuf, csz);
     }
+    const long long t_lf = ora_stage_timing ? stage_now() : 0;
     for (int mby = 0; mby < mbh; mby++)
         for (int mbx = 0; mbx < mbw; mbx++)
             loop_filter_mb(out, mbx, mby, &d.macroblocks[(size_t)mby * mbw + mbx]);
+    if (ora_stage_timing) ora_stage_add(2, stage_now() - t_lf);
     if (keep) { out->mbs = d.macroblocks; d.macroblocks = NULL; }
     dec_cleanup(&d);
     return ORA_OK;
@@ -1150,9 +1174,11 @@ void ora_fill_rgb_buffer_simple(uint8_t* buf, size_t buf_len, const uint8_t* yb,
 /* Frame::fill_rgb / fill_rgba, mod.rs:184-241 */
 void ora_frame_fill(const ora_frame* f, uint8_t* buf, int bpp, int fancy_up) {
     int bw = f->mbw * 16; /* buffer_width(), mod.rs:174-181 */
+    const long long t0 = ora_stage_timing ? stage_now() : 0;
     if (fancy_up)
         ora_fill_rgb_buffer_fancy(buf, f->ybuf, f->ubuf, f->vbuf, f->width, f->height, bw, bpp);
     else
         ora_fill_rgb_buffer_simple(buf, (size_t)f->width * f->height * bpp, f->ybuf, f->ubuf, f->vbuf,
                                    f->width, (f->width + 1) / 2, bw, f->mbh * 16, bpp);
+    if (ora_stage_timing) ora_stage_add(3, stage_now() - t0);
 }

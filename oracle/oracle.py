@@ -104,6 +104,23 @@ def lib():
     return _lib
 
 
+def stage_timing(on):
+    """Switch the per-stage timers of the decoder on or off and clear them (bench.py's CPU baseline split)."""
+    L = lib()
+    C.c_int.in_dll(L, "ora_stage_timing").value = 1 if on else 0
+    arr = (C.c_longlong * 4).in_dll(L, "ora_stage_ns")
+    for i in range(4):
+        arr[i] = 0
+
+
+def stage_seconds():
+    """Core-seconds spent per stage since stage_timing(True): entropy decode incl. dequantisation and inverse
+    transforms, intra prediction, loop filter, YUV -> RGB(A) (summed over the worker threads)."""
+    arr = (C.c_longlong * 4).in_dll(lib(), "ora_stage_ns")
+    names = ["entropy+dequant+itx", "predict", "loopfilter", "rgb"]
+    return {n: arr[i] / 1e9 for i, n in enumerate(names)}
+
+
 class OracleError(Exception):
     def __init__(self, code):
         super().__init__("oracle status %d" % code)
