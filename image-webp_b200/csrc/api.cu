@@ -181,6 +181,10 @@ struct webpb200_ctx {
     std::string err;
     uint64_t launches = 0;
     std::atomic<bool> in_flight{false};  // a webpb200_decode_batch_begin has not been ended yet
+    // AUTO placement of the entropy stage: microseconds per macroblock of one device chain and of one host thread.
+    // Start values measured on B200 with a 16-core host; every call that runs a stage refines its figure (moving average).
+    double dev_us_per_mb = 33.0, host_us_per_mb = 3.0;
+    double last_chain_mbs = 0;           // longest chain x oversubscription of the last device-entropy call
 
     PinBuf h_frames, h_mbs, h_levels, h_alpha, h_aux, h_bits, h_ehdr, h_status, h_vp8l_px, h_vp8l_planes, h_vp8l_aux;
     uint64_t last_h2d = 0, last_d2h = 0;  // bytes the last decode_batch copied each way
@@ -1083,15 +1087,25 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         // The device decodes every partition of every frame at once but each one slowly (one lane,
         // about 33 us per macroblock on B200); the host decodes fast (about 3 us per macroblock)
         // but only one frame per thread.  Many small frames: device.  A few large ones: host.
+        // The two rates are per-context moving averages of what the last calls measured.
         double longest = 0, streams = 0;
         for (int i = 0; i < n; i++)
             if (hdrs[i].num_parts) {
                 longest = std::max(longest, (double)frames[i].mbw * frames[i].mbh / hdrs[i].num_parts);
                 streams += hdrs[i].num_parts;
             }
-        const double est_device_us = longest * 33.0 * std::max(1.0, streams / 1184.0);
-        const double est_host_us = (double)c->total_mbs * 3.0 / std::max(1, std::min(host_threads, n));
+        const double est_device_us = longest * c->dev_us_per_mb * std::max(1.0, streams / 1184.0);
+        const double est_host_us = (double)c->total_mbs * c->host_us_per_mb / std::max(1, std::min(host_threads, n));
         if (est_device_us > est_host_us) return kPreferHostEntropy;
+        c->last_chain_mbs = longest * std::max(1.0, streams / 1184.0);
+    } else {
+        double longest = 0, streams = 0;
+        for (int i = 0; i < n; i++)
+            if (hdrs[i].num_parts) {
+                longest = std::max(longest, (double)frames[i].mbw * frames[i].mbh / hdrs[i].num_parts);
+                streams += hdrs[i].num_parts;
+            }
+        c->last_chain_mbs = longest * std::max(1.0, streams / 1184.0);
     }
     fill_row_order(frames, 0, n, reinterpret_cast<uint32_t*>(c->h_aux.p + c->aux_order_off));
     const double t_host = ms_since();
@@ -1277,6 +1291,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         CU(c, cudaStreamSynchronize(s), "sync");
         CU(c, cudaStreamSynchronize(r), "sync");
         cudaEventElapsedTime(&c->last_entropy_ms, c->ev[5], c->ev[6]);
+        if (c->last_chain_mbs >= 256 && c->last_entropy_ms > 0) c->dev_us_per_mb = 0.5 * c->dev_us_per_mb + 0.5 * (1e3 * c->last_entropy_ms / c->last_chain_mbs);
         for (int i = 0; i < n; i++)
             if (dev_status[i]) c->items[i].status = dev_status[i];  // those pixels are not valid
         if ((rc = check_abort(c)) != 0) return rc;
@@ -1326,6 +1341,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     if (outs && (rc = download_range(c, outs, out_lens, 0, n)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
     cudaEventElapsedTime(&c->last_entropy_ms, c->ev[5], c->ev[6]);
+    if (c->last_chain_mbs >= 256 && c->last_entropy_ms > 0) c->dev_us_per_mb = 0.5 * c->dev_us_per_mb + 0.5 * (1e3 * c->last_entropy_ms / c->last_chain_mbs);
     if ((rc = check_abort(c)) != 0) return rc;
     if (trace) {
         float ems = 0;
@@ -1503,6 +1519,7 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
         }
     };
     int nthreads = std::max(1, std::min(host_threads, n));
+    const auto t_workers = std::chrono::steady_clock::now();
     std::vector<std::thread> pool;
     for (int t = 0; t < nthreads; t++) pool.emplace_back(worker);
 
@@ -1570,6 +1587,10 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
             if (int r = download_range(c, outs, out_lens, i0, i1)) err = r;
     }
     for (auto& t : pool) t.join();
+    if (c->total_mbs >= 4096 && !c->alpha_bytes) {  // refine the host figure of the AUTO cost model (ALPH work would distort it)
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_workers).count();
+        c->host_us_per_mb = 0.5 * c->host_us_per_mb + 0.5 * (us * nthreads / (double)c->total_mbs);
+    }
     if (err) {
         cudaStreamSynchronize(s);
         return err;

@@ -108,7 +108,31 @@ __device__ __forceinline__ void st_edge(uint2* p, uint32_t pixels, uint32_t tag)
 // Watchdog: a wait that lasts absurdly long (a scheduling bug, never a data property) raises the abort
 // word; every waiter then stops waiting, the kernel drains with garbage pixels and the host reports an
 // error instead of hanging the device.
-__device__ __forceinline__ uint32_t wait_edge(const uint2* p, uint2 v, uint32_t tag, unsigned int* abort_word) {
+// The whole warp waits together: the loop's exit is a warp-uniform vote, so the lanes never leave it one by one (a
+// loop that only some lanes run and leave at different times puts the warp on the compiler's "not converged" copy of
+// the code that follows, where every warp-level operation is several times slower).  `want`: this lane's unit matters.
+__device__ __forceinline__ uint32_t wait_edge(const uint2* p, uint2 v, uint32_t tag, bool want, unsigned int* abort_word) {
+    unsigned spins = 0;
+    bool ok = !want || v.y == tag;
+    while (!__all_sync(kFull, ok)) {
+#if WF_SLEEP_NS > 0
+        __nanosleep(WF_SLEEP_NS);
+#endif
+        if (!ok) {
+            v = ld_edge(p);
+            ok = v.y == tag;
+        }
+        if ((++spins & 0x3ff) == 0) {
+            if (spins > (1u << 24)) atomicExch(abort_word, 1u);
+            if (*reinterpret_cast<volatile unsigned int*>(abort_word)) break;
+        }
+    }
+    return v.x;
+}
+
+// Every lane of the warp has a unit to wait for (normal loop filter): each lane polls its own; measured faster than
+// the voting loop there, and the warp reconverges at the caller's next __syncwarp.
+__device__ __forceinline__ uint32_t wait_edge_each(const uint2* p, uint2 v, uint32_t tag, unsigned int* abort_word) {
     unsigned spins = 0;
     while (v.y != tag) {
 #if WF_SLEEP_NS > 0
@@ -461,9 +485,11 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
         // is checked when it is needed), prev = of the one above mbx - 1
         uint2 nxt = make_uint2(0u, 0u);
         uint32_t cur = 0, prev = 0;
-        if (mby > 0 && lane < 8) {
-            cur = wait_edge(edge_above, ld_edge(edge_above), tag_above, A.abort_word);
-            if (mbw > 1) nxt = ld_edge(edge_above + 8);
+        if (mby > 0) {
+            uint2 first = make_uint2(0u, 0u);
+            if (lane < 8) first = ld_edge(edge_above);
+            cur = wait_edge(edge_above, first, tag_above, lane < 8, A.abort_word);
+            if (lane < 8 && mbw > 1) nxt = ld_edge(edge_above + 8);
         }
         uint8_t* const yout = Y + (size_t)(mby * 16 + (lane >> 1)) * ystride + (lane & 1) * 8;
         uint8_t* const cout = (lane < 16 ? U : V) + (size_t)(mby * 8 + ((lane & 15) >> 1)) * cstride + (lane & 1) * 4;
@@ -613,9 +639,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_predict(PredictArgs A)
                 }
             } else {
                 const bool last = mbx == mbw - 1;
-                uint32_t nx = 0;
+                const uint32_t nx = wait_edge(edge_above + (size_t)(mbx + 1) * 8, nxt, tag_above, lane < 8 && !last, A.abort_word);
                 if (lane < 8) {
-                    if (!last) nx = wait_edge(edge_above + (size_t)(mbx + 1) * 8, nxt, tag_above, A.abort_word);
                     *top_dst = cur;
                     // corner: no macroblock to the left -> 129, else the last pixel above it
                     if (corner_lane) *corner_dst = mbx == 0 ? 0x81818181u : prev;
@@ -946,9 +971,13 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
             }
             // ---- ... rows -4..-1 from the edge record of the macroblock above (there once the row above
             // has filtered the left edge of ITS next macroblock); the record after it is requested now ----
-            if (up_lane) {
-                *up_dst = wait_edge(edge_above + (size_t)mbx * 32, upv, tag_above, A.abort_word);
-                if (mbx + 1 < mbw) upv = ld_edge(edge_above + (size_t)(mbx + 1) * 32);
+            if (mby > 0) {
+                const uint32_t strip = simple ? wait_edge(edge_above + (size_t)mbx * 32, upv, tag_above, up_lane, A.abort_word)
+                                              : wait_edge_each(edge_above + (size_t)mbx * 32, upv, tag_above, A.abort_word);
+                if (up_lane) {
+                    *up_dst = strip;
+                    if (mbx + 1 < mbw) upv = ld_edge(edge_above + (size_t)(mbx + 1) * 32);
+                }
             }
 
             const int ymode = mbword & 0xff, segment = (mbword >> 16) & 3;

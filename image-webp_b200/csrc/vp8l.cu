@@ -184,11 +184,17 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
             uint32_t L = 0, T = 0, TL = 0, mine = 0, first = 0;
             uint2 nxt = make_uint2(0u, 0u);
             unsigned spins_total = 0;
-            auto wait_unit = [&](const uint2* u, uint2 v) -> uint32_t {
+            // the whole warp waits with lane 0 (a loop that one lane runs alone leaves the warp on the compiler's
+            // "not converged" code path afterwards, several times slower): the exit is a warp-uniform vote
+            auto wait_unit = [&](const uint2* u, uint2 v, bool want) -> uint32_t {
                 unsigned spins = 0;
-                while (v.y != tag_in) {
+                bool ok = !want || v.y == tag_in;
+                while (!__all_sync(kFull, ok)) {
                     __nanosleep(40);
-                    v = ld_unit(u);
+                    if (!ok) {
+                        v = ld_unit(u);
+                        ok = v.y == tag_in;
+                    }
                     if ((++spins & 0x3ff) == 0) {
                         spins_total += 0x400;
                         if (spins_total > (1u << 24)) atomicExch(B.abort_word, 1u);
@@ -197,11 +203,16 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                 }
                 return v.x;
             };
-            if (lane == 0 && g > 0) {
+            if (g > 0) {
                 // lane 0's "lane above" is the last row of the band above: its pixel 0 goes into the pipeline as
                 // `top` now, the others arrive one per step as `top-right`
-                T = wait_unit(above, ld_unit(above));
-                if (w > 1) nxt = ld_unit(above + 1);
+                uint2 first_unit = make_uint2(0u, 0u);
+                if (lane == 0) first_unit = ld_unit(above);
+                const uint32_t t0 = wait_unit(above, first_unit, lane == 0);
+                if (lane == 0) {
+                    T = t0;
+                    if (w > 1) nxt = ld_unit(above + 1);
+                }
             }
             // residuals: block b (columns 8b..8b+7) of my row sits in the ring while it is used, block b + 1 is in
             // flight in `ahead` and is put into the ring when block b + 1 begins, block b + 2 is requested then
@@ -225,13 +236,16 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                 // top-right of my column: what the lane above finished in the previous step (its column x + 1)
                 uint32_t tr = __shfl_up_sync(kFull, mine, 1);
                 const int x = i - 2 * lane;
-                if (lane == 0) {
-                    if (g > 0 && x + 1 < w) {
-                        tr = wait_unit(above + x + 1, nxt);  // requested one step earlier
-                        if (x + 2 < w) nxt = ld_unit(above + x + 2);
-                    } else {
-                        tr = 0;
+                if (g > 0) {
+                    // (x of lane 0 is i: the condition below is the same for every lane that evaluates it)
+                    const bool want = lane == 0 && i + 1 < w;
+                    const uint32_t unit = wait_unit(above + (lane == 0 ? i + 1 : 0), nxt, want);  // requested one step earlier
+                    if (lane == 0) {
+                        tr = want ? unit : 0u;
+                        if (i + 2 < w) nxt = ld_unit(above + i + 2);
                     }
+                } else if (lane == 0) {
+                    tr = 0;
                 }
                 const uint32_t TRv = tr;
                 if (row_ok && x >= 0 && x < w) {
