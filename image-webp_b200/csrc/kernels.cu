@@ -971,11 +971,18 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
             }
             // ---- ... rows -4..-1 from the edge record of the macroblock above (there once the row above
             // has filtered the left edge of ITS next macroblock); the record after it is requested now ----
+#ifndef LF_WAIT_UNIFORM
+#define LF_WAIT_UNIFORM 0   // 1: the normal filter waits by vote too (A/B)
+#endif
             if (mby > 0) {
-                const uint32_t strip = simple ? wait_edge(edge_above + (size_t)mbx * 32, upv, tag_above, up_lane, A.abort_word)
-                                              : wait_edge_each(edge_above + (size_t)mbx * 32, upv, tag_above, A.abort_word);
-                if (up_lane) {
-                    *up_dst = strip;
+                if (simple || LF_WAIT_UNIFORM) {  // half of the lanes have nothing to wait for: wait as one warp
+                    const uint32_t strip = wait_edge(edge_above + (size_t)mbx * 32, upv, tag_above, up_lane, A.abort_word);
+                    if (up_lane) {
+                        *up_dst = strip;
+                        if (mbx + 1 < mbw) upv = ld_edge(edge_above + (size_t)(mbx + 1) * 32);
+                    }
+                } else {                          // every lane has its unit
+                    *up_dst = wait_edge_each(edge_above + (size_t)mbx * 32, upv, tag_above, A.abort_word);
                     if (mbx + 1 < mbw) upv = ld_edge(edge_above + (size_t)(mbx + 1) * 32);
                 }
             }
