@@ -1111,19 +1111,29 @@ __global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(Filt
 // k_yuv2rgb: one thread = 8 horizontally adjacent pixels of the two rows (2q-1, 2q) that share
 // their pair of chroma rows (q = 0: row 0 alone)
 // ---------------------------------------------------------------------------------------------
-// yuv.rs:30-71
-__device__ __forceinline__ int mulhi8(int v, int coeff) { return (v * coeff) >> 8; }
-__device__ __forceinline__ int clip6(int v) { return min(max(v >> 6, 0), 255); }
+// yuv.rs:30-71: r = clip((mulhi(y, 19077) + mulhi(v, 26149) - 14234) >> 6) etc. with mulhi(v, c) = (v * c) >> 8.
+// The kernel is bound by the ALU pipe (shifts, adds, logic), not by the multiplier, so the floors are arranged to
+// need one shift per channel: floor(A / 256) + floor(B / 256) == floor(((A & ~255) + B) / 256) because the masked
+// term is a multiple of 256; the constants are multiples of 256 and go into the masked term; the final >> 6 merges
+// with the >> 8 (nested floors); a SUBTRACTED term uses -floor(B / 256) == floor((255 - B) / 256), i.e. the running
+// sum is OR-ed with 255 instead of masked.  (Tried and slower: the high half of (v << 24) * c as the mulhi, 0.48 ms
+// against 0.37 on cfg2 -- IMAD.HI issues at a quarter of the IMAD rate; the three luma terms from a 256-entry
+// shared-memory table, 0.45 ms -- sixteen 16-byte gathers per thread with random bank conflicts.)
 __device__ __forceinline__ uint32_t yuv_to_rgb(int y, int u, int v) {  // r | g << 8 | b << 16
-    const int yy = mulhi8(y, 19077);
-    const int r = (yy + mulhi8(v, 26149) - 14234) >> 6;
-    const int g = (yy - mulhi8(u, 6419) - mulhi8(v, 13320) + 8708) >> 6;
-    const int b = (yy + mulhi8(u, 33050) - 17685) >> 6;
-    // clip(x) = clamp(x >> 6, 0, 255) (yuv.rs:66-71): the clamps and the packing are two saturating cvt.pack
+    const int yy = y * 19077;
+    const int r = (v * 26149 + ((yy - 14234 * 256) & ~255)) >> 14;
+    const int g = ((((yy + 8708 * 256) | 255) - u * 6419) | 255) - v * 13320 >> 14;
+    const int b = (u * 33050 + ((yy - 17685 * 256) & ~255)) >> 14;
+    // clip(x) = clamp(x, 0, 255) (yuv.rs:66-71): the clamps and the packing are two saturating cvt.pack
     uint32_t hi, px;
     asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(0), "r"(b), "r"(0));
     asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(px) : "r"(g), "r"(r), "r"(hi));
     return px;
+}
+__device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
 
 struct RgbArgs {
@@ -1133,26 +1143,30 @@ struct RgbArgs {
     int q_first, q_end;  // row pairs [q_first, q_end) only (pair q = rows 2q-1, 2q)
 };
 
-// Horizontal half of the fancy upsampler for 8 pixels of one chroma row.  c[0..5] are the chroma
-// samples at columns 4k-1 .. 4k+4 (clamped to the visible chroma width, which is how yuv.rs:163-170
-// and 204-219 treat the first and last pixel).  Pixel i uses main column cm and second column cs
-// (cm, cs = same, left / same, right alternating); h[i] = 3*c[cm] + c[cs] + 2, so that
-// (3*h_main + h_second) >> 4 == (9*a + 3*b + 3*c + d + 8) >> 4 of yuv.rs:276-282.
-__device__ __forceinline__ void chroma_row8(const uint8_t* row, int k4, int lim, int* h) {
-    const uint32_t wd = __ldg(reinterpret_cast<const uint32_t*>(row + k4));
-    int c[6];
-    c[0] = __ldg(row + max(k4 - 1, 0));
-    c[1] = __byte_perm(wd, 0, 0x4440); c[2] = __byte_perm(wd, 0, 0x4441); c[3] = __byte_perm(wd, 0, 0x4442); c[4] = __byte_perm(wd, 0, 0x4443);
-    c[5] = __ldg(row + k4 + min(4, lim));
-    if (lim < 3) {  // the row's last thread: columns past the visible width repeat the last one
-        if (lim < 1) c[2] = c[1];
-        if (lim < 2) c[3] = c[2];
-        c[4] = c[3];
-    }
-    h[0] = 3 * c[1] + c[0] + 2; h[1] = 3 * c[1] + c[2] + 2;
-    h[2] = 3 * c[2] + c[1] + 2; h[3] = 3 * c[2] + c[3] + 2;
-    h[4] = 3 * c[3] + c[2] + 2; h[5] = 3 * c[3] + c[4] + 2;
-    h[6] = 3 * c[4] + c[3] + 2; h[7] = 3 * c[4] + c[5] + 2;
+// Horizontal half of the fancy upsampler for 8 pixels of one chroma row, TWO pixels per register (16-bit fields:
+// pixel i in the low half, pixel i + 4 in the high half; every sum stays below 2^16).  c[0..5] are the chroma
+// samples at columns 4k-1 .. 4k+4 (clamped to the visible chroma width, which is how yuv.rs:163-170 and 204-219
+// treat the first and last pixel).  Pixel 2j has main column c[j+1] and second column c[j], pixel 2j+1 has
+// c[j+1] and c[j+2]; h = 3 * main + second, so that (3 * h_main_row + h_second_row + 8) >> 4 ==
+// (9*a + 3*b + 3*c + d + 8) >> 4 of yuv.rs:276-282.  `rep` replicates the last visible column (lim < 3 only).
+__device__ __forceinline__ void chroma_row8(const uint8_t* row, int k4, int lim, uint32_t rep, uint32_t* h) {
+    uint32_t wd = __ldg(reinterpret_cast<const uint32_t*>(row + k4));
+    const uint32_t c0 = __ldg(row + max(k4 - 1, 0)), c5 = __ldg(row + k4 + min(4, lim));
+    if (lim < 3) wd = __byte_perm(wd, 0, rep);     // the row's last thread: columns past the visible width repeat the last one
+    const uint32_t A = __byte_perm(wd, 0, 0x4240);   // c1 | c3 << 16
+    const uint32_t B = __byte_perm(wd, 0, 0x4341);   // c2 | c4 << 16
+    const uint32_t L = __byte_perm(wd, c0, 0x5154);  // c0 | c2 << 16
+    const uint32_t R = __byte_perm(wd, c5, 0x5452);  // c3 | c5 << 16
+    h[0] = 3 * A + L;  // pixels 0 | 4
+    h[1] = 3 * A + B;  // pixels 1 | 5
+    h[2] = 3 * B + A;  // pixels 2 | 6
+    h[3] = 3 * B + R;  // pixels 3 | 7
+}
+// Vertical half: t = 16 * (3 * main + second + 8), i.e. the upsampled sample is byte 1 (pixel i) and byte 3
+// (pixel i + 4) of t: one PRMT each to extract.  (Both products as multiply-adds: the multiplier has room, the ALU pipe not.)
+__device__ __forceinline__ void chroma_blend(const uint32_t* hm, const uint32_t* hs, uint32_t* t) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) t[j] = mad_lo(hs[j], 16u, mad_lo(hm[j], 48u, 0x00800080u));
 }
 
 // 8 pixels -> tightly packed RGB8 / RGBA8 (yuv.rs:285-289; byte 3 of RGBA belongs to the ALPH merge
@@ -1190,10 +1204,14 @@ __device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int
     }
 }
 
-__global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
+#ifndef RGB_PAIRS_PER_BLOCK
+#define RGB_PAIRS_PER_BLOCK 2
+#endif
+constexpr int kRgbPairsPerBlock = RGB_PAIRS_PER_BLOCK;  // block = 64 x 2 threads = 512 pixels x 4 rows
+__global__ void __launch_bounds__(64 * kRgbPairsPerBlock) k_yuv2rgb(RgbArgs A) {
     const webpb200_frame_desc* fd = A.frames + blockIdx.z;
     const int w = fd->width, h = fd->height;
-    const int q = A.q_first + blockIdx.y * 2 + threadIdx.y;
+    const int q = A.q_first + blockIdx.y * kRgbPairsPerBlock + threadIdx.y;
     const int x0 = (blockIdx.x * 64 + threadIdx.x) * 8;
     const int ya = q == 0 ? 0 : 2 * q - 1, yb = 2 * q;
     if (x0 >= w || ya >= h || q >= A.q_end) return;
@@ -1206,7 +1224,7 @@ __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
     const uint2 ywa = __ldg(reinterpret_cast<const uint2*>(Y + (size_t)ya * ystride));
     uint2 ywb = make_uint2(0, 0);
     if (has_b) ywb = __ldg(reinterpret_cast<const uint2*>(Y + (size_t)yb * ystride));
-    int ua[8], va[8], ub[8], vb[8];
+    uint32_t ua[8], va[8], ub[8], vb[8];
     if (fd->upsampling == WEBPB200_UPSAMPLING_SIMPLE) {  // fill_rgb_buffer_simple, yuv.rs:293-382
         const uint32_t u0 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->u_off + (size_t)(ya >> 1) * cstride + k4));
         const uint32_t v0 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->v_off + (size_t)(ya >> 1) * cstride + k4));
@@ -1215,8 +1233,8 @@ __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
         const uint32_t v1 = __ldg(reinterpret_cast<const uint32_t*>(A.planes + fd->v_off + (size_t)rb * cstride + k4));
 #pragma unroll
         for (int i = 0; i < 8; i++) {
-            ua[i] = (u0 >> (8 * (i >> 1))) & 0xff; va[i] = (v0 >> (8 * (i >> 1))) & 0xff;
-            ub[i] = (u1 >> (8 * (i >> 1))) & 0xff; vb[i] = (v1 >> (8 * (i >> 1))) & 0xff;
+            ua[i] = __byte_perm(u0, 0, 0x4440 | (i >> 1)); va[i] = __byte_perm(v0, 0, 0x4440 | (i >> 1));
+            ub[i] = __byte_perm(u1, 0, 0x4440 | (i >> 1)); vb[i] = __byte_perm(v1, 0, 0x4440 | (i >> 1));
         }
     } else {
         // fill_rgb_buffer_fancy, yuv.rs:76-282.  Row 2q-1 takes chroma row q-1 as main and q as second,
@@ -1225,25 +1243,36 @@ __global__ void __launch_bounds__(128) k_yuv2rgb(RgbArgs A) {
         const int cw = (w + 1) >> 1, chh = (h + 1) >> 1;
         const int ca = q == 0 ? 0 : q - 1, cb = min(q, chh - 1);
         const int lim = cw - 1 - k4;  // last visible chroma column relative to k4
-        int ha[8], hb[8];
+        const uint32_t rep = lim == 0 ? 0x0000u : lim == 1 ? 0x1110u : 0x2210u;
+        uint32_t ha[4], hb[4], ta[4], tb[4];
         const uint8_t* U = A.planes + fd->u_off;
-        chroma_row8(U + (size_t)ca * cstride, k4, lim, ha);
-        chroma_row8(U + (size_t)cb * cstride, k4, lim, hb);
+        chroma_row8(U + (size_t)ca * cstride, k4, lim, rep, ha);
+        chroma_row8(U + (size_t)cb * cstride, k4, lim, rep, hb);
+        chroma_blend(ha, hb, ta);
+        chroma_blend(hb, ha, tb);
 #pragma unroll
-        for (int i = 0; i < 8; i++) { ua[i] = (3 * ha[i] + hb[i]) >> 4; ub[i] = (3 * hb[i] + ha[i]) >> 4; }
+        for (int i = 0; i < 4; i++) {
+            ua[i] = __byte_perm(ta[i], 0, 0x4441); ua[i + 4] = ta[i] >> 24;
+            ub[i] = __byte_perm(tb[i], 0, 0x4441); ub[i + 4] = tb[i] >> 24;
+        }
         const uint8_t* V = A.planes + fd->v_off;
-        chroma_row8(V + (size_t)ca * cstride, k4, lim, ha);
-        chroma_row8(V + (size_t)cb * cstride, k4, lim, hb);
+        chroma_row8(V + (size_t)ca * cstride, k4, lim, rep, ha);
+        chroma_row8(V + (size_t)cb * cstride, k4, lim, rep, hb);
+        chroma_blend(ha, hb, ta);
+        chroma_blend(hb, ha, tb);
 #pragma unroll
-        for (int i = 0; i < 8; i++) { va[i] = (3 * ha[i] + hb[i]) >> 4; vb[i] = (3 * hb[i] + ha[i]) >> 4; }
+        for (int i = 0; i < 4; i++) {
+            va[i] = __byte_perm(ta[i], 0, 0x4441); va[i + 4] = ta[i] >> 24;
+            vb[i] = __byte_perm(tb[i], 0, 0x4441); vb[i + 4] = tb[i] >> 24;
+        }
     }
     uint32_t px[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(__byte_perm(i < 4 ? ywa.x : ywa.y, 0, 0x4440 | (i & 3)), ua[i], va[i]);
+    for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb((int)__byte_perm(i < 4 ? ywa.x : ywa.y, 0, 0x4440 | (i & 3)), (int)ua[i], (int)va[i]);
     store_row8(A.out + fd->out_off + ((size_t)ya * w + x0) * bpp, px, n, bpp);
     if (has_b) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb(__byte_perm(i < 4 ? ywb.x : ywb.y, 0, 0x4440 | (i & 3)), ub[i], vb[i]);
+        for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb((int)__byte_perm(i < 4 ? ywb.x : ywb.y, 0, 0x4440 | (i & 3)), (int)ub[i], (int)vb[i]);
         store_row8(A.out + fd->out_off + ((size_t)yb * w + x0) * bpp, px, n, bpp);
     }
 }
@@ -1555,6 +1584,13 @@ static int wavefront_grid(const BatchDev& b, int blocks_per_sm) {
     if (grid > need) grid = need;
     return grid < 1 ? 1 : grid;
 }
+#ifdef WF_GRID_ENV  // experiments only: grid sizes from the environment
+#include <cstdlib>
+static int env_grid(const char* name, int dflt) { const char* e = getenv(name); return e && atoi(e) > 0 ? atoi(e) : dflt; }
+#define WF_GRID(name, g) env_grid(name, g)
+#else
+#define WF_GRID(name, g) (g)
+#endif
 
 cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     PredictArgs a;
@@ -1571,8 +1607,8 @@ cudaError_t launch_predict(const BatchDev& b, cudaStream_t s) {
     const int lat_blocks = b.predict_blocks_latency > 0 ? b.predict_blocks_latency : 1;
     const bool latency_bound = b.predict_blocks_latency > 0 && (uint64_t)b.total_rows <= 2ull * lat_blocks * (b.sm_count > 0 ? b.sm_count : 1) * kWarpsPerBlock;
     if (latency_bound) {
-        if (b.levels_packed) k_predict<kPredictBlocksLatency, true><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
-        else k_predict<kPredictBlocksLatency, false><<<wavefront_grid(b, lat_blocks), kThreads, 0, s>>>(a);
+        if (b.levels_packed) k_predict<kPredictBlocksLatency, true><<<WF_GRID("WF_PGRID", wavefront_grid(b, lat_blocks)), kThreads, 0, s>>>(a);
+        else k_predict<kPredictBlocksLatency, false><<<WF_GRID("WF_PGRID", wavefront_grid(b, lat_blocks)), kThreads, 0, s>>>(a);
     } else {
         if (b.levels_packed) k_predict<kPredictBlocksThroughput, true><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
         else k_predict<kPredictBlocksThroughput, false><<<wavefront_grid(b, b.predict_blocks), kThreads, 0, s>>>(a);
@@ -1591,7 +1627,7 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
-    k_loopfilter<<<wavefront_grid(b, b.filter_blocks), kThreads, 0, s>>>(a);
+    k_loopfilter<<<WF_GRID("WF_FGRID", wavefront_grid(b, b.filter_blocks)), kThreads, 0, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -1603,8 +1639,8 @@ cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
     a.q_first = b.q_end > b.q_first ? b.q_first : 0;
     a.q_end = b.q_end > b.q_first ? (b.q_end < q_all ? b.q_end : q_all) : q_all;
     if (a.q_end <= a.q_first) return cudaSuccess;
-    dim3 grid((b.max_w + 511) / 512, (a.q_end - a.q_first + 1) / 2, b.n_frames);
-    k_yuv2rgb<<<grid, dim3(64, 2), 0, s>>>(a);
+    dim3 grid((b.max_w + 511) / 512, (a.q_end - a.q_first + kRgbPairsPerBlock - 1) / kRgbPairsPerBlock, b.n_frames);
+    k_yuv2rgb<<<grid, dim3(64, kRgbPairsPerBlock), 0, s>>>(a);
     return cudaGetLastError();
 }
 
