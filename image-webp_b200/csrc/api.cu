@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <condition_variable>
 #include <functional>
 #include <memory>
@@ -174,6 +175,8 @@ struct webpb200_ctx {
     int predict_blocks = 1, predict_blocks_latency = 1, filter_blocks = 1;  // resident blocks per SM of the wavefront kernels on this device
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;      // reconstruction of finished bands while k_entropy still runs
+    cudaStream_t stream3 = nullptr;      // the bands' downloads: a queued copy (other contexts share the copy engine) must not hold up the next band's kernels
+    cudaEvent_t band_ev[16] = {};        // band k's pixels are converted
     unsigned int* h_rows = nullptr;      // mapped pinned: [frame * 8 + partition] rows finished (written by k_entropy)
     unsigned int* d_rows = nullptr;
     size_t rows_cap = 0;
@@ -755,12 +758,16 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
+    if (c->stream3) cudaStreamSynchronize(c->stream3);
     for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status, &c->h_vp8l_px, &c->h_vp8l_planes, &c->h_vp8l_aux}) b->release();
     for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status, &c->d_vp8l_px, &c->d_vp8l_planes, &c->d_vp8l_aux, &c->d_vp8l_hand})
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->stream3) cudaStreamDestroy(c->stream3);
+    for (auto& e : c->band_ev)
+        if (e) cudaEventDestroy(e);
     if (c->h_rows) cudaFreeHost(c->h_rows);
     delete c;
 }
@@ -968,6 +975,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     std::vector<WorkItem> items = items_in;  // the caller keeps its list: the cost model may hand the batch to the host path
     const int n = (int)items.size();
     if (c->stream2) cudaStreamSynchronize(c->stream2);  // nothing of an earlier call that ended early may still be in flight
+    if (c->stream3) cudaStreamSynchronize(c->stream3);
     const double t_items = ms_since();
     cudaStream_t s = c->stream;
     int rc = 0;
@@ -1007,7 +1015,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     if ((rc = reserve_device(c)) != 0) return rc;
     if (!direct_base) CU(c, c->d_bits.reserve((size_t)bits_bytes + 16), "device bitstreams");
     CU(c, c->d_ehdr.reserve(sizeof(Vp8EntropyHdr) * (size_t)std::max(n, 1)), "device entropy headers");
-    CU(c, c->d_status.reserve(sizeof(int) * (size_t)std::max(n, 1)), "device status");
+    CU(c, c->d_status.reserve(sizeof(int) * 3 * (size_t)std::max(n, 1)), "device status");  // status[n] | k_entropy's sync words [2n]
     Vp8EntropyHdr* hdrs = reinterpret_cast<Vp8EntropyHdr*>(c->h_ehdr.p);
 
     // clear the outputs of the entropy stage while the host parses headers
@@ -1017,7 +1025,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
         // the others are never touched), so the 800 bytes per macroblock need no clearing
         CU(c, cudaMemsetAsync(c->d_mbs.p, 0, sizeof(webpb200_mb_desc) * (size_t)c->total_mbs, s), "clear mbs");
     }
-    CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * (size_t)std::max(n, 1), s), "clear status");
+    CU(c, cudaMemsetAsync(c->d_status.p, 0, sizeof(int) * 3 * (size_t)std::max(n, 1), s), "clear status");
     if (trace) cudaEventRecord(c->ev[9], s);
 
     auto drop = [&](int i, int st) {  // the frame stays in the batch as all-DC, all-zero macroblocks nobody looks at
@@ -1156,6 +1164,10 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
             }
             band_start[nbands] = mbh;
             if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
+            if (!c->stream3) {
+                CU(c, cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking), "copy stream");
+                for (auto& e : c->band_ev) CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "band events");
+            }
             if (c->rows_cap < (size_t)n * 8) {
                 if (c->h_rows) cudaFreeHost(c->h_rows);
                 c->h_rows = nullptr;
@@ -1167,51 +1179,89 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
             std::memset(c->h_rows, 0, sizeof(unsigned int) * 8 * (size_t)n);
         }
     }
+    if (!c->alpha_bytes) {  // the frame lists are complete without the ALPH headers: up they go before the long kernel
+        finish_items(c);
+        CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
+    }
     // Let the clears and uploads drain before the long-lived entropy blocks are placed: launched
     // right behind them, the 1024 blocks usually ended up unevenly spread over the SMs and the kernel
     // ran 9.5 % longer (42.9 vs 39.2 ms, bimodal); the wait itself costs nothing that is not needed anyway.
     CU(c, cudaStreamSynchronize(s), "sync before k_entropy");
     CU(c, cudaEventRecord(c->ev[7], s), "event");  // every input of the reconstruction kernels is on the device
     cudaEventRecord(c->ev[5], s);
+    // Which block layout k_entropy uses for single-partition batches.  A call made through webpb200_decode_batch_begin
+    // expects other batches on the GPU: the split layout (mode warps in blocks of their own, half the registers per
+    // chain) keeps the chains of three batches resident and is 10-20 % faster per step there, but a batch that has
+    // the GPU to itself is 5 % slower in it (its token blocks spread a little less evenly): 36.6 against 35.0 ms.
+    static const int split_env = [] { const char* e = std::getenv("WEBPB200_ENTROPY_SPLIT"); return e ? std::atoi(e) : -1; }();
+    const bool split_layout = split_env >= 0 ? split_env != 0 : c->in_flight.load();
     if (c->total_mbs) {
         CU(c, launch_entropy(c->bd, reinterpret_cast<const Vp8EntropyHdr*>(c->d_ehdr.p), c->d_bits.p,
                              reinterpret_cast<webpb200_mb_desc*>(c->d_mbs.p), reinterpret_cast<int16_t*>(c->d_levels.p),
-                             reinterpret_cast<int*>(c->d_status.p), max_parts, same_probs, nbands ? c->d_rows : nullptr, s), "k_entropy");
+                             reinterpret_cast<int*>(c->d_status.p), max_parts, same_probs, nbands ? c->d_rows : nullptr,
+                             split_layout ? reinterpret_cast<unsigned int*>(c->d_status.p) + std::max(n, 1) : nullptr, s), "k_entropy");
         c->launches++;
     }
     cudaEventRecord(c->ev[6], s);
-    // which frames ran out of bits is known only now; their pixels are not handed out
+    // Which frames ran out of bits is known when k_entropy has ended.  NOTHING that a copy engine executes may be
+    // queued behind k_entropy: an engine takes the copies of all streams in the order they were enqueued, so a copy
+    // that waits for this kernel would hold up the uploads and downloads of every other batch in flight for tens of
+    // milliseconds (measured with three batches in flight: their calls fell into lockstep, one context's downloads
+    // ran to the end before the next one's first band moved).  The status words are fetched after the kernel's
+    // end has been seen (fetch_status), the frame lists went up before the launch, and what the ALPH planes need
+    // goes up on a second stream.
     int* dev_status = reinterpret_cast<int*>(c->h_status.p);
-    CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
+    auto fetch_status = [&]() -> int {  // call with k_entropy finished
+        CU(c, cudaMemcpyAsync(dev_status, c->d_status.p, sizeof(int) * (size_t)std::max(n, 1), cudaMemcpyDeviceToHost, s), "D2H status");
+        CU(c, cudaStreamSynchronize(s), "sync");
+        return 0;
+    };
     // ALPH planes (extended.rs:253-308; VP8L or raw) are host work in both entropy modes: here they are decoded
-    // on the host threads while k_entropy runs, then follow it on the stream together with the per-filter
-    // frame lists (the filter method is in the ALPH chunk header) and the descriptors they may have changed.
+    // on the host threads while k_entropy runs and uploaded beside it, together with the per-filter frame lists
+    // (the filter method is in the ALPH chunk header); the descriptors they may have changed follow the kernel.
     if (c->alpha_bytes) {
         parallel_for(n, host_threads, [&](int i) {
             if (!c->items[i].status && frames[i].alpha_mode)
                 if (const int st = alpha_one(c, i, frames[i])) drop(i, st);
         });
+        finish_items(c);
+        if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
+        cudaStream_t up = c->stream2;
+        CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, up), "H2D alpha");
+        if (int r2 = upload_vp8l(c, 0, c->vp8l_n, up)) return r2;
+        CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, up), "H2D lists");
+        CU(c, cudaEventRecord(c->ev[11], up), "event");
+        CU(c, cudaStreamSynchronize(s), "sync");  // k_entropy has ended (it reads the descriptors that are replaced now)
         CU(c, cudaMemcpyAsync(c->d_frames.p, frames, sizeof(webpb200_frame_desc) * (size_t)n, cudaMemcpyHostToDevice, s), "H2D frames");
-        CU(c, cudaMemcpyAsync(c->d_alpha.p, c->h_alpha.p, (size_t)c->alpha_bytes, cudaMemcpyHostToDevice, s), "H2D alpha");
-        if (int r2 = upload_vp8l(c, 0, c->vp8l_n, s)) return r2;
+        CU(c, cudaStreamWaitEvent(s, c->ev[11], 0), "wait uploads");
     }
-    finish_items(c);
-    CU(c, cudaMemcpyAsync(c->d_aux.p + c->aux_lists_off, c->h_aux.p + c->aux_lists_off, c->aux_bytes - c->aux_lists_off, cudaMemcpyHostToDevice, s), "H2D lists");
     if (nbands) {
         cudaStream_t r = c->stream2;
-        CU(c, cudaEventRecord(c->ev[4], s), "event");  // k_entropy (and the status copy) finished
+        CU(c, cudaEventRecord(c->ev[4], s), "event");  // k_entropy finished
         CU(c, cudaStreamWaitEvent(r, c->ev[7], 0), "wait inputs");
         const BatchDev& B = c->bd;
         CU(c, cudaMemsetAsync(B.scratch + B.lay.edge_pred_off, 0, (size_t)(B.lay.zero_bytes - B.lay.edge_pred_off), r), "clear edge records");
         const int mbh = frames[0].mbh, w = frames[0].width, h = frames[0].height;
         const int q_all = h / 2 + 1;
-        int q_done = 0;
+        int q_done = 0, emitted = 0;
         cudaEvent_t bev[kMaxBands][4];
         int band_now = 0;
         double t_seen[kMaxBands];
         if (trace)
             for (int k = 0; k < nbands; k++)
                 for (auto& e : bev[k]) cudaEventCreate(&e);
+        struct BandCopy { size_t off, bytes; int ev; };
+        std::deque<BandCopy> copies;  // converted, not yet handed to the copy engine
+        auto pump_copies = [&](bool wait) -> int {
+            while (!copies.empty()) {
+                const BandCopy& bc = copies.front();
+                if (wait) CU(c, cudaEventSynchronize(c->band_ev[bc.ev]), "band event");
+                else if (cudaEventQuery(c->band_ev[bc.ev]) != cudaSuccess) break;
+                CU(c, cudaMemcpy2DAsync(outs[0] + bc.off, dpitch, c->d_out.p + frames[0].out_off + bc.off, spitch, bc.bytes, (size_t)n, cudaMemcpyDeviceToHost, c->stream3), "D2H band");
+                copies.pop_front();
+            }
+            return 0;
+        };
         auto emit = [&](int q_end) -> int {  // convert row pairs [q_done, q_end) and send their pixel rows home
             if (q_end <= q_done) return 0;
             BatchDev bd = B;
@@ -1226,8 +1276,14 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
                 q_done = q_end;
                 return 0;
             }
-            // one 2-D copy for the band of every frame (a copy per frame is API-bound: 5 us x 1024 per band)
-            CU(c, cudaMemcpy2DAsync(outs[0] + off, dpitch, c->d_out.p + frames[0].out_off + off, spitch, bytes, (size_t)n, cudaMemcpyDeviceToHost, r), "D2H band");
+            // One 2-D copy for the band of every frame (a copy per frame is API-bound: 5 us x 1024 per band), on its own
+            // stream, and handed to the copy engine only once the band's pixels exist (pump_copies): the engine takes
+            // the copies of all streams in the order they were enqueued, so a copy that is still waiting for its event
+            // holds up the finished bands of every other batch in flight (measured with three batches: the downloads of
+            // one context ran to the end before the next context's first band moved).
+            CU(c, cudaEventRecord(c->band_ev[emitted % 16], r), "band event");
+            copies.push_back({off, bytes, emitted % 16});
+            emitted++;
             c->last_d2h += bytes * (uint64_t)n;
             q_done = q_end;
             return 0;
@@ -1267,6 +1323,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
                     scan_from++;
                 }
                 if (scan_from >= n || cudaEventQuery(c->ev[4]) != cudaErrorNotReady) break;
+                if ((rc = pump_copies(false)) != 0) return rc;
                 std::this_thread::sleep_for(std::chrono::microseconds(20));
             }
             scan_from = 0;
@@ -1285,11 +1342,15 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
             // last row pair converted is the one whose second chroma row is the row just above those
             if (trace) cudaEventRecord(bev[k][1], r);
             if ((rc = emit(lf_end < mbh ? 8 * lf_end - 4 : q_all)) != 0) return rc;
-            if (trace) cudaEventRecord(bev[k][2], r);
+            if ((rc = pump_copies(false)) != 0) return rc;
+            if (trace) cudaEventRecord(bev[k][2], outs ? c->stream3 : r);
         }
         const double t_lastband = ms_since();
+        if ((rc = pump_copies(true)) != 0) return rc;
         CU(c, cudaStreamSynchronize(s), "sync");
+        if ((rc = fetch_status()) != 0) return rc;
         CU(c, cudaStreamSynchronize(r), "sync");
+        CU(c, cudaStreamSynchronize(c->stream3), "sync");
         cudaEventElapsedTime(&c->last_entropy_ms, c->ev[5], c->ev[6]);
         if (c->last_chain_mbs >= 256 && c->last_entropy_ms > 0) c->dev_us_per_mb = 0.5 * c->dev_us_per_mb + 0.5 * (1e3 * c->last_entropy_ms / c->last_chain_mbs);
         for (int i = 0; i < n; i++)
@@ -1335,6 +1396,7 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
     }
     if ((rc = reconstruct(c, c->bd, c->alpha_bytes ? 0xF : 0x7, s, nullptr)) != 0) return rc;
     CU(c, cudaStreamSynchronize(s), "sync");
+    if ((rc = fetch_status()) != 0) return rc;
     const double t_kernels = ms_since();
     for (int i = 0; i < n; i++)
         if (!c->items[i].status && dev_status[i]) c->items[i].status = dev_status[i];

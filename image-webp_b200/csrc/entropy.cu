@@ -19,7 +19,9 @@
 //                  mod.rs:124-129), handed over in a shared-memory ring of P+1 context rows
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
+#include <cstdio>
 
 #include "entropy.h"
 #include "kernels.cuh"
@@ -285,6 +287,9 @@ struct EntropyArgs {
     int frames_per_block;
     int shared_probs;  // every frame of the launch carries the same token probabilities: one table per block instead of one per frame
     unsigned int* rows_done;  // host-mapped, [frame * 8 + partition] = macroblock rows that partition has finished; or null
+    int wave;                 // split layout only: blocks per wave (the SM count)
+    unsigned int* sync;       // split layout only, zero at launch: [frame] = macroblock rows whose descriptors are in global memory (~0u: the
+                              // frame failed), [frames + frame] = somebody has taken the frame's mode partition
 };
 
 struct EntropyCtl {
@@ -317,154 +322,150 @@ __device__ __forceinline__ bool wait_shared(volatile int* word, int need, volati
     return true;
 }
 
-// Block layouts.  frames_per_block = 1: one frame, warp 0 = modes, warps 1..P = token partitions.
-// frames_per_block = 4 (batches whose frames all have one token partition): warps 0-3 = the token
-// partitions of four frames, warps 4-7 = their mode partitions.  With two warps per block the token
-// warps all sat on odd warp slots, i.e. on two of the SM's four schedulers, while the other two
-// idled once the short mode partitions were done; four consecutive token warps always cover all
-// four schedulers (ncu: "not selected" stalls 0.36 -> 0.1 per instruction, 35.6 -> 33 ms on cfg2).
-__global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
-    extern __shared__ __align__(16) uint8_t smem_all[];
-    const int F = A.frames_per_block;
-    const int warp_all = threadIdx.x >> 5;
-    const int slot = F == 1 ? 0 : (warp_all & 3);             // which of the block's frames this warp serves
-    const int warp = F == 1 ? warp_all : (warp_all < 4 ? 1 : 0);  // role: 0 = modes, 1.. = token partition + 1
-    // Batches whose frames all carry the same token probabilities (no probability updates: the usual case)
-    // keep ONE table per block: 17 KB instead of 68 KB of shared memory for four frames, so that twice as many
-    // blocks fit an SM and the chains of a second batch can run beside the first one's.
-    const bool own = !A.shared_probs;
-    const size_t per_frame = entropy_smem_per_frame(A.max_parts, A.max_mbw, own);
-    const size_t frames_at = own ? 0 : kProbBytes;
-    const size_t ctl_at = own ? kProbBytes : 0;  // offset of EntropyCtl inside a frame's region
-
-    // which of the block's frames the shared table is filled from: the first one the host did not drop
-    // (a dropped frame's header is all zero)
-    int table_from = 0;
-    if (!own)
-        for (int sl = F - 1; sl >= 0; sl--)
-            if (blockIdx.x * F + sl < A.n_frames && A.hdrs[A.frame_first + blockIdx.x * F + sl].num_parts) table_from = sl;
-
-    // shared tables of all the block's frames, filled by the whole block
-    for (int sl = 0; sl < F; sl++) {
-        const int fi = blockIdx.x * F + sl;
-        if (fi >= A.n_frames) break;
-        uint8_t* sm = smem_all + frames_at + sl * per_frame;
-        const Vp8EntropyHdr& Hs = A.hdrs[A.frame_first + fi];
-        TokenProb* pr = reinterpret_cast<TokenProb*>(own ? sm : smem_all);
-        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(sm + ctl_at);
-        uint32_t* tb = reinterpret_cast<uint32_t*>(sm + ctl_at + kCtlBytes);
-        if (own || sl == table_from)
-            for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) pr[i] = make_token_prob(Hs.probs[i]);
-        for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(cs)[i] = 0;
-        for (int i = threadIdx.x; i < A.max_mbw; i += blockDim.x) tb[i] = 0;
+// the same on a global word another block writes (split layout)
+__device__ __forceinline__ bool wait_global(const volatile unsigned int* word, unsigned int need, int* status) {
+    unsigned spins = 0;
+    while (*word < need) {
+        __nanosleep(200);
+        if (++spins > (1u << 24)) {
+            *status = WEBPB200_ERR_CUDA;
+            return false;
+        }
     }
-    __syncthreads();
-    for (int sl = 0; sl < F; sl++) {
-        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(smem_all + frames_at + sl * per_frame + ctl_at);
-        if (threadIdx.x < 17) cs->lut[threadIdx.x] = band_of(threadIdx.x) * 33u * (uint32_t)sizeof(TokenProb) | (zigzag_of(threadIdx.x & 15) * 2u) << 16;
-    }
-    __syncthreads();
+    __threadfence();
+    return true;
+}
 
-    const int fi = blockIdx.x * F + slot;
-    if ((threadIdx.x & 31) != 0 || fi >= A.n_frames) return;  // one working lane per partition
-    uint8_t* smem = smem_all + frames_at + slot * per_frame;
-    TokenProb* s_probs = reinterpret_cast<TokenProb*>(own ? smem : smem_all);
-    EntropyCtl* ctl = reinterpret_cast<EntropyCtl*>(smem + ctl_at);
-    uint32_t* s_top_bpred = reinterpret_cast<uint32_t*>(smem + ctl_at + kCtlBytes);
-    uint16_t* s_top_nz = reinterpret_cast<uint16_t*>(smem + ctl_at + kCtlBytes + 4 * (size_t)A.max_mbw);
+// one frame's working set in shared memory
+struct FrameSmem {
+    TokenProb* probs;
+    EntropyCtl* ctl;
+    uint32_t* top_bpred;
+    uint16_t* top_nz;
+};
 
-    const int f = A.frame_first + fi;
+// ---------------- macroblock headers of frame f (read_macroblock_header, mod.rs:615-671) ----------------
+// kSplit = false: the token warps of the frame sit in the same block and follow `modes_done` in shared memory,
+// macroblock by macroblock.  kSplit = true: they sit in another block and follow A.sync[1 + f] in global memory,
+// macroblock row by macroblock row (one device-scope fence per row).
+template <bool kSplit>
+__device__ __forceinline__ void decode_modes(const EntropyArgs& A, int f, const FrameSmem& M) {
     const Vp8EntropyHdr& H = A.hdrs[f];
-    const int P = H.num_parts;
-    if (P == 0 || warp > P) return;  // failed on the host / no such partition
     const webpb200_frame_desc& fd = A.frames[f];
     const int mbw = fd.mbw, mbh = fd.mbh;
-    const uint8_t* chunk = A.bits + H.data_off;
     webpb200_mb_desc* mbs = A.mbs + fd.mb_base;
-    volatile int* v_abort = &ctl->abort;
-    volatile int* v_modes = &ctl->modes_done;
-
-    if (warp == 0) {
-        // ---------------- macroblock headers (read_macroblock_header, mod.rs:615-671) ----------------
-        DevBool b;
-        b.load(chunk + H.first_off, H.first_len, H.first);
-        const bool update_map = H.update_map, has_skip = H.has_prob_skip;
-        const int prob_skip = H.prob_skip;
-        const uint8_t seg_probs[3] = {H.seg_probs[0], H.seg_probs[1], H.seg_probs[2]};
-        int done = 0;
-        for (int mby = 0; mby < mbh; mby++) {
-            uint32_t left = 0;  // four B modes, one per byte (row y in byte y)
-            for (int mbx = 0; mbx < mbw; mbx++) {
-                uint32_t w0 = 0, bp0 = 0, bp1 = 0;  // the descriptor's 16 bytes: {w0, nflags = 0, bp0, bp1}
-                if (update_map) {
-                    int i = 0;
-                    do {
-                        i = c_segment_tree[i + (int)b.get(seg_probs[i >> 1])];
-                    } while (i > 0);
-                    w0 |= (uint32_t)(-i) << 16;
-                }
-                const int skipped = has_skip ? (int)b.get(prob_skip) : 0;
-                w0 |= (uint32_t)skipped << 24;
-                const int ymode = b.tree(c_ymode_tree, c_ymode_probs);
-                w0 |= (uint32_t)ymode;
-                uint32_t top = s_top_bpred[mbx];  // column x in byte x
-                if (ymode == 4) {
-                    uint32_t nt = 0;
+    volatile int* v_abort = &M.ctl->abort;
+    volatile int* v_modes = &M.ctl->modes_done;
+    volatile unsigned int* g_rows = kSplit ? A.sync + f : nullptr;
+    if (kSplit && atomicCAS(A.sync + A.frame_first + A.n_frames + f, 0u, 1u) != 0u) return;  // the frame's token warp got tired of waiting and does it
+    uint32_t* s_top_bpred = M.top_bpred;
+    DevBool b;
+    b.load(A.bits + H.data_off + H.first_off, H.first_len, H.first);
+    const bool update_map = H.update_map, has_skip = H.has_prob_skip;
+    const int prob_skip = H.prob_skip;
+    const uint8_t seg_probs[3] = {H.seg_probs[0], H.seg_probs[1], H.seg_probs[2]};
+    int done = 0;
+    for (int mby = 0; mby < mbh; mby++) {
+        uint32_t left = 0;  // four B modes, one per byte (row y in byte y)
+        for (int mbx = 0; mbx < mbw; mbx++) {
+            uint32_t w0 = 0, bp0 = 0, bp1 = 0;  // the descriptor's 16 bytes: {w0, nflags = 0, bp0, bp1}
+            if (update_map) {
+                int i = 0;
+                do {
+                    i = c_segment_tree[i + (int)b.get(seg_probs[i >> 1])];
+                } while (i > 0);
+                w0 |= (uint32_t)(-i) << 16;
+            }
+            const int skipped = has_skip ? (int)b.get(prob_skip) : 0;
+            w0 |= (uint32_t)skipped << 24;
+            const int ymode = b.tree(c_ymode_tree, c_ymode_probs);
+            w0 |= (uint32_t)ymode;
+            uint32_t top = s_top_bpred[mbx];  // column x in byte x
+            if (ymode == 4) {
+                uint32_t nt = 0;
 #pragma unroll 1
-                    for (int y = 0; y < 4; y++) {
-                        int l = (left >> (8 * y)) & 0xff;
-                        uint32_t row = 0;
+                for (int y = 0; y < 4; y++) {
+                    int l = (left >> (8 * y)) & 0xff;
+                    uint32_t row = 0;
 #pragma unroll 1
-                        for (int x = 0; x < 4; x++) {
-                            const int t = (top >> (8 * x)) & 0xff;
-                            const int bm = b.tree(c_bmode_tree, c_bmode_probs + (t * 10 + l) * 9);
-                            row |= (uint32_t)bm << (8 * x);
-                            l = bm;
-                        }
-                        top = row;
-                        if (y == 3) nt = row;
-                        left = (left & ~(0xffu << (8 * y))) | ((uint32_t)l << (8 * y));
-                        // nibbles of sub-blocks 4y..4y+3
-                        const uint32_t nib = (row & 0xf) | ((row >> 4) & 0xf0) | ((row >> 8) & 0xf00) | ((row >> 12) & 0xf000);
-                        if (y < 2) bp0 |= nib << (16 * y);
-                        else bp1 |= nib << (16 * (y - 2));
+                    for (int x = 0; x < 4; x++) {
+                        const int t = (top >> (8 * x)) & 0xff;
+                        const int bm = b.tree(c_bmode_tree, c_bmode_probs + (t * 10 + l) * 9);
+                        row |= (uint32_t)bm << (8 * x);
+                        l = bm;
                     }
-                    s_top_bpred[mbx] = nt;
+                    top = row;
+                    if (y == 3) nt = row;
+                    left = (left & ~(0xffu << (8 * y))) | ((uint32_t)l << (8 * y));
+                    // nibbles of sub-blocks 4y..4y+3
+                    const uint32_t nib = (row & 0xf) | ((row >> 4) & 0xf0) | ((row >> 8) & 0xf00) | ((row >> 12) & 0xf000);
+                    if (y < 2) bp0 |= nib << (16 * y);
+                    else bp1 |= nib << (16 * (y - 2));
+                }
+                s_top_bpred[mbx] = nt;
+            } else {
+                const uint32_t m = (0x01030200u >> (8 * ymode)) & 0xff;  // DC->B_DC V->B_VE H->B_HE TM->B_TM
+                left = m * 0x01010101u;
+                s_top_bpred[mbx] = left;
+            }
+            w0 |= (uint32_t)b.tree(c_uvmode_tree, c_uvmode_probs) << 8;
+            if (b.eof) {
+                A.status[f] = WEBPB200_ERR_BITSTREAM;
+                if (kSplit) {
+                    __threadfence();
+                    *g_rows = ~0u;
                 } else {
-                    const uint32_t m = (0x01030200u >> (8 * ymode)) & 0xff;  // DC->B_DC V->B_VE H->B_HE TM->B_TM
-                    left = m * 0x01010101u;
-                    s_top_bpred[mbx] = left;
-                }
-                w0 |= (uint32_t)b.tree(c_uvmode_tree, c_uvmode_probs) << 8;
-                if (b.eof) {
-                    A.status[f] = WEBPB200_ERR_BITSTREAM;
                     *v_abort = 1;
-                    return;
                 }
-                *reinterpret_cast<uint4*>(mbs + (size_t)mby * mbw + mbx) = make_uint4(w0, 0u, bp0, bp1);
+                return;
+            }
+            *reinterpret_cast<uint4*>(mbs + (size_t)mby * mbw + mbx) = make_uint4(w0, 0u, bp0, bp1);
+            if (!kSplit) {
                 __threadfence_block();
                 *v_modes = ++done;
             }
         }
-        return;
+        if (kSplit) {
+            __threadfence();
+            *g_rows = (unsigned int)mby + 1u;
+        }
     }
+}
 
-    // ---------------- coefficient tokens (read_residual_data, mod.rs:874-963) ----------------
-    const int p = warp - 1;
+// ---------------- coefficient tokens of partition p of frame f (read_residual_data, mod.rs:874-963) ----------------
+template <bool kSplit>
+__device__ __forceinline__ void decode_tokens(const EntropyArgs& A, int f, int p, int max_mbw, const FrameSmem& M) {
+    const Vp8EntropyHdr& H = A.hdrs[f];
+    const int P = H.num_parts;
+    const webpb200_frame_desc& fd = A.frames[f];
+    const int mbw = fd.mbw, mbh = fd.mbh;
+    webpb200_mb_desc* mbs = A.mbs + fd.mb_base;
+    EntropyCtl* ctl = M.ctl;
+    volatile int* v_abort = &ctl->abort;
+    volatile int* v_modes = &ctl->modes_done;
+    const TokenProb* s_probs = M.probs;
+    uint16_t* s_top_nz = M.top_nz;
     DevBool br;
-    br.init(chunk + H.part_off[p], H.part_len[p]);
+    br.init(A.bits + H.data_off + H.part_off[p], H.part_len[p]);
     int16_t* levels = A.levels + (size_t)fd.mb_base * WEBPB200_LEVELS_PER_MB;
     const int ring = P + 1;
     int seen_modes = 0;
+    unsigned int seen_rows = 0;
     for (int mby = p; mby < mbh; mby += P) {
-        uint16_t* cur = s_top_nz + (size_t)(mby % ring) * A.max_mbw;
-        const uint16_t* prev = s_top_nz + (size_t)((mby + ring - 1) % ring) * A.max_mbw;
+        uint16_t* cur = s_top_nz + (size_t)(mby % ring) * max_mbw;
+        const uint16_t* prev = s_top_nz + (size_t)((mby + ring - 1) % ring) * max_mbw;
         volatile int* my_prog = &ctl->row_prog[mby % ring];
         volatile int* up_prog = &ctl->row_prog[(mby + ring - 1) % ring];
+        if (kSplit && seen_rows <= (unsigned int)mby) {  // this row's descriptors (written by the frame's mode warp in another block)
+            const volatile unsigned int* g_rows = A.sync + f;
+            if (!wait_global(g_rows, (unsigned int)mby + 1u, A.status + f)) return;
+            seen_rows = *g_rows;
+            if (seen_rows == ~0u) return;  // the mode partition ran out of bits
+        }
         uint32_t l = 0;  // left context: bit 0 Y2, 1-4 Y rows, 5-6 U rows, 7-8 V rows
         for (int mbx = 0; mbx < mbw; mbx++) {
             const int mbi = mby * mbw + mbx;
-            if (seen_modes <= mbi) {
+            if (!kSplit && seen_modes <= mbi) {
                 if (!wait_shared(v_modes, mbi + 1, v_abort, A.status + f)) return;
                 seen_modes = *v_modes;
             }
@@ -508,7 +509,7 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
                 mbs[mbi].nflags = nflags;
                 if (br.eof) {
                     A.status[f] = WEBPB200_ERR_BITSTREAM;
-                    *v_abort = 1;
+                    if (!kSplit) *v_abort = 1;
                     return;
                 }
             }
@@ -531,6 +532,130 @@ __global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
     }
 }
 
+// shared tables of the block's frames [frame0, frame0 + F), filled by the whole block (ends with a barrier)
+__device__ __forceinline__ void fill_frame_tables(const EntropyArgs& A, uint8_t* smem_all, int frame0, int F, bool own, size_t per_frame) {
+    const size_t frames_at = own ? 0 : kProbBytes;
+    const size_t ctl_at = own ? kProbBytes : 0;  // offset of EntropyCtl inside a frame's region
+    // which of the block's frames the shared table is filled from: the first one the host did not drop
+    // (a dropped frame's header is all zero)
+    int table_from = 0;
+    if (!own)
+        for (int sl = F - 1; sl >= 0; sl--)
+            if (frame0 + sl < A.n_frames && A.hdrs[A.frame_first + frame0 + sl].num_parts) table_from = sl;
+    for (int sl = 0; sl < F; sl++) {
+        const int fi = frame0 + sl;
+        if (fi >= A.n_frames) break;
+        uint8_t* sm = smem_all + frames_at + sl * per_frame;
+        const Vp8EntropyHdr& Hs = A.hdrs[A.frame_first + fi];
+        TokenProb* pr = reinterpret_cast<TokenProb*>(own ? sm : smem_all);
+        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(sm + ctl_at);
+        uint32_t* tb = reinterpret_cast<uint32_t*>(sm + ctl_at + kCtlBytes);
+        if (own || sl == table_from)
+            for (int i = threadIdx.x; i < kTokenProbs; i += blockDim.x) pr[i] = make_token_prob(Hs.probs[i]);
+        for (int i = threadIdx.x; i < (int)(sizeof(EntropyCtl) / 4); i += blockDim.x) reinterpret_cast<int*>(cs)[i] = 0;
+        for (int i = threadIdx.x; i < A.max_mbw; i += blockDim.x) tb[i] = 0;
+    }
+    __syncthreads();
+    for (int sl = 0; sl < F; sl++) {
+        EntropyCtl* cs = reinterpret_cast<EntropyCtl*>(smem_all + frames_at + sl * per_frame + ctl_at);
+        if (threadIdx.x < 17) cs->lut[threadIdx.x] = band_of(threadIdx.x) * 33u * (uint32_t)sizeof(TokenProb) | (zigzag_of(threadIdx.x & 15) * 2u) << 16;
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ FrameSmem frame_smem(const EntropyArgs& A, uint8_t* smem_all, int slot, bool own, size_t per_frame) {
+    uint8_t* smem = smem_all + (own ? 0 : kProbBytes) + slot * per_frame;
+    const size_t ctl_at = own ? kProbBytes : 0;
+    FrameSmem M;
+    M.probs = reinterpret_cast<TokenProb*>(own ? smem : smem_all);
+    M.ctl = reinterpret_cast<EntropyCtl*>(smem + ctl_at);
+    M.top_bpred = reinterpret_cast<uint32_t*>(smem + ctl_at + kCtlBytes);
+    M.top_nz = reinterpret_cast<uint16_t*>(smem + ctl_at + kCtlBytes + 4 * (size_t)A.max_mbw);
+    return M;
+}
+
+// Block layouts of k_entropy.  frames_per_block = 1 (frames with several token partitions): one frame, warp 0 =
+// modes, warps 1..P = token partitions.  frames_per_block = 4 (batches whose frames all have one token partition):
+// warps 0-3 = the token partitions of four frames, warps 4-7 = their mode partitions.  With two warps per block the
+// token warps all sat on odd warp slots, i.e. on two of the SM's four schedulers, while the other two idled once the
+// short mode partitions were done; four consecutive token warps always cover all four schedulers (ncu: "not
+// selected" stalls 0.36 -> 0.1 per instruction, 35.6 -> 33 ms on cfg2).
+// Batches whose frames all carry the same token probabilities (no probability updates: the usual case)
+// keep ONE table per block (17 KB) instead of one per frame.
+__global__ void __launch_bounds__(288) k_entropy(EntropyArgs A) {
+    extern __shared__ __align__(16) uint8_t smem_all[];
+    const int F = A.frames_per_block;
+    const int warp_all = threadIdx.x >> 5;
+    const int slot = F == 1 ? 0 : (warp_all & 3);                 // which of the block's frames this warp serves
+    const int warp = F == 1 ? warp_all : (warp_all < 4 ? 1 : 0);  // role: 0 = modes, 1.. = token partition + 1
+    const bool own = !A.shared_probs;
+    const size_t per_frame = entropy_smem_per_frame(A.max_parts, A.max_mbw, own);
+    fill_frame_tables(A, smem_all, blockIdx.x * F, F, own, per_frame);
+    const int fi = blockIdx.x * F + slot;
+    if ((threadIdx.x & 31) != 0 || fi >= A.n_frames) return;  // one working lane per partition
+    const FrameSmem M = frame_smem(A, smem_all, slot, own, per_frame);
+    const int f = A.frame_first + fi;
+    const int P = A.hdrs[f].num_parts;
+    if (P == 0 || warp > P) return;  // failed on the host / no such partition
+    if (warp == 0) decode_modes<false>(A, f, M);
+    else decode_tokens<false>(A, f, warp - 1, A.max_mbw, M);
+}
+
+// Batches whose frames all have ONE token partition (split layout): blocks of four warps, four frames per block,
+// and the mode partitions of those four frames in ANOTHER block of four warps.  A warp's registers are allocated for
+// all 32 lanes although one lane works, so the number of resident chains is set by registers per block: with the
+// mode warps (a fifth of the work, finished early) in the same block as the token warps, half of every block's
+// registers sat idle for most of the kernel and an SM held 16 token chains; now it holds 36, which is what lets the
+// chains of several batches in flight share the issue slots (webpb200_decode_batch_begin).
+//
+// A chain slows down with every other chain on its SM (28.5 ms with three others, 33 ms among sixteen), so the
+// token blocks must be spread evenly.  The hardware places the blocks of a grid breadth-first in blockIdx order, one
+// per SM and round again (tools/micro/placement.cu) -- as long as every block stays -- so the roles go by blockIdx in
+// waves of one block per SM: modes of groups 0..S-1, tokens of groups 0..S-1, modes of the next S groups, ...
+// (Roles by atomic ticket, i.e. in arrival order, put 256 token blocks on 94 of 148 SMs: 35 instead of 32 ms.)
+// Token warps follow their frame's mode warp row by row through A.sync (global memory, one device-scope fence per
+// macroblock row on the producer's side).  Nothing guarantees that a lower blockIdx starts first, so whoever gets to a
+// frame's mode partition first claims it: a token warp that sees no progress decodes the modes itself.
+constexpr int kSplitFrames = 4;
+__global__ void __launch_bounds__(32 * kSplitFrames) k_entropy_split(EntropyArgs A) {
+    extern __shared__ __align__(16) uint8_t smem_all[];
+    const int groups = (A.n_frames + kSplitFrames - 1) / kSplitFrames;
+    // waves of A.wave blocks: an even wave holds mode blocks, the odd wave after it the token blocks of the same groups;
+    // the last pair of waves is short (no block without work)
+    const int per_pair = 2 * A.wave;
+    const int pair = (int)blockIdx.x / per_pair, in_pair = (int)blockIdx.x % per_pair;
+    const int in_wave = min(A.wave, groups - pair * A.wave);  // groups in this pair of waves
+    const bool modes = in_pair < in_wave;
+    const int frame0 = (pair * A.wave + (modes ? in_pair : in_pair - in_wave)) * kSplitFrames;
+    const bool own = !A.shared_probs;
+    const size_t per_frame = entropy_smem_per_frame(1, A.max_mbw, own);
+    fill_frame_tables(A, smem_all, frame0, kSplitFrames, own, per_frame);
+    const int slot = threadIdx.x >> 5;
+    const int fi = frame0 + slot;
+    if ((threadIdx.x & 31) != 0 || fi >= A.n_frames) return;  // one working lane per chain
+    const FrameSmem M = frame_smem(A, smem_all, slot, own, per_frame);
+    const int f = A.frame_first + fi;
+    if (A.hdrs[f].num_parts == 0) return;  // failed on the host
+#ifdef ENT_DEBUG
+    unsigned long long t0, t1; unsigned sm, wid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+    asm volatile("mov.u32 %0, %%warpid;" : "=r"(wid));
+#endif
+    if (!modes) {
+        // nobody may have started on the frame's modes (its mode block is not resident yet, and nothing says it will be
+        // before this block ends): after a while, do them here (a no-op if the mode warp has claimed the frame meanwhile)
+        const volatile unsigned int* g_rows = A.sync + f;
+        unsigned spins = 0;
+        while (*g_rows == 0u && ++spins < 2000u) __nanosleep(200);
+    }
+    if (modes || *(const volatile unsigned int*)(A.sync + f) == 0u) decode_modes<true>(A, f, M);
+    if (!modes) decode_tokens<true>(A, f, 0, A.max_mbw, M);
+#ifdef ENT_DEBUG
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    printf("ENT %d %d %u %u %llu %llu\n", modes ? 1 : 0, fi, sm, wid, t0, t1);
+#endif
+}
+
 }  // namespace
 
 void upload_entropy_tables_once() {
@@ -538,7 +663,8 @@ void upload_entropy_tables_once() {
 }
 
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, cudaStream_t s) {
+                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, unsigned int* d_sync,
+                           cudaStream_t s) {
     if (b.n_frames <= 0) return cudaSuccess;
     EntropyArgs a;
     a.frames = b.frames; a.hdrs = d_hdrs; a.bits = d_bits; a.mbs = d_mbs; a.levels = d_levels; a.status = d_status;
@@ -546,17 +672,32 @@ cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const
     a.max_parts = max_parts;
     a.max_mbw = (int)((b.max_w + 15) / 16);
     a.n_frames = b.n_frames;
-    a.frames_per_block = max_parts == 1 && b.n_frames >= 8 ? 4 : 1;
+    // single-partition batches: four frames per block; split = their mode warps in blocks of their own (see k_entropy_split)
+    const bool four = max_parts == 1 && b.n_frames >= 8;
+    const bool split = four && d_sync != nullptr;
+    a.frames_per_block = four ? kSplitFrames : 1;
     a.rows_done = rows_done;
     a.shared_probs = same_probs ? 1 : 0;
-    const size_t smem = entropy_smem_per_frame(max_parts, a.max_mbw, !same_probs) * (size_t)a.frames_per_block + (same_probs ? kProbBytes : 0);
+    a.sync = d_sync;
+    a.wave = 1;
     static_assert(sizeof(EntropyCtl) <= kCtlBytes, "EntropyCtl outgrew its slot");
-    if (smem > 48 * 1024) {  // per device and function: cheap enough to repeat
-        cudaError_t e = cudaFuncSetAttribute(k_entropy, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
     const int F = a.frames_per_block;
-    k_entropy<<<(b.n_frames + F - 1) / F, F == 1 ? 32 * (1 + max_parts) : 256, smem, s>>>(a);
+    const size_t smem = entropy_smem_per_frame(split ? 1 : max_parts, a.max_mbw, !same_probs) * (size_t)F + (same_probs ? kProbBytes : 0);
+    if (split) {
+        if (smem > 48 * 1024) {  // per device and function: cheap enough to repeat
+            cudaError_t e = cudaFuncSetAttribute(k_entropy_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        const int groups = (b.n_frames + F - 1) / F;
+        a.wave = b.sm_count > 0 ? b.sm_count : 1;
+        k_entropy_split<<<2 * groups, 32 * kSplitFrames, smem, s>>>(a);
+    } else {
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(k_entropy, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        k_entropy<<<(b.n_frames + F - 1) / F, F == 1 ? 32 * (1 + max_parts) : 256, smem, s>>>(a);
+    }
     return cudaGetLastError();
 }
 

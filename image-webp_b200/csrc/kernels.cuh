@@ -89,9 +89,12 @@ void upload_entropy_tables_once();
 // same_probs: every frame of the launch has the same token probabilities (one shared-memory table per block);
 // rows_done (may be null): host-mapped array, [frame * 8 + partition] = number of macroblock rows that
 // token partition has finished (plain store after a system-scope fence), so the host can start
-// reconstructing the top of the frames while the bottom is still being decoded
+// reconstructing the top of the frames while the bottom is still being decoded;
+// d_sync (may be null): 2 * (frame_first + n_frames) zeroed words for the split layout (single-partition batches: mode warps
+// and token warps in separate blocks, entropy.cu), without it every frame gets one block of 1 + partitions warps
 cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const uint8_t* d_bits, webpb200_mb_desc* d_mbs,
-                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, cudaStream_t s);
+                           int16_t* d_levels, int* d_status, int max_parts, bool same_probs, unsigned int* rows_done, unsigned int* d_sync,
+                           cudaStream_t s);
 
 struct CompositeArgs {  // one composite_frame call, reference extended.rs:30-129
     uint8_t* canvas;       // canvas_w * canvas_h * 4, device
