@@ -89,7 +89,7 @@ SYMBOLS = [
     "webpb200_workspace_sizes", "webpb200_reconstruct_device", "webpb200_decode_animation",
     "webpb200_predict_device_static", "webpb200_predict_device_static_check", "webpb200_open_with_options", "webpb200_set_memory_limit",
     "webpb200_background_color_hint", "webpb200_icc_profile", "webpb200_exif_metadata", "webpb200_xmp_metadata", "webpb200_decode_animation_opts", "webpb200_decode_batch_multi", "webpb200_decode_batch_begin", "webpb200_decode_batch_end", "webpb200_ctx_set_entropy", "webpb200_batch_download_packed",
-    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed",
+    "webpb200_last_transfer", "webpb200_device_pci_bus_id", "webpb200_batch_output_device", "webpb200_last_entropy_ms", "webpb200_debug_entropy_resumed", "webpb200_debug_entropy_faults",
 ]
 
 

@@ -1715,6 +1715,8 @@ extern "C" int webpb200_host_entropy_decode(const uint8_t* file, size_t len, web
 }
 
 // The same through the hand-over structure of the device entropy stage (host_vp8.h), no ALPH part.
+extern "C" void webpb200_debug_entropy_faults(int flags) { set_entropy_faults(flags); }
+
 extern "C" int webpb200_debug_entropy_resumed(const uint8_t* file, size_t len, webpb200_frame_desc* fd, webpb200_mb_desc* mbs, size_t mbs_cap,
                                               int16_t* levels, size_t levels_cap) {
     std::vector<WorkItem> items;

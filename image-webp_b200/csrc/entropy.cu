@@ -288,6 +288,7 @@ struct EntropyArgs {
     int shared_probs;  // every frame of the launch carries the same token probabilities: one table per block instead of one per frame
     unsigned int* rows_done;  // host-mapped, [frame * 8 + partition] = macroblock rows that partition has finished; or null
     int wave;                 // split layout only: blocks per wave (the SM count)
+    int faults;               // test hook (webpb200_debug_entropy_faults): bit 0 = the split layout's mode blocks do nothing
     unsigned int* sync;       // split layout only, zero at launch: [frame] = macroblock rows whose descriptors are in global memory (~0u: the
                               // frame failed), [frames + frame] = somebody has taken the frame's mode partition
 };
@@ -635,6 +636,7 @@ __global__ void __launch_bounds__(32 * kSplitFrames) k_entropy_split(EntropyArgs
     const FrameSmem M = frame_smem(A, smem_all, slot, own, per_frame);
     const int f = A.frame_first + fi;
     if (A.hdrs[f].num_parts == 0) return;  // failed on the host
+    if (modes && (A.faults & 1)) return;   // test hook: as if this block had never been scheduled
 #ifdef ENT_DEBUG
     unsigned long long t0, t1; unsigned sm, wid;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -658,6 +660,9 @@ __global__ void __launch_bounds__(32 * kSplitFrames) k_entropy_split(EntropyArgs
 
 }  // namespace
 
+static int g_entropy_faults = 0;
+void set_entropy_faults(int flags) { g_entropy_faults = flags; }
+
 void upload_entropy_tables_once() {
     cudaMemcpyToSymbol(c_bmode_probs, kBModeProbs, sizeof(kBModeProbs));
 }
@@ -680,6 +685,7 @@ cudaError_t launch_entropy(const BatchDev& b, const Vp8EntropyHdr* d_hdrs, const
     a.shared_probs = same_probs ? 1 : 0;
     a.sync = d_sync;
     a.wave = 1;
+    a.faults = g_entropy_faults;
     static_assert(sizeof(EntropyCtl) <= kCtlBytes, "EntropyCtl outgrew its slot");
     const int F = a.frames_per_block;
     const size_t smem = entropy_smem_per_frame(split ? 1 : max_parts, a.max_mbw, !same_probs) * (size_t)F + (same_probs ? kProbBytes : 0);

@@ -86,6 +86,7 @@ cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches);
 // [b.frame_first, +b.n_frames) from the staged bitstreams into d_mbs / d_levels (both cleared by
 // the caller); d_status[frame] is set to WEBPB200_ERR_BITSTREAM for a frame that ran out of bits
 void upload_entropy_tables_once();
+void set_entropy_faults(int flags);  // test hook, see webpb200_debug_entropy_faults
 // same_probs: every frame of the launch has the same token probabilities (one shared-memory table per block);
 // rows_done (may be null): host-mapped array, [frame * 8 + partition] = number of macroblock rows that
 // token partition has finished (plain store after a system-scope fence), so the host can start

@@ -298,6 +298,12 @@ void webpb200_debug_bpred_eval(int mode, const uint8_t* edge13, uint8_t* out16);
  * the hand-over (csrc/entropy.h).  mbs_cap / levels_cap as in webpb200_host_entropy_decode. */
 int webpb200_debug_entropy_resumed(const uint8_t* file, size_t len, webpb200_frame_desc* fd,
                                    webpb200_mb_desc* mbs, size_t mbs_cap, int16_t* levels, size_t levels_cap);
+/* Test hook for the device entropy stage (process-wide, 0 = none).  Bit 0: in the layout that
+ * webpb200_decode_batch_begin uses for single-partition batches (mode partitions and token partitions
+ * in separate thread blocks), the mode blocks do nothing -- as if the hardware had never started them;
+ * every token warp must then notice, claim its frame's mode partition and decode it itself.  The
+ * results must not change. */
+void webpb200_debug_entropy_faults(int flags);
 
 /* Device-resident seam: reconstruct a batch whose packed arrays the caller already holds
  * in device memory (all pointers are device pointers; d_planes / d_out / d_scratch sized

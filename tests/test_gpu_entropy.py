@@ -312,3 +312,29 @@ def test_two_batches_in_flight(W, synth, oracle):
             assert np.array_equal(bufs[b][i], want[i].reshape(-1)), (b, i)
     for c in ctxs:
         c.close()
+
+
+def test_split_layout_without_its_mode_blocks(W, synth, oracle):
+    """The split layout of k_entropy (what webpb200_decode_batch_begin uses for single-partition batches: mode partitions
+    and token partitions in separate thread blocks).  Nothing guarantees that a frame's mode block starts before its
+    token block: with the test hook that makes every mode block do nothing, each token warp has to claim its frame's
+    mode partition and decode it itself, and every image must still equal the oracle's."""
+    n, w, h = 40, 192, 160
+    files = [synth.webp_simple(synth.vp8_frame(w, h, seed=9100 + i, filter_type=i % 2, filter_level=5 + i)) for i in range(n)]
+    want, st, bad = oracle.decode_batch(files, threads=8)
+    assert bad == 0
+    per = w * h * 3
+    lib = W.lib()
+    for faults in (0, 1):
+        lib.webpb200_debug_entropy_faults(faults)
+        try:
+            bd = W.BatchDecoder(0)
+            bd.set_entropy(bd.ENTROPY_DEVICE)
+            outs = _contiguous_outs(n, per)[1]
+            fl, ol = W.BufferList([np.frombuffer(f, np.uint8) for f in files]), W.BufferList(outs)
+            assert bd.decode_end(bd.decode_begin(fl, ol)) == [0] * n
+            for i in range(n):
+                assert np.array_equal(outs[i], want[i].reshape(-1)), (faults, i)
+            bd.close()
+        finally:
+            lib.webpb200_debug_entropy_faults(0)
