@@ -55,11 +55,17 @@ struct Bits {  // LSB-first bit reader (decoder/mod.rs:697-774)
     }
 };
 
-struct Code {  // prefix code: flat lookup on the next `width` bits
+// Prefix code: two-level lookup.  The next kRoot bits index the root table; codes longer than that lead to a
+// sub-table indexed by the following bits.  (One flat table over the longest code -- 15 bits, 128 KB -- is indexed by
+// what are effectively random bits on noisy planes and misses the first-level cache on most symbols; the root
+// table is 2 KB.)  Entries: symbol | length << 16, or (bit 31) sub-table offset | sub-table width << 16.
+struct Code {
+    static constexpr int kRoot = 9;
     bool single = true;
     uint16_t only = 0;
-    int width = 0;
-    std::vector<uint32_t> lut;  // symbol | length << 16
+    int width = 0;     // longest code
+    int root = 0;      // bits of the root table = min(width, kRoot)
+    std::vector<uint32_t> lut;  // root table, then the sub-tables
 
     int build(const std::vector<uint8_t>& len) {  // huffman.rs:46-177
         int hist[16] = {0}, used = 0;
@@ -81,24 +87,39 @@ struct Code {  // prefix code: flat lookup on the next `width` bits
         if (space != (1u << maxl)) return WEBPB200_ERR_HUFFMAN;
         single = false;
         width = maxl;
-        lut.assign((size_t)1 << maxl, 0);
+        root = maxl < kRoot ? maxl : kRoot;
+        const int sub = maxl - root;  // every sub-table spans the longest code (few of them exist)
+        lut.assign((size_t)1 << root, 0);
         uint32_t next[17] = {0}, c = 0;
         for (int l = 1; l <= maxl; l++) {
             next[l] = c;
             c = (c + (uint32_t)hist[l]) << 1;
         }
+        const uint32_t rmask = (1u << root) - 1;
         for (size_t s = 0; s < len.size(); s++) {
             int l = len[s];
             if (!l) continue;
             uint32_t code = next[l]++, rev = 0;
             for (int i = 0; i < l; i++) rev |= ((code >> i) & 1) << (l - 1 - i);
-            for (uint32_t k = rev; k < (1u << maxl); k += 1u << l) lut[k] = (uint32_t)s | ((uint32_t)l << 16);
+            const uint32_t e = (uint32_t)s | ((uint32_t)l << 16);
+            if (l <= root) {
+                for (uint32_t k = rev; k <= rmask; k += 1u << l) lut[k] = e;
+            } else {
+                uint32_t& r = lut[rev & rmask];
+                if (!(r & 0x80000000u)) {  // first long code under this root prefix: a new sub-table
+                    r = 0x80000000u | ((uint32_t)sub << 16) | (uint32_t)lut.size();  // offsets stay below 2^16: 512 + 512 * 64
+                    lut.resize(lut.size() + ((size_t)1 << sub), 0);
+                }
+                const uint32_t base = lut[rev & rmask] & 0xffffu;
+                for (uint32_t k = rev >> root; k < (1u << sub); k += 1u << (l - root)) lut[base + k] = e;
+            }
         }
         return 0;
     }
     void pair(uint16_t zero, uint16_t one) {  // huffman.rs:183-189
         single = false;
         width = 1;
+        root = 1;
         lut = {zero | (1u << 16), one | (1u << 16)};
     }
     bool get(Bits& b, uint32_t* sym) const {
@@ -106,7 +127,8 @@ struct Code {  // prefix code: flat lookup on the next `width` bits
             *sym = only;
             return true;
         }
-        uint32_t e = lut[b.acc & ((1u << width) - 1)];
+        uint32_t e = lut[b.acc & ((1u << root) - 1)];
+        if (e & 0x80000000u) e = lut[(e & 0xffffu) + ((uint32_t)(b.acc >> root) & ((1u << ((e >> 16) & 15)) - 1))];
         *sym = e & 0xffff;
         return b.drop((int)(e >> 16));
     }
@@ -276,12 +298,19 @@ struct Decoder {
             uint32_t s;
             NEED(g->c[0].get(br, &s));
             if (s < 256) {
-                uint32_t r, b, a;
-                NEED(g->c[1].get(br, &r));
-                NEED(g->c[2].get(br, &b));
-                if (br.n < 15) br.fill();
-                NEED(g->c[3].get(br, &a));
-                const uint32_t px = ((a & 0xff) << 24) | ((r & 0xff) << 16) | (s << 8) | (b & 0xff);
+                uint32_t px;
+                if (g->c[1].single && g->c[2].single && g->c[3].single) {
+                    // only green is coded (the usual ALPH plane): the other channels cost no bits, and nothing the
+                    // reference does between them (decoder/mod.rs:505-520) can fail
+                    px = ((uint32_t)(g->c[3].only & 0xff) << 24) | ((uint32_t)(g->c[1].only & 0xff) << 16) | (s << 8) | (g->c[2].only & 0xff);
+                } else {
+                    uint32_t r, b, a;
+                    NEED(g->c[1].get(br, &r));
+                    NEED(g->c[2].get(br, &b));
+                    if (br.n < 15) br.fill();
+                    NEED(g->c[3].get(br, &a));
+                    px = ((a & 0xff) << 24) | ((r & 0xff) << 16) | (s << 8) | (b & 0xff);
+                }
                 out[i++] = px;
                 if (cache_bits) remember(px);
             } else if (s < 280) {

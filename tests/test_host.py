@@ -285,3 +285,25 @@ def test_vp8l_longest_backward_reference(W, oracle, synth):
             assert np.array_equal(want.reshape(-1), g.astype(np.uint8))
             assert np.array_equal(alpha.reshape(-1), want.reshape(-1)), shift
     assert sorted(set(verdicts)) == [0, 9], verdicts  # both happen; which alignments fail follows from the bits left over before the fill
+
+
+def test_vp8l_host_decoder_all_transform_mixes(W, oracle, synth):
+    """The product's host VP8L decoder (two-level prefix-code tables, literal-only fast path) against the oracle on
+    noisy planes: every transform mix and ALPH filter of the cfg4 generator at a small size, with prefix codes longer
+    than the root table (noise over a gradient gives 10-bit and longer codes) and with all three colour channels
+    coded (subtract-green / colour transform mixes)."""
+    from harness import configs
+    w, h = 208, 120
+    longest = 0
+    for k in range(16):
+        ch = configs.cfg4_alpha_chunk(k, w, h)
+        payload = np.frombuffer(ch[8:], np.uint8)
+        f = synth.webp_extended(synth.vp8_frame(w, h, seed=40 + k, filter_level=0), w, h, ch)
+        want = np.zeros((h, w), np.uint8)
+        flt = C.c_int()
+        assert oracle.lib().ora_read_alpha_chunk(payload.ctypes.data, payload.size, w, h, want.ctypes.data, C.byref(flt)) == 0
+        fd, mbs, levels, alpha = W.host_entropy_decode(f)
+        assert fd.alpha_filter == flt.value
+        assert np.array_equal(alpha.reshape(-1), want.reshape(-1)), k
+        longest = max(longest, len(payload))
+    assert longest > w * h // 2  # the planes are noisy enough not to collapse into a few short codes
