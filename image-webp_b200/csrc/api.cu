@@ -180,7 +180,8 @@ struct webpb200_ctx {
     unsigned int* h_rows = nullptr;      // mapped pinned: [frame * 8 + partition] rows finished (written by k_entropy)
     unsigned int* d_rows = nullptr;
     size_t rows_cap = 0;
-    cudaEvent_t ev[12] = {};
+    cudaEvent_t ev[15] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;  // the ALPH stage runs beside k_predict / k_loopfilter on stream2
     std::string err;
     uint64_t launches = 0;
     std::atomic<bool> in_flight{false};  // a webpb200_decode_batch_begin has not been ended yet
@@ -194,7 +195,7 @@ struct webpb200_ctx {
     int last_entropy = WEBPB200_ENTROPY_HOST;  // where its entropy stage ran
     float last_entropy_ms = 0;  // device time of k_entropy in the last decode_batch (0 if it ran on the host)
     int entropy_where = WEBPB200_ENTROPY_AUTO;  // WEBPB200_ENTROPY_*: where decode_batch runs the boolean decode
-    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status, d_vp8l_px, d_vp8l_planes, d_vp8l_aux, d_vp8l_hand;
+    DevBuf d_frames, d_mbs, d_levels, d_alpha, d_alpha_out, d_aux, d_planes, d_out, d_scratch, d_flush, d_canvas, d_frames_out, d_handoff, d_bits, d_ehdr, d_status, d_vp8l_px, d_vp8l_planes, d_vp8l_aux, d_vp8l_hand;
     // VP8L-compressed ALPH planes of the current batch (entropy-decoded on the host, transforms undone on the device)
     std::vector<int> vp8l_of_item;          // item -> plane index, -1 = none
     std::vector<uint64_t> vp8l_aux_off;     // plane -> word offset of its transform data in the aux arena
@@ -484,6 +485,7 @@ int reserve_device(webpb200_ctx* c) {
     CU(c, c->d_out.reserve((size_t)std::max<uint64_t>(c->out_bytes, 1)), "device out");
     CU(c, c->d_scratch.reserve((size_t)c->bd.lay.total), "device scratch");
     if (c->alpha_bytes) CU(c, c->d_handoff.reserve((size_t)alpha_handoff_size(c->alpha_bytes)), "device alpha handoff");
+    if (c->alpha_bytes) CU(c, c->d_alpha_out.reserve((size_t)c->alpha_bytes), "device alpha planes");
     if (c->vp8l_n) {
         CU(c, c->d_vp8l_px.reserve(3 * 4 * (size_t)c->vp8l_px_words), "device VP8L pixels");
         CU(c, c->d_vp8l_aux.reserve(4 * (size_t)std::max<uint64_t>(c->vp8l_aux_words, 1)), "device VP8L transform data");
@@ -499,6 +501,8 @@ int reserve_device(webpb200_ctx* c) {
     bd.out = c->d_out.p;
     bd.scratch = c->d_scratch.p;
     bd.alpha_lists = reinterpret_cast<const int*>(c->d_aux.p + c->aux_lists_off);
+    bd.alpha_planar = c->alpha_bytes ? c->d_alpha_out.p : nullptr;
+    bd.merge_alpha = 0;
     bd.alpha_handoff = c->alpha_bytes ? reinterpret_cast<uint16_t*>(c->d_handoff.p) : nullptr;
     bd.alpha_handoff_bytes = c->alpha_bytes ? alpha_handoff_size(c->alpha_bytes) : 0;
     std::memset(&bd.vp8l, 0, sizeof(bd.vp8l));
@@ -583,21 +587,43 @@ int reconstruct(webpb200_ctx* c, const BatchDev& bd, unsigned stages, cudaStream
     // per batch, not per pass, so that a trip in any pass is still there when the host looks.  The
     // clears belong to the pass: a timing run records its first event before them.
     if (events) cudaEventRecord(events[0], s);
+    // The ALPH stage (VP8L inverse transforms, un-filter into the planar alpha arena) touches nothing the VP8 kernels
+    // touch, and its gradient filter and predictor transform are wavefronts of their own: it runs beside k_predict and
+    // k_loopfilter on a second stream and joins before the colour conversion, which puts the planes into byte 3 of
+    // the RGBA pixels it writes (stage 8 without stage 4 prepares the planes only).
+    const bool alpha_stage = (stages & 8) && bd.alpha != nullptr &&
+                             (bd.vp8l.n_planes > 0 || bd.alpha_counts[1] + bd.alpha_counts[2] + bd.alpha_counts[3] > 0);
+    if (alpha_stage) {
+        if (!c->stream2) CU(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second stream");
+        cudaStream_t as = c->stream2;
+        CU(c, cudaEventRecord(c->ev_fork, s), "fork");
+        CU(c, cudaStreamWaitEvent(as, c->ev_fork, 0), "fork");
+        if (events) cudaEventRecord(events[12], as);
+        if (int r = run_vp8l(c, bd, 0, bd.vp8l.n_planes, as)) return r;
+        int l = 0;
+        CU(c, launch_alpha(bd, as, &l), "k_alpha");
+        c->launches += (uint64_t)l;
+        if (events) cudaEventRecord(events[13], as);
+        CU(c, cudaEventRecord(c->ev_join, as), "join");
+    } else if (events) {
+        cudaEventRecord(events[12], s);
+        cudaEventRecord(events[13], s);
+    }
     CU(c, cudaMemsetAsync(bd.scratch, 0, 8, s), "clear tickets");
     CU(c, cudaMemsetAsync(bd.scratch + bd.lay.edge_pred_off, 0, (size_t)(bd.lay.zero_bytes - bd.lay.edge_pred_off), s), "clear edge records");
     if (stages & 1) { CU(c, launch_predict(bd, s), "k_predict"); c->launches++; }
     if (events) cudaEventRecord(events[1], s);
     if (stages & 2) { CU(c, launch_loopfilter(bd, s), "k_loopfilter"); c->launches++; }
     if (events) cudaEventRecord(events[2], s);
-    if (stages & 4) { CU(c, launch_yuv2rgb(bd, s), "k_yuv2rgb"); c->launches++; }
-    if (events) cudaEventRecord(events[3], s);
-    if (stages & 8) {
-        if (int r = run_vp8l(c, bd, 0, bd.vp8l.n_planes, s)) return r;
-        int l = 0;
-        CU(c, launch_alpha(bd, s, &l), "k_alpha");
-        c->launches += (uint64_t)l;
+    if (alpha_stage) CU(c, cudaStreamWaitEvent(s, c->ev_join, 0), "join");
+    if (events) cudaEventRecord(events[14], s);
+    if (stages & 4) {
+        BatchDev rgb = bd;
+        rgb.merge_alpha = (stages & (8 | 16)) && bd.alpha != nullptr;  // 16: the planes were un-filtered by the caller
+        CU(c, launch_yuv2rgb(rgb, s), "k_yuv2rgb");
+        c->launches++;
     }
-    if (events) cudaEventRecord(events[4], s);
+    if (events) { cudaEventRecord(events[3], s); cudaEventRecord(events[4], s); }
     return 0;
 }
 
@@ -738,6 +764,8 @@ extern "C" int webpb200_ctx_create(int device, webpb200_ctx** out) {
     }
     c->sm_count = prop.multiProcessorCount;
     for (auto& e : c->ev) cudaEventCreate(&e);
+    cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
     if (upload_tables_once() != cudaSuccess) {
         delete c;
         return WEBPB200_ERR_CUDA;
@@ -760,9 +788,11 @@ extern "C" void webpb200_ctx_destroy(webpb200_ctx* c) {
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->stream3) cudaStreamSynchronize(c->stream3);
     for (PinBuf* b : {&c->h_frames, &c->h_mbs, &c->h_levels, &c->h_alpha, &c->h_aux, &c->h_bits, &c->h_ehdr, &c->h_status, &c->h_vp8l_px, &c->h_vp8l_planes, &c->h_vp8l_aux}) b->release();
-    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status, &c->d_vp8l_px, &c->d_vp8l_planes, &c->d_vp8l_aux, &c->d_vp8l_hand})
+    for (DevBuf* b : {&c->d_frames, &c->d_mbs, &c->d_levels, &c->d_alpha, &c->d_alpha_out, &c->d_aux, &c->d_planes, &c->d_out, &c->d_scratch, &c->d_flush, &c->d_canvas, &c->d_frames_out, &c->d_handoff, &c->d_bits, &c->d_ehdr, &c->d_status, &c->d_vp8l_px, &c->d_vp8l_planes, &c->d_vp8l_aux, &c->d_vp8l_hand})
         b->release();
     for (auto& e : c->ev) cudaEventDestroy(e);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     cudaStreamDestroy(c->stream);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->stream3) cudaStreamDestroy(c->stream3);
@@ -907,8 +937,11 @@ extern "C" int webpb200_batch_time(webpb200_ctx* c, unsigned stages, int iters, 
         float ms = 0;
         cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]);
         total += ms;
+        // events: 0 start, 1 after k_predict, 2 after k_loopfilter, 14 .. 3 = 4 k_yuv2rgb (after the ALPH stage has joined),
+        // 12 .. 13 the ALPH stage on its own stream (beside the first two kernels: the four figures need not add up to the pass)
+        static const int from[4] = {0, 1, 14, 12}, to[4] = {1, 2, 3, 13};
         for (int k = 0; k < 4; k++) {
-            cudaEventElapsedTime(&ms, c->ev[k], c->ev[k + 1]);
+            cudaEventElapsedTime(&ms, c->ev[from[k]], c->ev[to[k]]);
             per[k] += ms;
         }
     }
@@ -1600,17 +1633,9 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
             const size_t lb = sizeof(int16_t) * WEBPB200_LEVELS_PER_MB;
             fail(cudaMemcpyAsync(c->d_levels.p + lb * mb0, c->h_levels.p + lb * mb0, lb * (mb1 - mb0), cudaMemcpyHostToDevice, s), "H2D levels");
         }
-        if (row1 > row0 && !err) {
-            BatchDev bd = c->bd;
-            bd.frame_first = i0;
-            bd.n_frames = i1 - i0;
-            bd.order_first = row0;
-            bd.total_rows = row1 - row0;
-            if (int r = reconstruct(c, bd, 0x7, s, nullptr)) err = r;
-        }
         if (any_alpha && !err) {
             // ALPH planes of this chunk: their filter methods are known now (entropy_one read the chunk
-            // headers), so the un-filter + merge runs per chunk too and nothing is left for the end.
+            // headers), so the un-filter runs per chunk too, ahead of the chunk's colour conversion (which merges the planes), and nothing is left for the end.
             // The chunk's index lists live at [4 * i0, 4 * i1) of the list area, method-major.
             const int nc = i1 - i0;
             int* lists = reinterpret_cast<int*>(c->h_aux.p + c->aux_lists_off) + (size_t)4 * i0;
@@ -1644,6 +1669,14 @@ int decode_items_host_entropy(webpb200_ctx* c, std::vector<WorkItem>&& items, ui
                 if (!err) fail(launch_alpha(bd, s, &l), "k_alpha");
                 c->launches += (uint64_t)l;
             }
+        }
+        if (row1 > row0 && !err) {
+            BatchDev bd = c->bd;
+            bd.frame_first = i0;
+            bd.n_frames = i1 - i0;
+            bd.order_first = row0;
+            bd.total_rows = row1 - row0;
+            if (int r = reconstruct(c, bd, any_alpha ? 0x17 : 0x7, s, nullptr)) err = r;  // 0x10: merge the ALPH planes prepared above
         }
         if (!err && outs)
             if (int r = download_range(c, outs, out_lens, i0, i1)) err = r;
@@ -1753,7 +1786,7 @@ extern "C" int webpb200_workspace_sizes(const webpb200_frame_desc* frames, int n
     if (plane_bytes) *plane_bytes = p;
     if (out_bytes) *out_bytes = o;
     if (scratch_bytes)
-        *scratch_bytes = scratch_layout(rows, mbs, edge_slots_of(frames, n)).total + align256(16 * (uint64_t)std::max(n, 1)) + (alpha_end ? alpha_handoff_size(alpha_end) : 0);
+        *scratch_bytes = scratch_layout(rows, mbs, edge_slots_of(frames, n)).total + align256(16 * (uint64_t)std::max(n, 1)) + (alpha_end ? alpha_handoff_size(alpha_end) + align256(alpha_end) : 0);
     return 0;
 }
 
@@ -1812,6 +1845,7 @@ extern "C" int webpb200_reconstruct_device(const webpb200_frame_desc* hf, const 
     if (alpha_end) {
         bd.alpha_handoff = reinterpret_cast<uint16_t*>(scratch + bd.lay.total + align256(16 * (uint64_t)n));
         bd.alpha_handoff_bytes = alpha_handoff_size(alpha_end);
+        bd.alpha_planar = reinterpret_cast<uint8_t*>(bd.alpha_handoff) + bd.alpha_handoff_bytes;
     }
     return reconstruct(c, bd, stages, s, nullptr);
 }

@@ -1143,6 +1143,10 @@ struct RgbArgs {
     const uint8_t* planes;
     uint8_t* out;
     int q_first, q_end;  // row pairs [q_first, q_end) only (pair q = rows 2q-1, 2q)
+    // ALPH merge (decoder.rs:718-734): alpha of a frame with an ALPH plane = the un-filtered plane (alpha_planar) or, for
+    // filter method none, the residual plane itself (alpha_res); both null = byte 3 stays 255
+    const uint8_t* alpha_res;
+    const uint8_t* alpha_planar;
 };
 
 // Horizontal half of the fancy upsampler for 8 pixels of one chroma row, TWO pixels per register (16-bit fields:
@@ -1173,14 +1177,20 @@ __device__ __forceinline__ void chroma_blend(const uint32_t* hm, const uint32_t*
 
 // 8 pixels -> tightly packed RGB8 / RGBA8 (yuv.rs:285-289; byte 3 of RGBA belongs to the ALPH merge
 // that always follows, decoder.rs:704-734: 255 until then)
-__device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int n, int bpp) {
+// (al = the 8 alpha bytes of the row segment, RGBA only)
+__device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int n, int bpp, uint2 al) {
     if (bpp == 4) {
+        uint32_t q[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) q[i] = __byte_perm(px[i], i < 4 ? al.x : al.y, 0x4210 | ((i & 3) << 12));  // r g b | alpha byte i
         if (n == 8 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
             uint4* o = reinterpret_cast<uint4*>(out);
-            o[0] = make_uint4(px[0] | 0xff000000u, px[1] | 0xff000000u, px[2] | 0xff000000u, px[3] | 0xff000000u);
-            o[1] = make_uint4(px[4] | 0xff000000u, px[5] | 0xff000000u, px[6] | 0xff000000u, px[7] | 0xff000000u);
+            o[0] = make_uint4(q[0], q[1], q[2], q[3]);
+            o[1] = make_uint4(q[4], q[5], q[6], q[7]);
         } else {
-            for (int i = 0; i < n; i++) reinterpret_cast<uint32_t*>(out)[i] = px[i] | 0xff000000u;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (i < n) reinterpret_cast<uint32_t*>(out)[i] = q[i];
         }
         return;
     }
@@ -1204,6 +1214,18 @@ __device__ __forceinline__ void store_row8(uint8_t* out, const uint32_t* px, int
     } else {
         for (int i = 0; i < n; i++) { out[3 * i] = (uint8_t)px[i]; out[3 * i + 1] = (uint8_t)(px[i] >> 8); out[3 * i + 2] = (uint8_t)(px[i] >> 16); }
     }
+}
+
+// the 8 alpha bytes at p (n valid), by one 8-byte load when the address allows
+__device__ __forceinline__ uint2 load_alpha8(const uint8_t* p, int n) {
+    if (n == 8 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) return __ldg(reinterpret_cast<const uint2*>(p));
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (i < n) lo |= (uint32_t)__ldg(p + i) << (8 * i);
+        if (i + 4 < n) hi |= (uint32_t)__ldg(p + i + 4) << (8 * i);
+    }
+    return make_uint2(lo, hi);
 }
 
 #ifndef RGB_PAIRS_PER_BLOCK
@@ -1271,11 +1293,16 @@ __global__ void __launch_bounds__(64 * kRgbPairsPerBlock) k_yuv2rgb(RgbArgs A) {
     uint32_t px[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb((int)__byte_perm(i < 4 ? ywa.x : ywa.y, 0, 0x4440 | (i & 3)), (int)ua[i], (int)va[i]);
-    store_row8(A.out + fd->out_off + ((size_t)ya * w + x0) * bpp, px, n, bpp);
+    // ALPH merge: the plane's bytes for this row segment, or 255
+    const uint8_t* asrc = nullptr;
+    if (bpp == 4 && fd->alpha_mode) asrc = fd->alpha_filter == 0 ? A.alpha_res : A.alpha_planar;
+    if (asrc) asrc += fd->alpha_off + x0;
+    const uint2 opaque = make_uint2(0xffffffffu, 0xffffffffu);
+    store_row8(A.out + fd->out_off + ((size_t)ya * w + x0) * bpp, px, n, bpp, asrc ? load_alpha8(asrc + (size_t)ya * w, n) : opaque);
     if (has_b) {
 #pragma unroll
         for (int i = 0; i < 8; i++) px[i] = yuv_to_rgb((int)__byte_perm(i < 4 ? ywb.x : ywb.y, 0, 0x4440 | (i & 3)), (int)ub[i], (int)vb[i]);
-        store_row8(A.out + fd->out_off + ((size_t)yb * w + x0) * bpp, px, n, bpp);
+        store_row8(A.out + fd->out_off + ((size_t)yb * w + x0) * bpp, px, n, bpp, asrc ? load_alpha8(asrc + (size_t)yb * w, n) : opaque);
     }
 }
 
@@ -1287,20 +1314,16 @@ __global__ void __launch_bounds__(64 * kRgbPairsPerBlock) k_yuv2rgb(RgbArgs A) {
 //   vertical:   column prefix sums, row 0 is a horizontal prefix sum
 //   gradient:   clamp(L + T - TL) -- a true 2-D recurrence, done as a row-skewed wavefront
 // ---------------------------------------------------------------------------------------------
+// The un-filtered alpha goes to a PLANAR arena (same offsets as the residual arena); k_yuv2rgb, which runs after
+// these kernels, puts it into byte 3 of the RGBA words it writes anyway.  (Writing byte 3 of finished pixels from
+// here cost a 4-sector store per 32 useful bytes and a second pass over the output.)  Filter "none" has no kernel:
+// k_yuv2rgb reads the residual plane itself.
 struct AlphaArgs {
     const webpb200_frame_desc* frames;
     const uint8_t* alpha;
-    uint8_t* out;
+    uint8_t* out;     // planar alpha arena
     const int* list;  // frame indices handled by this launch
 };
-
-__global__ void k_alpha_none(AlphaArgs A) {
-    const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.y];
-    const size_t n = (size_t)fd->width * fd->height;
-    const uint8_t* a = A.alpha + fd->alpha_off;
-    uint8_t* o = A.out + fd->out_off;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) o[4 * i + 3] = a[i];
-}
 
 // first column (horizontal filter) / first row (vertical filter): one warp per image does the
 // serial prefix sum in 32-element steps
@@ -1308,7 +1331,7 @@ __global__ void k_alpha_seed(AlphaArgs A, int vertical) {
     const webpb200_frame_desc* fd = A.frames + A.list[blockIdx.x];
     const int w = fd->width, h = fd->height;
     const uint8_t* a = A.alpha + fd->alpha_off;
-    uint8_t* o = A.out + fd->out_off;
+    uint8_t* o = A.out + fd->alpha_off;
     const int lane = threadIdx.x;
     const int n = vertical ? w : h;
     const size_t stride = vertical ? 1 : (size_t)w;
@@ -1321,7 +1344,7 @@ __global__ void k_alpha_seed(AlphaArgs A, int vertical) {
             if (lane >= d) v += u;
         }
         v += carry;
-        if (i < n) o[(size_t)i * stride * 4 + 3] = (uint8_t)v;
+        if (i < n) o[(size_t)i * stride] = (uint8_t)v;
         carry = __shfl_sync(kFull, v, 31) & 0xff;
     }
 }
@@ -1334,8 +1357,8 @@ __global__ void k_alpha_rows(AlphaArgs A) {
     if (y >= h) return;
     const int lane = threadIdx.x & 31;
     const uint8_t* a = A.alpha + fd->alpha_off + (size_t)y * w;
-    uint8_t* o = A.out + fd->out_off + (size_t)y * w * 4;
-    unsigned carry = o[3];
+    uint8_t* o = A.out + fd->alpha_off + (size_t)y * w;
+    unsigned carry = o[0];
     for (int base = 1; base < w; base += 32) {
         const int x = base + lane;
         unsigned v = x < w ? a[x] : 0;
@@ -1344,7 +1367,7 @@ __global__ void k_alpha_rows(AlphaArgs A) {
             if (lane >= d) v += u;
         }
         v += carry;
-        if (x < w) o[(size_t)x * 4 + 3] = (uint8_t)v;
+        if (x < w) o[x] = (uint8_t)v;
         carry = __shfl_sync(kFull, v, 31) & 0xff;
     }
 }
@@ -1356,8 +1379,8 @@ __global__ void k_alpha_cols(AlphaArgs A) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= w) return;
     const uint8_t* a = A.alpha + fd->alpha_off;
-    uint8_t* o = A.out + fd->out_off;
-    unsigned v = o[(size_t)x * 4 + 3];
+    uint8_t* o = A.out + fd->alpha_off;
+    unsigned v = o[x];
     for (int y0 = 1; y0 < h; y0 += 8) {  // 8 independent loads in flight, then the serial sums
         unsigned r[8];
 #pragma unroll
@@ -1366,7 +1389,7 @@ __global__ void k_alpha_cols(AlphaArgs A) {
         for (int i = 0; i < 8; i++) {
             if (y0 + i < h) {
                 v = (v + r[i]) & 0xff;
-                o[((size_t)(y0 + i) * w + x) * 4 + 3] = (uint8_t)v;
+                o[(size_t)(y0 + i) * w + x] = (uint8_t)v;
             }
         }
     }
@@ -1422,7 +1445,7 @@ __global__ void __launch_bounds__(kGradWarps * 32, 4) k_alpha_gradient(GradArgs 
         const int nbands = (h + 31) >> 5, ntiles = (w + 31) >> 5;
         if (g >= nbands) continue;
         const uint8_t* a = G.a.alpha + fd->alpha_off;
-        uint8_t* o = G.a.out + fd->out_off;
+        uint8_t* o = G.a.out + fd->alpha_off;
         uint16_t* hand = G.handoff + (fd->alpha_off >> 4);  // row g of it = last row of band g
         const uint16_t* above = hand + (size_t)(g - 1) * w;
         uint16_t* below = g + 1 < nbands ? hand + (size_t)g * w : nullptr;  // written by lane 31 only
@@ -1443,12 +1466,12 @@ __global__ void __launch_bounds__(kGradWarps * 32, 4) k_alpha_gradient(GradArgs 
 #pragma unroll
             for (int r = 0; r < 32; r++) pre[r] = (r < nrows && x < w) ? a[(size_t)(y0 + r) * w + x] : 0;
         };
-        auto flush = [&](int c) {  // finished tile c -> byte 3 of the output pixels
+        auto flush = [&](int c) {  // finished tile c -> the planar alpha arena
             const int x = 32 * c + lane;
             const uint8_t* tl = S.tile[c & 1];
             if (x < w) {
 #pragma unroll 8
-                for (int r = 0; r < nrows; r++) o[((size_t)(y0 + r) * w + x) * 4 + 3] = tl[r * 32 + lane];
+                for (int r = 0; r < nrows; r++) o[(size_t)(y0 + r) * w + x] = tl[r * 32 + lane];
             }
         };
 
@@ -1636,6 +1659,8 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
 cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
     RgbArgs a;
     a.frames = b.frames + b.frame_first; a.planes = b.planes; a.out = b.out;
+    a.alpha_res = b.merge_alpha ? b.alpha : nullptr;
+    a.alpha_planar = b.merge_alpha ? b.alpha_planar : nullptr;
     // thread = 8 pixels x 2 rows; block = 64 x 2 threads = 512 pixels x 4 rows; row pairs: h/2 + 1
     const int q_all = (int)b.max_h / 2 + 1;
     a.q_first = b.q_end > b.q_first ? b.q_first : 0;
@@ -1649,14 +1674,10 @@ cudaError_t launch_yuv2rgb(const BatchDev& b, cudaStream_t s) {
 cudaError_t launch_alpha(const BatchDev& b, cudaStream_t s, int* launches) {
     // frames grouped by ALPH filter method; the index lists were uploaded with the batch
     const int* const counts = b.alpha_counts;
-    if (counts[0] + counts[1] + counts[2] + counts[3] == 0) return cudaSuccess;
+    if (counts[1] + counts[2] + counts[3] == 0) return cudaSuccess;  // (filter none: k_yuv2rgb reads the residual plane)
+    if (!b.alpha_planar) return cudaErrorInvalidValue;
     AlphaArgs a;
-    a.frames = b.frames; a.alpha = b.alpha; a.out = b.out;
-    if (counts[0]) {
-        a.list = b.alpha_lists;
-        k_alpha_none<<<dim3(b.sm_count * 2, counts[0]), 256, 0, s>>>(a);
-        ++*launches;
-    }
+    a.frames = b.frames; a.alpha = b.alpha; a.out = b.alpha_planar;
     if (counts[1]) {
         a.list = b.alpha_lists + b.n_frames;
         k_alpha_seed<<<counts[1], 32, 0, s>>>(a, 0);

@@ -42,6 +42,8 @@ struct BatchDev {
     const int16_t* levels;
     int levels_packed;      // levels are in k_entropy's packed form (kernels.cu, "Level records"), not the dense boundary format
     const uint8_t* alpha;  // alpha residual planes (may be null)
+    uint8_t* alpha_planar;  // un-filtered alpha planes, same offsets (written by k_alpha_*, read by k_yuv2rgb; may be null when no frame has ALPH)
+    int merge_alpha;        // k_yuv2rgb puts the alpha planes into byte 3 of RGBA pixels (set by the pass that ran the ALPH stage)
     uint8_t* planes;
     uint8_t* out;
     uint8_t* scratch;
