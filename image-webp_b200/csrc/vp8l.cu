@@ -61,6 +61,28 @@ __device__ __forceinline__ uint32_t predict_mixed(int mode, uint32_t L, uint32_t
     return p;
 }
 
+// the same for a mode that every lane of the step shares (a plane with one predictor, or lanes inside one block):
+// only that predictor is computed
+__device__ __forceinline__ uint32_t predict_one(int mode, uint32_t L, uint32_t T, uint32_t TL, uint32_t TR) {
+    switch (mode) {
+        case 0: return 0xff000000u;
+        case 1: return L;
+        case 2: return T;
+        case 3: return TR;
+        case 4: return TL;
+        case 5: return avg4(avg4(L, TR), T);
+        case 6: return avg4(L, TL);
+        case 7: return avg4(L, T);
+        case 8: return avg4(TL, T);
+        case 9: return avg4(T, TR);
+        case 10: return avg4(avg4(L, TL), avg4(T, TR));
+        case 11: return select4(L, T, TL);
+        case 12: return clamp_full(L, T, TL);
+        case 13: return clamp_half(L, T, TL);
+        default: return 0u;  // the reference leaves such pixels as they are
+    }
+}
+
 __device__ __forceinline__ uint2 ld_unit(const uint2* p) {
     unsigned long long v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
@@ -248,25 +270,35 @@ __global__ void __launch_bounds__(kWarps * 32) k_vp8l_stage(StageArgs A) {
                     tr = 0;
                 }
                 const uint32_t TRv = tr;
-                if (row_ok && x >= 0 && x < w) {
+                const bool in = row_ok && x >= 0 && x < w;
+                if (in && (x & bmask) == 0 && x > 0) {
+                    mode_w = mode_next;
+                    const int nb = (x >> S.bits) + 1;
+                    mode_next = nb < bx ? mrow[nb] : 0u;
+                }
+                // do all the lanes that predict in this step use the same predictor?  (a vote: the warp is converged here)
+                const int mode = (int)((mode_w >> 8) & 0xffu);
+                const bool general = in && y > 0 && x > 0;
+                const int mode0 = (int)__reduce_max_sync(kFull, general ? (unsigned)mode : 0u);
+                const bool uniform = __all_sync(kFull, !general || mode == mode0);
+                if (in) {
                     if ((x & 7) == 0 && x > 0) {
                         store8(x);
                         load8(x + 8);
-                    }
-                    if ((x & bmask) == 0 && x > 0) {
-                        mode_w = mode_next;
-                        const int nb = (x >> S.bits) + 1;
-                        mode_next = nb < bx ? mrow[nb] : 0u;
                     }
                     const uint32_t res = ring[x & 15];
                     uint32_t pred;
                     if (y == 0) pred = x == 0 ? 0xff000000u : L;          // top row: left; first pixel: opaque black
                     else if (x == 0) pred = T;                              // left column: top
                     else {
-                        const int mode = (int)((mode_w >> 8) & 0xffu);
                         // the last column's top-right is the first pixel of the CURRENT row (memory order, 3 | 108-116)
-                        pred = predict_mixed(mode, L, T, TL, x == w - 1 ? first : TRv);
-                        if (mode >= 14) pred = 0u;  // the reference leaves such pixels as they are
+                        const uint32_t trp = x == w - 1 ? first : TRv;
+                        if (uniform) {
+                            pred = predict_one(mode0, L, T, TL, trp);
+                        } else {
+                            pred = predict_mixed(mode, L, T, TL, trp);
+                            if (mode >= 14) pred = 0u;  // the reference leaves such pixels as they are
+                        }
                     }
                     mine = add4(res, pred);
                     orow[x] = mine;
