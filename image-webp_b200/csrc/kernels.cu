@@ -879,11 +879,20 @@ struct FilterArgs {
     uint32_t total_rows;
 };
 
-#ifndef FILTER_MIN_BLOCKS
-#define FILTER_MIN_BLOCKS 3
+// Two register budgets, like k_predict: four blocks per SM (56 registers) when every resident warp has work -- more
+// warps to hide latency behind: cfg2 0.504 -> 0.467 ms, cfg3 256 x 4K 8.85 -> 8.27 ms -- and three (72 registers, fewer
+// instructions on each macroblock's dependency chain) when the rows of a few large frames wait on each other (32 x 4K:
+// 1.76 ms against 1.93).  Five blocks (46 registers) and six (40, spills) are slower on both.
+#ifndef FILTER_BLOCKS_T
+#define FILTER_BLOCKS_T 4
 #endif
+#ifndef FILTER_BLOCKS_L
+#define FILTER_BLOCKS_L 3
+#endif
+constexpr int kFilterBlocksThroughput = FILTER_BLOCKS_T, kFilterBlocksLatency = FILTER_BLOCKS_L;
 
-__global__ void __launch_bounds__(kThreads, FILTER_MIN_BLOCKS) k_loopfilter(FilterArgs A) {
+template <int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) k_loopfilter(FilterArgs A) {
     __shared__ FilterSmem smem[kWarpsPerBlock];
     const int lane = threadIdx.x & 31;
     FilterSmem& S = smem[threadIdx.x >> 5];
@@ -1596,7 +1605,7 @@ void wavefront_blocks_per_sm(int* predict_blocks, int* predict_blocks_latency, i
     int p = 0, l = 0, f = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p, reinterpret_cast<const void*>(k_predict<kPredictBlocksThroughput, false>), kThreads, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&l, reinterpret_cast<const void*>(k_predict<kPredictBlocksLatency, false>), kThreads, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&f, reinterpret_cast<const void*>(k_loopfilter), kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&f, reinterpret_cast<const void*>(k_loopfilter<kFilterBlocksThroughput>), kThreads, 0);
     *predict_blocks = p < 1 ? 1 : p;
     *predict_blocks_latency = l < 1 ? 1 : l;
     *filter_blocks = f < 1 ? 1 : f;
@@ -1652,7 +1661,13 @@ cudaError_t launch_loopfilter(const BatchDev& b, cudaStream_t s) {
     a.order = reinterpret_cast<const uint32_t*>(b.scratch + b.lay.order_off) + b.order_first;
     a.mbinfo = b.scratch + b.lay.mbinfo_off;
     a.total_rows = b.total_rows;
-    k_loopfilter<<<WF_GRID("WF_FGRID", wavefront_grid(b, b.filter_blocks)), kThreads, 0, s>>>(a);
+#ifndef LF_LATENCY_ROWS
+#define LF_LATENCY_ROWS 2   // the latency build up to this many times the rows it keeps resident
+#endif
+    const int sms = b.sm_count > 0 ? b.sm_count : 1;
+    const bool latency_bound = (uint64_t)b.total_rows <= (uint64_t)LF_LATENCY_ROWS * kFilterBlocksLatency * sms * kWarpsPerBlock;
+    if (latency_bound) k_loopfilter<kFilterBlocksLatency><<<WF_GRID("WF_FGRID", wavefront_grid(b, std::min(b.filter_blocks, kFilterBlocksLatency))), kThreads, 0, s>>>(a);
+    else k_loopfilter<kFilterBlocksThroughput><<<WF_GRID("WF_FGRID", wavefront_grid(b, b.filter_blocks)), kThreads, 0, s>>>(a);
     return cudaGetLastError();
 }
 
