@@ -55,17 +55,11 @@ struct Bits {  // LSB-first bit reader (decoder/mod.rs:697-774)
     }
 };
 
-// Prefix code: two-level lookup.  The next kRoot bits index the root table; codes longer than that lead to a
-// sub-table indexed by the following bits.  (One flat table over the longest code -- 15 bits, 128 KB -- is indexed by
-// what are effectively random bits on noisy planes and misses the first-level cache on most symbols; the root
-// table is 2 KB.)  Entries: symbol | length << 16, or (bit 31) sub-table offset | sub-table width << 16.
-struct Code {
-    static constexpr int kRoot = 9;
+struct Code {  // prefix code: flat lookup on the next `width` bits
     bool single = true;
     uint16_t only = 0;
-    int width = 0;     // longest code
-    int root = 0;      // bits of the root table = min(width, kRoot)
-    std::vector<uint32_t> lut;  // root table, then the sub-tables
+    int width = 0;
+    std::vector<uint32_t> lut;  // symbol | length << 16
 
     int build(const std::vector<uint8_t>& len) {  // huffman.rs:46-177
         int hist[16] = {0}, used = 0;
@@ -87,39 +81,24 @@ struct Code {
         if (space != (1u << maxl)) return WEBPB200_ERR_HUFFMAN;
         single = false;
         width = maxl;
-        root = maxl < kRoot ? maxl : kRoot;
-        const int sub = maxl - root;  // every sub-table spans the longest code (few of them exist)
-        lut.assign((size_t)1 << root, 0);
+        lut.assign((size_t)1 << maxl, 0);
         uint32_t next[17] = {0}, c = 0;
         for (int l = 1; l <= maxl; l++) {
             next[l] = c;
             c = (c + (uint32_t)hist[l]) << 1;
         }
-        const uint32_t rmask = (1u << root) - 1;
         for (size_t s = 0; s < len.size(); s++) {
             int l = len[s];
             if (!l) continue;
             uint32_t code = next[l]++, rev = 0;
             for (int i = 0; i < l; i++) rev |= ((code >> i) & 1) << (l - 1 - i);
-            const uint32_t e = (uint32_t)s | ((uint32_t)l << 16);
-            if (l <= root) {
-                for (uint32_t k = rev; k <= rmask; k += 1u << l) lut[k] = e;
-            } else {
-                uint32_t& r = lut[rev & rmask];
-                if (!(r & 0x80000000u)) {  // first long code under this root prefix: a new sub-table
-                    r = 0x80000000u | ((uint32_t)sub << 16) | (uint32_t)lut.size();  // offsets stay below 2^16: 512 + 512 * 64
-                    lut.resize(lut.size() + ((size_t)1 << sub), 0);
-                }
-                const uint32_t base = lut[rev & rmask] & 0xffffu;
-                for (uint32_t k = rev >> root; k < (1u << sub); k += 1u << (l - root)) lut[base + k] = e;
-            }
+            for (uint32_t k = rev; k < (1u << maxl); k += 1u << l) lut[k] = (uint32_t)s | ((uint32_t)l << 16);
         }
         return 0;
     }
     void pair(uint16_t zero, uint16_t one) {  // huffman.rs:183-189
         single = false;
         width = 1;
-        root = 1;
         lut = {zero | (1u << 16), one | (1u << 16)};
     }
     bool get(Bits& b, uint32_t* sym) const {
@@ -127,8 +106,7 @@ struct Code {
             *sym = only;
             return true;
         }
-        uint32_t e = lut[b.acc & ((1u << root) - 1)];
-        if (e & 0x80000000u) e = lut[(e & 0xffffu) + ((uint32_t)(b.acc >> root) & ((1u << ((e >> 16) & 15)) - 1))];
+        uint32_t e = lut[b.acc & ((1u << width) - 1)];
         *sym = e & 0xffff;
         return b.drop((int)(e >> 16));
     }

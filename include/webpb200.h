@@ -259,14 +259,18 @@ int webpb200_batch_prepare(webpb200_ctx* c, const uint8_t* const* files, const s
 int webpb200_batch_upload(webpb200_ctx* c);
 /* stages: bit0 dequant+IWHT/IDCT+intra prediction (mod.rs:673-783, 866, 898-952),
  * bit1 loop filter (mod.rs:966-1244), bit2 YUV->RGB(A) (mod.rs:184-241, yuv.rs),
- * bit3 alpha un-filter + merge (decoder.rs:718-734); 0xF = all.  Asynchronous. */
+ * bit3 alpha un-filter + merge (decoder.rs:718-734); 0xF = all.  Asynchronous.
+ * The ALPH stage (bit3) un-filters into a planar alpha arena on a second stream beside bit0 / bit1, and
+ * the colour conversion of the SAME call (bit2) puts the plane into byte 3 of the RGBA pixels it
+ * writes: bit3 without bit2 prepares the planes only, bit2 without bit3 leaves byte 3 at 255. */
 int webpb200_batch_reconstruct(webpb200_ctx* c, unsigned stages);
 int webpb200_batch_sync(webpb200_ctx* c);
 int webpb200_batch_download(webpb200_ctx* c, uint8_t* const* outs, const size_t* out_lens);
 /* Runs reconstruct(stages) `iters` times back to back and returns the mean device time of
  * one pass in milliseconds, measured with CUDA events on the context's stream.  If
  * flush_l2 != 0 a buffer larger than L2 is overwritten between passes (outside the
- * timed spans).  kernel_ms (may be NULL) receives per-kernel mean times [4]. */
+ * timed spans).  kernel_ms (may be NULL) receives per-kernel mean times [4]: prediction, loop filter,
+ * colour conversion, ALPH stage (which runs beside the first two: the four need not add up to the pass). */
 int webpb200_batch_time(webpb200_ctx* c, unsigned stages, int iters, int flush_l2, float* ms_per_pass,
                         float* kernel_ms);
 /* introspection for tests and bench */
