@@ -1135,8 +1135,12 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
                 longest = std::max(longest, (double)frames[i].mbw * frames[i].mbh / hdrs[i].num_parts);
                 streams += hdrs[i].num_parts;
             }
-        const double est_device_us = longest * c->dev_us_per_mb * std::max(1.0, streams / 1184.0);
-        const double est_host_us = (double)c->total_mbs * c->host_us_per_mb / std::max(1, std::min(host_threads, n));
+        // ALPH planes are decoded by the same host threads: beside k_entropy when the device decodes the VP8 tokens, on
+        // top of the VP8 work when the host does (6 ns per alpha pixel: a VP8L plane on one core of the boxes measured)
+        const int workers = std::max(1, std::min(host_threads, n));
+        const double est_alph_us = (double)c->alpha_bytes * 0.006 / workers;
+        const double est_device_us = std::max(longest * c->dev_us_per_mb * std::max(1.0, streams / 1184.0), est_alph_us);
+        const double est_host_us = (double)c->total_mbs * c->host_us_per_mb / workers + est_alph_us;
         if (est_device_us > est_host_us) return kPreferHostEntropy;
         c->last_chain_mbs = longest * std::max(1.0, streams / 1184.0);
     } else {
