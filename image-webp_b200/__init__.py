@@ -16,6 +16,7 @@ The directory name carries a hyphen, so import it with
 """
 import ctypes as C
 import os
+import weakref
 import subprocess
 
 import numpy as np
@@ -344,23 +345,31 @@ def vp8_decode_frame(vp8_payload):
 
 
 class PinnedBuffer:
-    """Page-locked host memory exposed as a numpy uint8 array (webpb200_host_alloc)."""
+    """Page-locked host memory exposed as a numpy uint8 array (webpb200_host_alloc).  The memory lives as long as
+    any numpy view of it does: it is released when the last view and this object are gone, or by free()."""
 
     def __init__(self, nbytes):
         self.ptr = lib().webpb200_host_alloc(nbytes)
         if not self.ptr:
             raise DecodingError(101, "pinned allocation of %d bytes failed" % nbytes)
         self.nbytes = nbytes
-        self.array = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(self.ptr))
+        backing = (C.c_uint8 * nbytes).from_address(self.ptr)   # every view's base chain ends in this object
+        self._fin = weakref.finalize(backing, _host_free, self.ptr)
+        self.array = np.ctypeslib.as_array(backing)
 
     def free(self):
+        """Release the memory now (the caller vouches that no view of it is used any more)."""
         if self.ptr:
             self.array = None
-            lib().webpb200_host_free(self.ptr)
+            self._fin()
             self.ptr = None
 
-    def __del__(self):
-        self.free()
+
+def _host_free(ptr):
+    try:
+        lib().webpb200_host_free(ptr)
+    except Exception:  # interpreter shutdown
+        pass
 
 
 def device_pci_bus_id(device):
