@@ -351,3 +351,34 @@ def test_vp8l_alpha_transforms_on_device(W, bd, oracle, synth, size):
     bd.download([o.reshape(-1) for o in outs2])
     for a, b in zip(again, outs2):
         assert np.array_equal(a, b)
+
+
+def test_alpha_stage_bits_and_pinned_views(W, bd, oracle, synth):
+    """Staged API: the ALPH merge happens in the colour conversion of the same reconstruct call (include/webpb200.h): without
+    stage bit 3 byte 3 of every RGBA pixel stays 255, with it the plane is merged, whatever the filter method; bit 3 alone
+    changes no pixel.  And a numpy view of a PinnedBuffer keeps the pinned memory alive after the object is gone."""
+    w, h = 72, 40
+    files, wants = [], []
+    for filtering in range(4):
+        alpha = np.random.default_rng(900 + filtering).integers(0, 256, (h, w)).astype(np.uint8)
+        vp8 = synth.vp8_frame(w, h, seed=77 + filtering, filter_type=filtering & 1, filter_level=12)
+        files.append(synth.webp_extended(vp8, w, h, synth.alph_raw(alpha, filtering=filtering)))
+        wants.append(oracle.WebPDecoder(files[-1]).read_image())
+    assert bd.prepare(files) == [0] * 4
+    bd.upload()
+    pin = W.PinnedBuffer(4 * w * h * 4)
+    view = pin.array
+    outs = [view[i * w * h * 4:(i + 1) * w * h * 4].reshape(h, w, 4) for i in range(4)]
+    del pin                                            # the views own the memory now
+    bd.reconstruct(bd.STAGE_PREDICT | bd.STAGE_LOOPFILTER | bd.STAGE_RGB)
+    bd.download(outs)
+    for o, want in zip(outs, wants):
+        assert np.array_equal(o[:, :, :3], want[:, :, :3]) and (o[:, :, 3] == 255).all()
+    bd.reconstruct(bd.STAGE_ALPHA)                     # prepares the planes only
+    bd.download(outs)
+    for o in outs:
+        assert (o[:, :, 3] == 255).all()
+    bd.reconstruct()
+    bd.download(outs)
+    for o, want in zip(outs, wants):
+        assert np.array_equal(o, want)
