@@ -1136,9 +1136,13 @@ int decode_batch_device_entropy(webpb200_ctx* c, const std::vector<WorkItem>& it
                 streams += hdrs[i].num_parts;
             }
         // ALPH planes are decoded by the same host threads: beside k_entropy when the device decodes the VP8 tokens, on
-        // top of the VP8 work when the host does (6 ns per alpha pixel: a VP8L plane on one core of the boxes measured)
+        // top of the VP8 work when the host does (6 ns per pixel of a VP8L-compressed plane on one core of the boxes measured)
         const int workers = std::max(1, std::min(host_threads, n));
-        const double est_alph_us = (double)c->alpha_bytes * 0.006 / workers;
+        double vp8l_px = 0;  // (raw ALPH planes cost the host a copy; the compression method is the chunk's first byte, extended.rs:266-283)
+        for (int i = 0; i < n; i++)
+            if (!c->items[i].status && c->items[i].alph && c->items[i].alph_len > 0 && (c->items[i].alph[0] & 3) == 1)
+                vp8l_px += (double)frames[i].width * frames[i].height;
+        const double est_alph_us = vp8l_px * 0.006 / workers;
         const double est_device_us = std::max(longest * c->dev_us_per_mb * std::max(1.0, streams / 1184.0), est_alph_us);
         const double est_host_us = (double)c->total_mbs * c->host_us_per_mb / workers + est_alph_us;
         if (est_device_us > est_host_us) return kPreferHostEntropy;
