@@ -9,7 +9,8 @@ from harness import synth as S
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 6
 cores = os.cpu_count() or 1
-files = S.make_batch(S.cfg2_image, n, threads=cores)
+CFG = os.environ.get("INFLIGHT_CFG", "cfg2")
+files = S.make_batch(S.cfg3_image if CFG == "cfg3" else S.cfg2_image, n, threads=cores)
 starts, total = [], 0
 for f in files:
     starts.append(total); total += (len(f) + 63) & ~63
@@ -18,8 +19,8 @@ pf = []
 for f, o in zip(files, starts):
     pin_in.array[o:o + len(f)] = np.frombuffer(f, dtype=np.uint8); pf.append(pin_in.array[o:o + len(f)])
 fl = W.BufferList(pf)
-per = 512 * 512 * 3
-KMAX = 4
+per = (3840 * 2160 if CFG == 'cfg3' else 512 * 512) * 3
+KMAX = int(os.environ.get('INFLIGHT_KMAX', '4'))
 ctxs = [W.BatchDecoder(0) for _ in range(KMAX)]
 pins = [W.PinnedBuffer(n * per) for _ in range(KMAX)]
 outs = [W.BufferList([p.array[i * per:(i + 1) * per] for i in range(n)]) for p in pins]
@@ -50,4 +51,4 @@ for download in DL:
         for k in range(K): end(pend[k])
         ms = 1e3 * (time.perf_counter() - t0) / total_steps
         print("download %d  in flight %d: %.1f ms per step = %.2f GPix/s   k_entropy of the last calls: %s" %
-              (download, K, ms, n * 512 * 512 / ms / 1e6, " ".join("%.1f" % c.last_entropy_ms() for c in ctxs[:K])), flush=True)
+              (download, K, ms, n * (per // 3) / ms / 1e6, " ".join("%.1f" % c.last_entropy_ms() for c in ctxs[:K])), flush=True)
