@@ -1,3 +1,7 @@
+#!/usr/bin/env python3
+"""Per-SM load and chain times of k_entropy_split from the printf lines of an ENT_DEBUG build
+(tools/ab_build.sh entdbg "-DENT_DEBUG"; WEBPB200_SO=ab/libwebpb200_entdbg.so python tools/entropy_ab.py 1024 > log):
+usage: tools/entdbg_parse.py log"""
 import sys, collections
 rows=[l.split() for l in open(sys.argv[1]) if l.startswith('ENT ')]
 # keep the last launch: take last 2048 lines
